@@ -1,0 +1,327 @@
+// extern "C" surface of the host runtime (see include/kungfu_host.h).
+#include <cstring>
+#include <string>
+
+#include "../../include/kungfu_host.h"
+#include "core/base.hpp"
+#include "core/graph.hpp"
+#include "core/log.hpp"
+#include "core/plan.hpp"
+#include "ctrl/peer.hpp"
+#include "elastic/runner.hpp"
+
+using namespace kf;
+
+struct kf_peer {
+    std::unique_ptr<Peer> peer;
+};
+
+static thread_local std::string g_err;
+
+static int fail(const std::string &e)
+{
+    g_err = e;
+    return -1;
+}
+
+static int done(kf_peer *p, bool ok)
+{
+    if (ok) return 0;
+    g_err = p->peer->last_error();
+    return -1;
+}
+
+static Workspace ws(const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    Workspace w;
+    w.send  = send;
+    w.recv  = recv;
+    w.count = (size_t)count;
+    w.dtype = (uint32_t)dtype;
+    w.op    = (Op)op;
+    w.name  = name ? name : "";
+    return w;
+}
+
+static int copy_out(const std::string &s, char *out, int cap)
+{
+    if ((int)s.size() + 1 > cap) return fail("output buffer too small");
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)s.size();
+}
+
+extern "C" {
+
+const char *kf_last_error(void) { return g_err.c_str(); }
+
+kf_peer *kf_peer_create_from_env(void)
+{
+    PeerConfig cfg;
+    std::string err;
+    if (!PeerConfig::from_env(&cfg, &err)) {
+        g_err = err;
+        return nullptr;
+    }
+    kf_peer *p = new kf_peer();
+    p->peer.reset(new Peer(cfg));
+    return p;
+}
+
+int kf_peer_start(kf_peer *p) { return done(p, p->peer->start()); }
+
+void kf_peer_close(kf_peer *p)
+{
+    if (!p) return;
+    p->peer->close();
+    delete p;
+}
+
+int kf_rank(kf_peer *p) { return p->peer->session()->rank(); }
+int kf_size(kf_peer *p) { return p->peer->session()->size(); }
+int kf_local_rank(kf_peer *p) { return p->peer->session()->local_rank(); }
+int kf_local_size(kf_peer *p) { return p->peer->session()->local_size(); }
+int kf_host_count(kf_peer *p) { return p->peer->session()->host_count(); }
+int kf_detached(kf_peer *p) { return p->peer->detached() ? 1 : 0; }
+int kf_cluster_version(kf_peer *p) { return p->peer->cluster_version(); }
+uint64_t kf_uid(kf_peer *p) { return p->peer->uid(); }
+
+int kf_peer_addr(kf_peer *p, int rank, char *buf, int cap)
+{
+    Session *s = p->peer->session();
+    if (rank < 0 || rank >= s->size()) return fail("bad rank");
+    return copy_out(s->peers()[rank].str(), buf, cap) < 0 ? -1 : 0;
+}
+
+int kf_barrier(kf_peer *p) { return done(p, p->peer->session()->barrier()); }
+
+#define KF_CHECK_DTYPE(dt)                                                     \
+    if (!dtype_valid((uint32_t)(dt))) return fail("unsupported dtype code " + std::to_string(dt))
+
+int kf_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    StallDetector sd(std::string("all_reduce ") + (name ? name : ""));
+    return done(p, p->peer->session()->all_reduce(ws(send, recv, count, dtype, op, name)));
+}
+
+int kf_monitored_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op,
+                            const int32_t *tree, int tree_len, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    Session *s = p->peer->session();
+    if (tree && tree_len > 0) {
+        std::vector<int32_t> forest(tree, tree + tree_len);
+        if (!s->set_tree(forest)) return done(p, false);
+    }
+    return done(p, s->monitored_all_reduce(ws(send, recv, count, dtype, op, name)));
+}
+
+int kf_cross_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->cross_all_reduce(ws(send, recv, count, dtype, op, name)));
+}
+
+int kf_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->reduce(ws(send, recv, count, dtype, op, name)));
+}
+
+int kf_broadcast(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->broadcast(ws(send, recv, count, dtype, SUM, name)));
+}
+
+int kf_local_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->local_reduce(ws(send, recv, count, dtype, op, name)));
+}
+
+int kf_local_broadcast(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->local_broadcast(ws(send, recv, count, dtype, SUM, name)));
+}
+
+int kf_all_gather(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->all_gather(ws(send, recv, count, dtype, SUM, name)));
+}
+
+int kf_gather(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    return done(p, p->peer->session()->gather(ws(send, recv, count, dtype, SUM, name)));
+}
+
+int kf_consensus(kf_peer *p, const void *data, int64_t nbytes, const char *name, int *agree)
+{
+    bool a        = false;
+    const bool ok = p->peer->session()->bytes_consensus(data, (size_t)nbytes, name ? name : "", &a);
+    if (agree) *agree = a ? 1 : 0;
+    return done(p, ok);
+}
+
+int64_t kf_all_reduce_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
+{
+    if (!dtype_valid((uint32_t)dtype)) return fail("unsupported dtype");
+    Workspace w = ws(send, recv, count, dtype, op, name);
+    Peer *peer  = p->peer.get();
+    return peer->submit([peer, w] { return peer->session()->all_reduce(w); });
+}
+
+int64_t kf_broadcast_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name)
+{
+    if (!dtype_valid((uint32_t)dtype)) return fail("unsupported dtype");
+    Workspace w = ws(send, recv, count, dtype, SUM, name);
+    Peer *peer  = p->peer.get();
+    return peer->submit([peer, w] { return peer->session()->broadcast(w); });
+}
+
+int kf_wait_handle(kf_peer *p, int64_t handle) { return done(p, p->peer->wait(handle)); }
+
+int kf_save(kf_peer *p, const char *version, const char *name, const void *data, int64_t nbytes)
+{
+    p->peer->save(version ? version : "", name, data, (size_t)nbytes);
+    return 0;
+}
+
+int kf_request(kf_peer *p, int target_rank, const char *version, const char *name, void *buf, int64_t nbytes)
+{
+    return done(p, p->peer->request(target_rank, version ? version : "", name, buf, (size_t)nbytes));
+}
+
+int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached)
+{
+    bool c = false, d = false;
+    const bool ok = p->peer->resize_cluster(new_size, &c, &d);
+    *changed  = c;
+    *detached = d;
+    return done(p, ok);
+}
+
+int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached)
+{
+    bool c = false, d = false;
+    const bool ok = p->peer->resize_cluster_from_url(&c, &d);
+    *changed  = c;
+    *detached = d;
+    return done(p, ok);
+}
+
+int kf_propose_new_size(kf_peer *p, int new_size) { return done(p, p->peer->propose_new_size(new_size)); }
+
+int kf_set_tree(kf_peer *p, const int32_t *forest, int n)
+{
+    return done(p, p->peer->session()->set_tree(std::vector<int32_t>(forest, forest + n)));
+}
+
+int kf_set_strategy(kf_peer *p, const char *name)
+{
+    Strategy s;
+    if (!parse_strategy(name, &s)) return fail(std::string("unknown strategy ") + name);
+    return done(p, p->peer->session()->set_strategy(s));
+}
+
+int kf_calc_stats(kf_peer *p)
+{
+    p->peer->session()->calc_stats();
+    return 0;
+}
+int kf_log_stats(kf_peer *p)
+{
+    p->peer->session()->log_stats();
+    return 0;
+}
+int kf_print_strategy_stats(kf_peer *p)
+{
+    p->peer->session()->print_strategy_stats();
+    return 0;
+}
+int kf_check_interference(kf_peer *p) { return p->peer->session()->check_interference() ? 1 : 0; }
+
+int kf_get_peer_latencies(kf_peer *p, float *out, int n)
+{
+    auto v = p->peer->session()->peer_latencies();
+    for (int i = 0; i < n && i < (int)v.size(); ++i) out[i] = v[i];
+    return 0;
+}
+
+int kf_egress_rates(kf_peer *p, float *out, int n)
+{
+    auto v = p->peer->egress_rates();
+    for (int i = 0; i < n && i < (int)v.size(); ++i) out[i] = v[i];
+    return 0;
+}
+
+int kf_send_fd(kf_peer *p, int target_rank, const char *tag, int fd)
+{
+    return done(p, p->peer->send_fd(target_rank, tag, fd));
+}
+
+int kf_recv_fd(kf_peer *p, int src_rank, const char *tag, int *fd) { return done(p, p->peer->recv_fd(src_rank, tag, fd)); }
+
+// ---- planner utilities ---------------------------------------------------------------
+int kf_gen_strategy_graphs(const char *peers_csv, const char *strategy, char *out, int cap)
+{
+    PeerList peers;
+    Strategy s;
+    if (!parse_peer_list(peers_csv, &peers)) return fail("bad peer list");
+    if (!parse_strategy(strategy, &s)) return fail("unknown strategy");
+    std::string text;
+    for (auto &sg : gen_global_strategies(peers, s))
+        text += "reduce=" + sg.reduce.debug_string() + " bcast=" + sg.bcast.debug_string() + "\n";
+    return copy_out(text, out, cap);
+}
+
+int kf_minimum_spanning_tree(const float *weights, int n, int32_t *edges_out)
+{
+    std::vector<float> w(weights, weights + (size_t)n * n);
+    auto e = minimum_spanning_tree(w, n);
+    for (size_t i = 0; i < e.size(); ++i) edges_out[i] = e[i];
+    return (int)e.size() / 2;
+}
+
+void kf_transform2(const void *x, const void *y, void *z, int64_t n, int dtype, int op)
+{
+    transform2(x, y, z, (size_t)n, (uint32_t)dtype, (Op)op);
+}
+
+int kf_cluster_resize(const char *cluster_json, int new_size, char *out, int cap)
+{
+    Cluster c, next;
+    std::string err;
+    if (!parse_cluster_json(cluster_json, &c, &err)) return fail(err);
+    if (!c.validate(&err)) return fail(err);
+    if (!c.resize(new_size, &next, &err)) return fail(err);
+    return copy_out(next.json(), out, cap);
+}
+
+int kf_parse_hostfile(const char *text, char *out, int cap)
+{
+    HostList hl;
+    std::string err;
+    if (!parse_hostfile(text, &hl, &err)) return fail(err);
+    return copy_out(hl.str(), out, cap);
+}
+
+int kf_gen_peer_list(const char *hostlist, int np, const char *port_range, char *out, int cap)
+{
+    HostList hl;
+    PortRange pr;
+    PeerList pl;
+    std::string err;
+    if (!parse_host_list(hostlist, &hl)) return fail("bad host list");
+    if (port_range && *port_range && !parse_port_range(port_range, &pr)) return fail("bad port range");
+    if (!hl.gen_peer_list(np, pr, &pl, &err)) return fail(err);
+    return copy_out(pl.str(), out, cap);
+}
+
+int kf_run_main(int argc, char **argv) { return kungfu_run_main(argc, argv); }
+int kf_config_server_main(int argc, char **argv) { return config_server_main(argc, argv); }
+
+}  // extern "C"

@@ -1,0 +1,914 @@
+// Fused data-parallel optimizer steps and multi-tensor helpers for sm_100a.
+//
+//   kfb_fuse / kfb_defuse        bucket gather/scatter with cast + ||g||^2
+//                                (reference: tf.concat fuse/defuse,
+//                                 srcs/python/kungfu/tensorflow/ops/__init__.py:29-46)
+//   kfb_ssgd_fused_step          reduce-scatter -> SGD on the owned shard ->
+//                                all-gather of the new parameters, one kernel
+//                                (sync_sgd.py:78-109 did allreduce, g/np and
+//                                 the optimizer as separate TF ops)
+//   kfb_sma_fused_step           model average + blend + local SGD, one kernel
+//                                (sma_sgd.py:50-74)
+//   kfb_pair_avg_step            one-sided peer pull + 1/2 blend + SGD + publish
+//                                (async_sgd.py:110-142, peer_to_peer.cpp:141-149)
+//   kfb_grad_variance            E[g^2]-E[g]^2 in one pass (grad_variance.py:46-59)
+//   kfb_gns_finalize             noise-scale estimators + EMA
+//                                (ops/monitor.py:6-17, cpu/collective.cpp:223-258)
+//
+// All flat buffers are processed in packets of 8 elements; the arenas that own
+// them pad every tensor to a multiple of 16 elements.
+#include <cstring>
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace kfb {
+
+// ---- 8-element packets of any storage type as fp32 ---------------------------
+template <typename T> struct Pk8;
+template <> struct Pk8<float> {
+    __device__ static void load(const void *base, long long i, float *v)
+    {
+        const uint4 *p = reinterpret_cast<const uint4 *>(
+                             reinterpret_cast<const float *>(base)) +
+                         2 * i;
+        const uint4 a = ld_stream16(p), b = ld_stream16(p + 1);
+        Pack<float>::unpack(a, v);
+        Pack<float>::unpack(b, v + 4);
+    }
+    __device__ static void store(void *base, long long i, const float *v)
+    {
+        uint4 *p = reinterpret_cast<uint4 *>(base) + 2 * i;
+        st_stream16(p, Pack<float>::pack(v));
+        st_stream16(p + 1, Pack<float>::pack(v + 4));
+    }
+};
+template <> struct Pk8<__nv_bfloat16> {
+    __device__ static void load(const void *base, long long i, float *v)
+    {
+        Pack<__nv_bfloat16>::unpack(
+            ld_stream16(reinterpret_cast<const uint4 *>(base) + i), v);
+    }
+    __device__ static void store(void *base, long long i, const float *v)
+    {
+        st_stream16(reinterpret_cast<uint4 *>(base) + i,
+                    Pack<__nv_bfloat16>::pack(v));
+    }
+};
+template <> struct Pk8<__half> {
+    __device__ static void load(const void *base, long long i, float *v)
+    {
+        Pack<__half>::unpack(
+            ld_stream16(reinterpret_cast<const uint4 *>(base) + i), v);
+    }
+    __device__ static void store(void *base, long long i, const float *v)
+    {
+        st_stream16(reinterpret_cast<uint4 *>(base) + i, Pack<__half>::pack(v));
+    }
+};
+
+struct SgdH {
+    float lr, momentum, dampening, wd;
+    int nesterov, first;
+};
+
+// torch.optim.SGD update on 8 lanes; p/m are fp32 master and momentum.
+__device__ __forceinline__ void
+sgd_update8(float *p, float *m, const float *g, const SgdH &h)
+{
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        float d = fmaf(h.wd, p[k], g[k]);
+        if (h.momentum != 0.f) {
+            m[k] = h.first ? d : fmaf(h.momentum, m[k], (1.f - h.dampening) * d);
+            d    = h.nesterov ? fmaf(h.momentum, m[k], d) : m[k];
+        }
+        p[k] = fmaf(-h.lr, d, p[k]);
+    }
+}
+
+static SgdH to_h(const kfb_sgd_hyper *h)
+{
+    SgdH r;
+    r.lr       = h->lr;
+    r.momentum = h->momentum;
+    r.dampening = h->dampening;
+    r.wd       = h->weight_decay;
+    r.nesterov = h->nesterov;
+    r.first    = h->first_step;
+    return r;
+}
+
+// ---- fuse / defuse -------------------------------------------------------------
+#define KFB_FUSE_MAX 64
+struct FuseArgs {
+    const void *src[KFB_FUSE_MAX];
+    long long count[KFB_FUSE_MAX];
+    long long off[KFB_FUSE_MAX];
+    int n;
+};
+
+template <typename S> __device__ __forceinline__ float to_f32(S x);
+template <> __device__ __forceinline__ float to_f32<float>(float x) { return x; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 x) { return __bfloat162float(x); }
+template <> __device__ __forceinline__ float to_f32<__half>(__half x) { return __half2float(x); }
+template <typename D> __device__ __forceinline__ D from_f32(float x);
+template <> __device__ __forceinline__ float from_f32<float>(float x) { return x; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float x) { return __float2bfloat16_rn(x); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float x) { return __float2half_rn(x); }
+
+// grid = (blocks_x, n tensors). Sources are arbitrary torch tensors (only
+// element-aligned), so this kernel is scalar on the source side when the
+// source is not 16-byte aligned, vector otherwise. Block partial sums of x^2
+// go to scratch[blockIdx.y * gridDim.x + blockIdx.x] -- fixed slots, summed in
+// slot order by k_sum_slots, so the norm is reproducible.
+template <typename S, typename D, bool DEFUSE>
+__global__ void __launch_bounds__(256)
+    k_fuse(const __grid_constant__ FuseArgs a, void *flat, float *partials)
+{
+    const int t            = blockIdx.y;
+    const long long n      = a.count[t];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    float ss               = 0.f;
+    if (!DEFUSE) {
+        const S *src = reinterpret_cast<const S *>(a.src[t]);
+        D *dst       = reinterpret_cast<D *>(flat) + a.off[t];
+        constexpr int V = 16 / sizeof(S);  // source elements per 16 bytes
+        const bool vec_ok = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
+                            ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+        const long long nv = vec_ok ? n / V : 0;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+             i < nv; i += stride) {
+            const uint4 v = ld_stream16(reinterpret_cast<const uint4 *>(src) + i);
+            const S *e    = reinterpret_cast<const S *>(&v);
+            alignas(16) D o[V];
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                const float f = to_f32<S>(e[k]);
+                ss            = fmaf(f, f, ss);
+                o[k]          = from_f32<D>(f);
+            }
+            if (sizeof(D) == sizeof(S)) {
+                st_stream16(reinterpret_cast<uint4 *>(dst) + i,
+                            *reinterpret_cast<const uint4 *>(o));
+            } else if (sizeof(D) < sizeof(S)) {  // f32 -> 16-bit: 8 bytes out
+                *reinterpret_cast<uint2 *>(dst + i * V) =
+                    *reinterpret_cast<const uint2 *>(o);
+            } else {  // 16-bit -> f32: 32 bytes out
+                uint4 *q = reinterpret_cast<uint4 *>(dst + i * V);
+                st_stream16(q, reinterpret_cast<const uint4 *>(o)[0]);
+                st_stream16(q + 1, reinterpret_cast<const uint4 *>(o)[1]);
+            }
+        }
+        for (long long i = nv * V + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+             i < n; i += stride) {
+            const float f = to_f32<S>(src[i]);
+            ss            = fmaf(f, f, ss);
+            dst[i]        = from_f32<D>(f);
+        }
+        if (partials) {
+            __shared__ float red[32];
+            const float part = block_sum(ss, red);
+            if (threadIdx.x == 0)
+                partials[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = part;
+        }
+    } else {
+        // flat (S) -> tensors (D)
+        const S *src = reinterpret_cast<const S *>(flat) + a.off[t];
+        D *dst       = reinterpret_cast<D *>(const_cast<void *>(a.src[t]));
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+             i < n; i += stride)
+            dst[i] = from_f32<D>(to_f32<S>(src[i]));
+    }
+}
+
+// out[0] (+)= sum of partials[0..n) in index order, one warp-free thread per
+// 32 slots then a serial tail: deterministic and cheap (n is a few thousand).
+__global__ void k_sum_slots(const float *partials, int n, float *out,
+                            int accumulate)
+{
+    __shared__ float part[256];
+    // thread t sums slots [t*chunk, (t+1)*chunk) serially; thread 0 then adds
+    // the 256 chunk sums serially: the expression tree depends only on n.
+    const int chunk = (n + 255) / 256;
+    float s         = 0.f;
+    for (int i = threadIdx.x * chunk; i < min(n, (int)(threadIdx.x + 1) * chunk); ++i)
+        s += partials[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.f;
+        for (int i = 0; i < 256; ++i) t += part[i];
+        out[0] = accumulate ? out[0] + t : t;
+    }
+}
+
+// ---- S-SGD fused step --------------------------------------------------------------
+struct StepArgs {
+    PeerPads pads;
+    uint32_t *local_epoch;
+    float *scratch;
+    void *grads[KFB_MAX_RANKS];
+    void *params[KFB_MAX_RANKS];
+    void *stage[KFB_MAX_RANKS];
+    const void *grad_local;
+    float *master;
+    float *mom;
+    long long npk;  // number of 8-element packets
+    float grad_scale;
+    float alpha;
+    SgdH h;
+    int rank, np;
+    float *sumsq_out;
+};
+
+template <typename G, typename P, int NP, bool NORM>
+__global__ void __launch_bounds__(512)
+    k_ssgd_fused(const __grid_constant__ StepArgs a)
+{
+    const int rank = a.rank < 0 ? (int)blockIdx.y : a.rank;
+    const int np   = NP > 0 ? NP : a.np;
+    uint32_t *epoch =
+        a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
+    float *scratch = a.scratch + (a.rank < 0 ? rank * KFB_SCRATCH_FLOATS : 0);
+    // emulation: each emulated rank has its own master/momentum copy
+    float *master = a.master + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    float *mom    = a.mom + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    __shared__ float red[32];
+
+    if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+    const long long per    = (a.npk + np - 1) / np;
+    const long long lo     = (long long)rank * per;
+    const long long hi     = min(lo + per, a.npk);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    float ss               = 0.f;
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+         i < hi; i += stride) {
+        float g[8];
+        if (NP > 0) {
+            float t[NP > 0 ? NP : 1][8];
+#pragma unroll
+            for (int r = 0; r < NP; ++r) Pk8<G>::load(a.grads[r], i, t[r]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] = t[0][k];
+#pragma unroll
+            for (int r = 1; r < NP; ++r)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] += t[r][k];
+        } else {
+            Pk8<G>::load(a.grads[0], i, g);
+            for (int r = 1; r < np; ++r) {
+                float t[8];
+                Pk8<G>::load(a.grads[r], i, t);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] += t[k];
+            }
+        }
+        float p[8], m[8];
+        Pk8<float>::load(master, i, p);
+        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(mom, i, m);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            g[k] *= a.grad_scale;
+            if (NORM) ss = fmaf(g[k], g[k], ss);
+        }
+        sgd_update8(p, m, g, a.h);
+        Pk8<float>::store(master, i, p);
+        if (a.h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+        for (int k = 0; k < np; ++k) Pk8<P>::store(a.params[(rank + k) % np], i, p);
+    }
+    if (NORM) {
+        const float part = block_sum(ss, red);
+        __shared__ float s_part;
+        if (threadIdx.x == 0) s_part = part;
+        __syncthreads();
+        if (threadIdx.x < np)
+            st_relaxed_sys_f32(
+                pad_scalar(a.pads.pad[threadIdx.x], blockIdx.x, rank), s_part);
+    }
+    if (np > 1 || NORM) {
+        if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+        else __syncthreads();
+    }
+    if (NORM) {
+        __shared__ bool is_last;
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int r = 0; r < np; ++r)
+                t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            scratch[blockIdx.x] = t;
+            __threadfence();
+            unsigned int *ticket =
+                reinterpret_cast<unsigned int *>(scratch + KFB_MAX_BLOCKS);
+            is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+        }
+        __syncthreads();
+        if (is_last && threadIdx.x == 0) {
+            __threadfence();
+            float t = 0.f;
+            for (unsigned b = 0; b < gridDim.x; ++b)
+                t += *reinterpret_cast<volatile float *>(scratch + b);
+            a.sumsq_out[a.rank < 0 ? rank : 0] = t;
+            *reinterpret_cast<unsigned int *>(scratch + KFB_MAX_BLOCKS) = 0u;
+        }
+    }
+}
+
+// Plain local flat SGD on a reduced gradient (any-rank, no peers).
+template <typename G, typename P>
+__global__ void __launch_bounds__(512)
+    k_sgd_flat(const void *grad, void *param, float *master, float *mom,
+               long long npk, float grad_scale, SgdH h)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+         i < npk; i += stride) {
+        float g[8], p[8], m[8];
+        Pk8<G>::load(grad, i, g);
+        Pk8<float>::load(master, i, p);
+        if (h.momentum != 0.f && !h.first) Pk8<float>::load(mom, i, m);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) g[k] *= grad_scale;
+        sgd_update8(p, m, g, h);
+        Pk8<float>::store(master, i, p);
+        if (h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+        if (param != (void *)master) Pk8<P>::store(param, i, p);
+    }
+}
+
+// ---- SMA fused step -------------------------------------------------------------------
+template <typename G, typename P>
+__global__ void __launch_bounds__(512)
+    k_sma_fused(const __grid_constant__ StepArgs a)
+{
+    const int rank = a.rank < 0 ? (int)blockIdx.y : a.rank;
+    const int np   = a.np;
+    uint32_t *epoch =
+        a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
+    float *master = a.master + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    float *mom    = a.mom + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    const void *grad =
+        a.rank < 0 ? a.grads[rank] : a.grad_local;  // LOCAL gradient
+    const long long per    = (a.npk + np - 1) / np;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const float inv_np     = 1.f / (float)np;
+
+    if (np > 1) {
+        // phase 1: average my shard of everybody's parameters, push to all
+        peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+        const long long lo = (long long)rank * per;
+        const long long hi = min(lo + per, a.npk);
+        for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+             i < hi; i += stride) {
+            float s[8];
+            Pk8<P>::load(a.params[0], i, s);
+            for (int r = 1; r < np; ++r) {
+                float t[8];
+                Pk8<P>::load(a.params[r], i, t);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] += t[k];
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] *= inv_np;
+            for (int k = 0; k < np; ++k)
+                Pk8<float>::store(a.stage[(rank + k) % np], i, s);
+        }
+        // CTA b of every rank has now (1) read the slice of my parameters it
+        // needs and (2) delivered its slice of the average to me.
+        peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+    }
+    // phase 2: blend + local SGD over exactly the packets CTA b of each rank
+    // touched in phase 1 (same grid-stride pattern inside every shard).
+    for (int s_ = 0; s_ < np; ++s_) {
+        const long long lo = (long long)s_ * per;
+        const long long hi = min(lo + per, a.npk);
+        for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+             i < hi; i += stride) {
+            float p[8], m[8], g[8];
+            Pk8<float>::load(master, i, p);
+            if (np > 1) {
+                float avg[8];
+                Pk8<float>::load(a.stage[rank], i, avg);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    p[k] = fmaf(a.alpha, avg[k] - p[k], p[k]);
+            }
+            Pk8<G>::load(grad, i, g);
+            if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(mom, i, m);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g[k] *= a.grad_scale;
+            sgd_update8(p, m, g, a.h);
+            Pk8<float>::store(master, i, p);
+            if (a.h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+            Pk8<P>::store(a.params[rank], i, p);
+        }
+    }
+}
+
+// ---- PairAveraging fused step ---------------------------------------------------------
+struct PairArgs {
+    uint32_t *seq_peer;  // peer's published version word (peer mapped)
+    uint32_t *seq_self;
+    const void *snap_peer;
+    void *snap_self;
+    long long slot_bytes;
+    void *param;
+    const void *grad;
+    float *master;
+    float *mom;
+    float *scratch;
+    long long npk;
+    float grad_scale;
+    SgdH h;
+    int32_t *torn_out;
+    int has_peer;
+};
+
+template <typename G, typename P>
+__global__ void __launch_bounds__(512)
+    k_pair_avg(const __grid_constant__ PairArgs a)
+{
+    __shared__ uint32_t s_k, s_self;
+    if (threadIdx.x == 0) {
+        s_k    = a.has_peer ? ld_acquire_sys(a.seq_peer) : 0u;
+        s_self = ld_relaxed_sys(a.seq_self);
+    }
+    __syncthreads();
+    const uint32_t k = s_k, kself = s_self;
+    const char *peer =
+        reinterpret_cast<const char *>(a.snap_peer) + (k & 1) * a.slot_bytes;
+    char *mine =
+        reinterpret_cast<char *>(a.snap_self) + ((kself + 1) & 1) * a.slot_bytes;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+         i < a.npk; i += stride) {
+        float p[8], m[8], g[8];
+        Pk8<float>::load(a.master, i, p);
+        if (k != 0) {  // peer has published at least once
+            float o[8];
+            Pk8<P>::load(peer, i, o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) p[j] = 0.5f * (p[j] + o[j]);
+        }
+        Pk8<G>::load(a.grad, i, g);
+        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(a.mom, i, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] *= a.grad_scale;
+        sgd_update8(p, m, g, a.h);
+        Pk8<float>::store(a.master, i, p);
+        if (a.h.momentum != 0.f) Pk8<float>::store(a.mom, i, m);
+        Pk8<P>::store(a.param, i, p);
+        Pk8<P>::store(mine, i, p);
+    }
+    // The last CTA to finish publishes the new version; it also checks whether
+    // the slot we read was recycled underneath us (peer advanced >= 2).
+    __shared__ bool is_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        unsigned int *ticket =
+            reinterpret_cast<unsigned int *>(a.scratch + KFB_MAX_BLOCKS + 1);
+        is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+        if (is_last) {
+            *ticket = 0u;
+            __threadfence_system();
+            st_release_sys(a.seq_self, kself + 1);
+            if (a.has_peer && a.torn_out && k != 0) {
+                const uint32_t k2 = ld_acquire_sys(a.seq_peer);
+                if (k2 - k >= 2u) atomicAdd(a.torn_out, 1);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(512)
+    k_pair_publish(uint32_t *seq_self, const uint4 *param, char *snap_self,
+                   long long slot_bytes, long long nvec, float *scratch)
+{
+    __shared__ uint32_t s_self;
+    if (threadIdx.x == 0) s_self = ld_relaxed_sys(seq_self);
+    __syncthreads();
+    const uint32_t kself = s_self;
+    uint4 *mine = reinterpret_cast<uint4 *>(snap_self + ((kself + 1) & 1) * slot_bytes);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+         i < nvec; i += stride)
+        st_stream16(mine + i, ld_stream16(param + i));
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        unsigned int *ticket =
+            reinterpret_cast<unsigned int *>(scratch + KFB_MAX_BLOCKS + 1);
+        if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+            *ticket = 0u;
+            __threadfence_system();
+            st_release_sys(seq_self, kself + 1);
+        }
+    }
+}
+
+// ---- gradient variance -----------------------------------------------------------------
+struct VarArgs {
+    PeerPads pads;
+    uint32_t *local_epoch;
+    void *grads[KFB_MAX_RANKS];
+    const long long *seg_ends;  // device, cumulative element offsets
+    int n_seg;
+    float *seg_out;  // device float[n_seg]: this rank's partial sum of v^2
+    long long npk;
+    int rank, np;
+};
+
+template <typename G>
+__global__ void __launch_bounds__(512)
+    k_grad_variance(const __grid_constant__ VarArgs a)
+{
+    const int rank = a.rank < 0 ? (int)blockIdx.y : a.rank;
+    const int np   = a.np;
+    uint32_t *epoch =
+        a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
+    float *seg_out = a.seg_out + (a.rank < 0 ? rank * a.n_seg : 0);
+    if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+    const long long per    = (a.npk + np - 1) / np;
+    const long long lo     = (long long)rank * per;
+    const long long hi     = min(lo + per, a.npk);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const float inv_np     = 1.f / (float)np;
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+         i < hi; i += stride) {
+        float s1[8], s2[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+        for (int r = 0; r < np; ++r) {
+            float t[8];
+            Pk8<G>::load(a.grads[r], i, t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                s1[k] += t[k];
+                s2[k] = fmaf(t[k], t[k], s2[k]);
+            }
+        }
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float mean = s1[k] * inv_np;
+            const float v    = s2[k] * inv_np - mean * mean;
+            acc              = fmaf(v, v, acc);
+        }
+        // segment of this packet: first seg whose end > element index
+        const long long e = i * 8;
+        int l = 0, h = a.n_seg - 1;
+        while (l < h) {
+            const int mid = (l + h) >> 1;
+            if (a.seg_ends[mid] > e) h = mid;
+            else l = mid + 1;
+        }
+        atomicAdd(seg_out + l, acc);
+    }
+    if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+}
+
+__global__ void k_gns_finalize(const float *ss_local, const float *ss_global,
+                               float b_small, float b_big, float alpha,
+                               float *state)
+{
+    // G = (B_big |G_big|^2 - B_small |G_small|^2) / (B_big - B_small)
+    // S = (|G_small|^2 - |G_big|^2) / (1/B_small - 1/B_big)
+    const float gs = *ss_local, gb = *ss_global;
+    const float G  = (b_big * gb - b_small * gs) / (b_big - b_small);
+    const float S  = (gs - gb) / (1.f / b_small - 1.f / b_big);
+    float g_ema, s_ema;
+    if (state[2] != 0.f) {
+        g_ema = alpha * state[0] + (1.f - alpha) * G;
+        s_ema = alpha * state[1] + (1.f - alpha) * S;
+    } else {
+        g_ema = G;
+        s_ema = S;
+    }
+    state[0] = g_ema;
+    state[1] = s_ema;
+    state[2] = 1.f;
+    state[3] = s_ema / g_ema;
+}
+
+static void fill_pads(PeerPads &p, const kfb_comm *c)
+{
+    for (int r = 0; r < KFB_MAX_RANKS; ++r)
+        p.pad[r] = reinterpret_cast<uint32_t *>(r < c->np ? c->pads[r] : nullptr);
+}
+
+static int check_launch(const kfb_comm *c, int blocks, int threads)
+{
+    if (!c || c->np < 1 || c->np > KFB_MAX_RANKS || c->rank >= c->np) {
+        set_last_error("bad communicator");
+        return KFB_ERR_ARG;
+    }
+    if (blocks < 1 || blocks > KFB_MAX_BLOCKS || threads < 32 ||
+        threads > 512 || threads % 32) {
+        set_last_error("bad launch shape blocks=%d threads=%d (max %d x 512)",
+                       blocks, threads, KFB_MAX_BLOCKS);
+        return KFB_ERR_ARG;
+    }
+    return KFB_OK;
+}
+
+template <typename K, typename A>
+static int launch_step(const kfb_comm *c, K kernel, int blocks, int threads,
+                       cudaStream_t s, const A &args)
+{
+    if (c->rank < 0) {
+        void *argv[] = {(void *)&args};
+        KFB_CUDA_OK(cudaLaunchCooperativeKernel((const void *)kernel,
+                                                dim3(blocks, c->np),
+                                                dim3(threads), argv, 0, s));
+    } else {
+        kernel<<<blocks, threads, 0, s>>>(args);
+        KFB_CUDA_OK(cudaGetLastError());
+    }
+    return KFB_OK;
+}
+
+}  // namespace kfb
+
+using namespace kfb;
+
+#define KFB_DISPATCH_FLOAT(dt, T, ...)                                         \
+    switch (dt) {                                                              \
+    case KFB_F32: { using T = float; __VA_ARGS__; } break;                     \
+    case KFB_BF16: { using T = __nv_bfloat16; __VA_ARGS__; } break;            \
+    case KFB_F16: { using T = __half; __VA_ARGS__; } break;                    \
+    default: set_last_error("dtype %d must be f32/bf16/f16", dt); return KFB_ERR_ARG; \
+    }
+
+extern "C" int kfb_fuse(void *const *srcs, const int64_t *counts,
+                        const int64_t *dst_offs, int n, int src_dtype,
+                        void *dst, int dst_dtype, float *sumsq_out,
+                        float *scratch, void *stream)
+{
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    // scratch layout: KFB_FUSE_MAX * FUSE_BX partial slots per launch.
+    constexpr int BX = 16;
+    bool first       = true;
+    for (int base = 0; base < n; base += KFB_FUSE_MAX) {
+        FuseArgs a;
+        memset(&a, 0, sizeof(a));
+        a.n = std::min(KFB_FUSE_MAX, n - base);
+        for (int i = 0; i < a.n; ++i) {
+            a.src[i]   = srcs[base + i];
+            a.count[i] = counts[base + i];
+            a.off[i]   = dst_offs[base + i];
+        }
+        float *partials = sumsq_out ? scratch : nullptr;
+        if (sumsq_out && !scratch) {
+            set_last_error("kfb_fuse: sumsq_out needs scratch of %d floats",
+                           KFB_FUSE_MAX * BX);
+            return KFB_ERR_ARG;
+        }
+        dim3 grid(BX, a.n);
+        KFB_DISPATCH_FLOAT(src_dtype, S,
+            KFB_DISPATCH_FLOAT(dst_dtype, D,
+                (k_fuse<S, D, false><<<grid, 256, 0, s>>>(a, dst, partials))));
+        KFB_CUDA_OK(cudaGetLastError());
+        if (sumsq_out) {
+            k_sum_slots<<<1, 256, 0, s>>>(partials, BX * a.n, sumsq_out,
+                                          first ? 0 : 1);
+            KFB_CUDA_OK(cudaGetLastError());
+        }
+        first = false;
+    }
+    return KFB_OK;
+}
+
+extern "C" int kfb_defuse(const void *src, int src_dtype, void *const *dsts,
+                          const int64_t *counts, const int64_t *src_offs,
+                          int n, int dst_dtype, void *stream)
+{
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    for (int base = 0; base < n; base += KFB_FUSE_MAX) {
+        FuseArgs a;
+        memset(&a, 0, sizeof(a));
+        a.n = std::min(KFB_FUSE_MAX, n - base);
+        for (int i = 0; i < a.n; ++i) {
+            a.src[i]   = dsts[base + i];
+            a.count[i] = counts[base + i];
+            a.off[i]   = src_offs[base + i];
+        }
+        dim3 grid(16, a.n);
+        KFB_DISPATCH_FLOAT(src_dtype, S,
+            KFB_DISPATCH_FLOAT(dst_dtype, D,
+                (k_fuse<S, D, true><<<grid, 256, 0, s>>>(a, const_cast<void *>(src), nullptr))));
+        KFB_CUDA_OK(cudaGetLastError());
+    }
+    return KFB_OK;
+}
+
+static int fill_step(StepArgs &a, const kfb_comm *c, int64_t count)
+{
+    if (count % 8) {
+        set_last_error("flat buffers must hold a multiple of 8 elements (got %lld)",
+                       (long long)count);
+        return KFB_ERR_ARG;
+    }
+    memset(&a, 0, sizeof(a));
+    fill_pads(a.pads, c);
+    a.local_epoch = reinterpret_cast<uint32_t *>(c->local_epoch);
+    a.scratch     = reinterpret_cast<float *>(c->scratch);
+    a.rank        = c->rank;
+    a.np          = c->np;
+    a.npk         = count / 8;
+    return KFB_OK;
+}
+
+extern "C" int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
+                                   int grad_dtype, void *const *params,
+                                   int param_dtype, float *master, float *mom,
+                                   int64_t count, float grad_scale,
+                                   const kfb_sgd_hyper *h, float *sumsq_out,
+                                   int blocks, int threads, void *stream)
+{
+    int rc = check_launch(comm, blocks, threads);
+    if (rc) return rc;
+    StepArgs a;
+    rc = fill_step(a, comm, count);
+    if (rc) return rc;
+    for (int r = 0; r < comm->np; ++r) {
+        a.grads[r]  = grads[r];
+        a.params[r] = params[r];
+    }
+    a.master     = master;
+    a.mom        = mom;
+    a.grad_scale = grad_scale;
+    a.h          = to_h(h);
+    a.sumsq_out  = sumsq_out;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const int np   = comm->np;
+#define KFB_SSGD(NPV)                                                          \
+    do {                                                                       \
+        if (sumsq_out)                                                         \
+            return launch_step(comm, k_ssgd_fused<G, P, NPV, true>, blocks, threads, s, a);  \
+        return launch_step(comm, k_ssgd_fused<G, P, NPV, false>, blocks, threads, s, a);     \
+    } while (0)
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P, {
+            if (np == 1) KFB_SSGD(1);
+            if (np == 2) KFB_SSGD(2);
+            if (np == 4) KFB_SSGD(4);
+            if (np == 8) KFB_SSGD(8);
+            KFB_SSGD(0);
+        }));
+#undef KFB_SSGD
+    return KFB_OK;
+}
+
+extern "C" int kfb_sgd_flat(const void *grad, int grad_dtype, void *param,
+                            int param_dtype, float *master, float *mom,
+                            int64_t count, float grad_scale,
+                            const kfb_sgd_hyper *h, int blocks, int threads,
+                            void *stream)
+{
+    if (count % 8) {
+        set_last_error("flat buffers must hold a multiple of 8 elements");
+        return KFB_ERR_ARG;
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const SgdH hh  = to_h(h);
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P,
+            (k_sgd_flat<G, P><<<blocks, threads, 0, s>>>(grad, param, master, mom, count / 8, grad_scale, hh))));
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+extern "C" int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
+                                  int param_dtype, void *const *avg_stage,
+                                  const void *grad, int grad_dtype,
+                                  float *master, float *mom, int64_t count,
+                                  float alpha, float grad_scale,
+                                  const kfb_sgd_hyper *h, int blocks,
+                                  int threads, void *stream)
+{
+    int rc = check_launch(comm, blocks, threads);
+    if (rc) return rc;
+    StepArgs a;
+    rc = fill_step(a, comm, count);
+    if (rc) return rc;
+    for (int r = 0; r < comm->np; ++r) {
+        a.params[r] = params[r];
+        a.stage[r]  = avg_stage ? avg_stage[r] : nullptr;
+        // emulation: `grad` is a host array of np device pointers
+        if (comm->rank < 0)
+            a.grads[r] = reinterpret_cast<void *const *>(grad)[r];
+    }
+    a.grad_local = grad;
+    a.master     = master;
+    a.mom        = mom;
+    a.alpha      = alpha;
+    a.grad_scale = grad_scale;
+    a.h          = to_h(h);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P,
+            return launch_step(comm, k_sma_fused<G, P>, blocks, threads, s, a)));
+    return KFB_OK;
+}
+
+extern "C" int kfb_pair_avg_step(const kfb_comm *comm, int target,
+                                 const void *snap_peer, void *snap_self,
+                                 int64_t slot_bytes, void *param,
+                                 int param_dtype, const void *grad,
+                                 int grad_dtype, float *master, float *mom,
+                                 int64_t count, float grad_scale,
+                                 const kfb_sgd_hyper *h, int32_t *torn_out,
+                                 int blocks, int threads, void *stream)
+{
+    if (!comm || comm->rank < 0 || comm->rank >= comm->np) {
+        set_last_error("pair averaging needs a real rank");
+        return KFB_ERR_ARG;
+    }
+    if (count % 8 || blocks < 1 || blocks > KFB_MAX_BLOCKS) {
+        set_last_error("bad count/blocks");
+        return KFB_ERR_ARG;
+    }
+    PairArgs a;
+    memset(&a, 0, sizeof(a));
+    a.has_peer = (target >= 0 && target < comm->np && target != comm->rank);
+    a.seq_self = reinterpret_cast<uint32_t *>(comm->pads[comm->rank]) + KFB_PAD_MISC_WORD;
+    a.seq_peer = a.has_peer ? reinterpret_cast<uint32_t *>(comm->pads[target]) + KFB_PAD_MISC_WORD
+                            : a.seq_self;
+    a.snap_peer  = snap_peer;
+    a.snap_self  = snap_self;
+    a.slot_bytes = slot_bytes;
+    a.param      = param;
+    a.grad       = grad;
+    a.master     = master;
+    a.mom        = mom;
+    a.scratch    = reinterpret_cast<float *>(comm->scratch);
+    a.npk        = count / 8;
+    a.grad_scale = grad_scale;
+    a.h          = to_h(h);
+    a.torn_out   = torn_out;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P,
+            (k_pair_avg<G, P><<<blocks, threads, 0, s>>>(a))));
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+extern "C" int kfb_pair_publish(const kfb_comm *comm, const void *param,
+                                void *snap_self, int64_t slot_bytes,
+                                int64_t bytes, int blocks, int threads,
+                                void *stream)
+{
+    if (!comm || comm->rank < 0) {
+        set_last_error("pair averaging needs a real rank");
+        return KFB_ERR_ARG;
+    }
+    uint32_t *seq = reinterpret_cast<uint32_t *>(comm->pads[comm->rank]) + KFB_PAD_MISC_WORD;
+    k_pair_publish<<<blocks, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        seq, reinterpret_cast<const uint4 *>(param),
+        reinterpret_cast<char *>(snap_self), slot_bytes, (bytes + 15) / 16,
+        reinterpret_cast<float *>(comm->scratch));
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+extern "C" int kfb_grad_variance(const kfb_comm *comm, void *const *grads,
+                                 int dtype, int64_t count,
+                                 const int64_t *seg_ends_dev, int n_seg,
+                                 float *seg_out, int blocks, int threads,
+                                 void *stream)
+{
+    int rc = check_launch(comm, blocks, threads);
+    if (rc) return rc;
+    if (count % 8 || n_seg < 1) {
+        set_last_error("bad count / n_seg");
+        return KFB_ERR_ARG;
+    }
+    VarArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_pads(a.pads, comm);
+    a.local_epoch = reinterpret_cast<uint32_t *>(comm->local_epoch);
+    for (int r = 0; r < comm->np; ++r) a.grads[r] = grads[r];
+    a.seg_ends = reinterpret_cast<const long long *>(seg_ends_dev);
+    a.n_seg    = n_seg;
+    a.seg_out  = seg_out;
+    a.npk      = count / 8;
+    a.rank     = comm->rank;
+    a.np       = comm->np;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(dtype, G,
+        return launch_step(comm, k_grad_variance<G>, blocks, threads, s, a));
+    return KFB_OK;
+}
+
+extern "C" int kfb_gns_finalize(const float *sumsq_local,
+                                const float *sumsq_global, float batch_small,
+                                float batch_big, float alpha, float *state,
+                                void *stream)
+{
+    k_gns_finalize<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        sumsq_local, sumsq_global, batch_small, batch_big, alpha, state);
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}

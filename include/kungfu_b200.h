@@ -1,0 +1,274 @@
+/* kungfu_b200 device library — C ABI (libkungfu_cuda.so).
+ *
+ * Every entry point returns 0 on success or a negative KFB_ERR_* code; the
+ * message for the last failure on the calling thread is kfb_last_error().
+ * All launches are asynchronous on the given stream unless stated otherwise.
+ *
+ * Reference parity notes cite files under /root/reference/.
+ */
+#ifndef KUNGFU_B200_H
+#define KUNGFU_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KFB_MAX_RANKS 16  /* one NVSwitch domain; B200 HGX has 8 */
+#define KFB_MAX_BLOCKS 128 /* persistent comm CTAs per launch (<= 148 SMs) */
+/* Layout of a rank's signal pad in symmetric memory (uint32 words):
+ *   [0, FLAG_WORDS)                 barrier flags   [block][src_rank]
+ *   [FLAG_WORDS, 2*FLAG_WORDS)      exchanged f32   [block][src_rank]
+ *   [2*FLAG_WORDS, +64)             seqlock / misc words
+ */
+#define KFB_PAD_FLAG_WORDS (KFB_MAX_BLOCKS * KFB_MAX_RANKS)
+#define KFB_PAD_MISC_WORD (2 * KFB_PAD_FLAG_WORDS)
+#define KFB_PAD_BYTES 32768
+/* local (non-peer) per-rank state: epoch counters + reduction scratch */
+#define KFB_STATE_EPOCH_WORDS KFB_MAX_BLOCKS
+#define KFB_SCRATCH_FLOATS (KFB_MAX_BLOCKS + 8)
+#define KFB_FUSE_SCRATCH_FLOATS 1024
+
+enum kfb_error {
+    KFB_OK          = 0,
+    KFB_ERR_ARG     = -1,
+    KFB_ERR_CUDA    = -2,
+    KFB_ERR_UNSUPP  = -3,
+    KFB_ERR_DRIVER  = -4,
+};
+
+enum kfb_dtype {
+    KFB_F32  = 0,
+    KFB_BF16 = 1,
+    KFB_F16  = 2,
+    KFB_I32  = 3,
+    KFB_F64  = 4,
+    KFB_I64  = 5,
+    KFB_U8   = 6,
+};
+
+/* same numeric values as KungFu_Op (srcs/cpp/include/kungfu/op.h:8-13) */
+enum kfb_op { KFB_OP_SUM = 0, KFB_OP_MIN = 1, KFB_OP_MAX = 2, KFB_OP_PROD = 3 };
+
+enum kfb_algo {
+    KFB_ALGO_ONESHOT = 0, /* every rank pulls all peers, reduces locally     */
+    KFB_ALGO_TWOSHOT = 1, /* pull-reduce own shard, push result to all peers */
+    KFB_ALGO_NVLS    = 2, /* multimem.ld_reduce + multimem.st (switch math)  */
+};
+
+/* A communicator as the kernels see it. rank < 0 selects single-GPU
+ * emulation: one cooperative launch whose blockIdx.y plays the rank, used by
+ * tests when there are fewer GPUs than ranks (all "peer" pointers are then
+ * local). */
+typedef struct kfb_comm {
+    int32_t rank;
+    int32_t np;
+    void *pads[KFB_MAX_RANKS]; /* peer-mapped signal pads, KFB_PAD_BYTES each */
+    void *local_epoch; /* uint32[KFB_STATE_EPOCH_WORDS] (emulation: x np)     */
+    void *scratch;     /* float[KFB_SCRATCH_FLOATS]      (emulation: x np)    */
+    void *mc_pad;      /* multicast alias of the pads (NVLS) or NULL          */
+} kfb_comm;
+
+const char *kfb_last_error(void);
+int kfb_device_info(int device, int *sm_count, int *cc_major, int *cc_minor,
+                    int *multicast_supported);
+
+/* ---- collectives over peer memory (replace K1-K3, K8-K12 of SURVEY §2.7;
+ *      reference: srcs/cpp/src/nccl/gpu_collective.cpp:96-127,
+ *      srcs/go/kungfu/session/session.go:98-286) ---------------------------- */
+
+/* out = scale * reduce_op(in[0..np)) elementwise. in[r]/out[r] are the
+ * peer-mapped addresses of rank r's buffers (same offset in every rank's
+ * symmetric arena). ONESHOT writes out[rank] only (may be any local buffer);
+ * TWOSHOT/NVLS write every out[r] and allow out == in. count is in elements;
+ * buffers must be 16-byte aligned and padded to a 16-byte multiple.
+ * sumsq_out (device float*, may be NULL, SUM only): receives ||out||^2 summed
+ * in a fixed order (bit-identical on every rank and run to run).
+ * mc_in/mc_out: multicast addresses (NVLS only). */
+int kfb_allreduce(const kfb_comm *comm, int algo, void *const *in,
+                  void *const *out, void *mc_in, void *mc_out, int64_t count,
+                  int dtype, int op, float scale, float *sumsq_out, int blocks,
+                  int threads, void *stream);
+
+/* Rank `root` stores its buffer into every peer's out (push fan-out, or one
+ * multimem.st when mc_out != NULL). Byte-wise. (session.go:158-161) */
+int kfb_broadcast(const kfb_comm *comm, int root, const void *in,
+                  void *const *out, void *mc_out, int64_t bytes, int blocks,
+                  int threads, void *stream);
+
+/* Every rank stores its `bytes` block into slot `rank` of every peer's out.
+ * (srcs/go/kungfu/session/allgather.go:17-45) */
+int kfb_allgather(const kfb_comm *comm, const void *in, void *const *out,
+                  int64_t bytes, int blocks, int threads, void *stream);
+
+/* Root pulls and reduces (reduce) or pulls and concatenates (gather).
+ * (session.go:153-207) */
+int kfb_reduce(const kfb_comm *comm, int root, void *const *in, void *out,
+               int64_t count, int dtype, int op, int blocks, int threads,
+               void *stream);
+int kfb_gather(const kfb_comm *comm, int root, void *const *in, void *out,
+               int64_t bytes, int blocks, int threads, void *stream);
+
+/* Device-side barrier (K11) and byte consensus (K12): *agree_out (device
+ * int32) = 1 iff every rank's `bytes` of `in` are identical. */
+int kfb_barrier(const kfb_comm *comm, void *stream);
+int kfb_consensus(const kfb_comm *comm, void *const *in, int64_t bytes,
+                  int32_t *agree_out, int blocks, int threads, void *stream);
+
+/* One edge of a strategy graph (K8): dst = op(dst, src) or dst = src where
+ * src is a peer-mapped pointer. Used by the stream-ordered graph executor
+ * for ring/tree/star/binary-tree/set_tree strategies. No in-kernel waiting:
+ * ordering comes from events + kfb_barrier on the executor's stream. */
+int kfb_edge_reduce(void *dst, const void *src, int64_t count, int dtype,
+                    int op, int blocks, int threads, void *stream);
+int kfb_edge_copy(void *dst, const void *src, int64_t bytes, int blocks,
+                  int threads, void *stream);
+
+/* ---- multi-tensor helpers (replace K13 fuse/defuse + K17 local norm) ----- */
+
+/* Copy+cast n tensors into one flat buffer (the symmetric bucket) and
+ * accumulate sum(x^2) over everything copied into *sumsq_out (deterministic).
+ * srcs[i] has counts[i] elements of src_dtype, lands at dst + dst_offs[i]
+ * (elements of dst_dtype). Host arrays; any n (chunked launches of 64).
+ * scratch: device float[KFB_FUSE_SCRATCH_FLOATS], needed iff sumsq_out.
+ * (srcs/python/kungfu/tensorflow/ops/__init__.py:29-46) */
+int kfb_fuse(void *const *srcs, const int64_t *counts, const int64_t *dst_offs,
+             int n, int src_dtype, void *dst, int dst_dtype, float *sumsq_out,
+             float *scratch, void *stream);
+/* Inverse: scatter flat buffer back into n tensors (cast dst_dtype<-src). */
+int kfb_defuse(const void *src, int src_dtype, void *const *dsts,
+               const int64_t *counts, const int64_t *src_offs, int n,
+               int dst_dtype, void *stream);
+
+/* ---- fused optimizer steps ------------------------------------------------ */
+
+typedef struct kfb_sgd_hyper {
+    float lr;
+    float momentum;
+    float dampening;
+    float weight_decay;
+    int32_t nesterov;
+    int32_t first_step; /* momentum buffer := grad (torch.optim.SGD rule) */
+} kfb_sgd_hyper;
+
+/* S-SGD fused step (K1+K14+optimizer): reduce-scatter the gradient shard over
+ * peer memory, scale by grad_scale, apply SGD(momentum, wd) to the fp32 master
+ * shard this rank owns, and push the updated parameters (param_dtype) into
+ * every peer's flat parameter buffer. np==1 degenerates to a local fused SGD.
+ * grads[r]/params[r]: peer-mapped flat buffers. master/mom: local fp32 flat
+ * buffers (only this rank's shard is live). sumsq_out: ||avg grad||^2.
+ * (srcs/python/kungfu/tensorflow/optimizers/sync_sgd.py:78-109) */
+int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
+                        int grad_dtype, void *const *params, int param_dtype,
+                        float *master, float *mom, int64_t count,
+                        float grad_scale, const kfb_sgd_hyper *h,
+                        float *sumsq_out, int blocks, int threads,
+                        void *stream);
+
+/* Local flat SGD on an already-reduced gradient buffer (any-optimizer path's
+ * fast sibling; also the np==1 path). */
+int kfb_sgd_flat(const void *grad, int grad_dtype, void *param,
+                 int param_dtype, float *master, float *mom, int64_t count,
+                 float grad_scale, const kfb_sgd_hyper *h, int blocks,
+                 int threads, void *stream);
+
+/* SMA fused step (K15 + optimizer): avg = mean_r(params_r) over peer memory,
+ * v <- (1-alpha) v + alpha avg, then SGD with the LOCAL gradient, one kernel.
+ * avg_stage[r]: peer-mapped staging buffers (param_dtype, same size).
+ * (srcs/python/kungfu/tensorflow/optimizers/sma_sgd.py:50-74) */
+int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
+                       int param_dtype, void *const *avg_stage,
+                       const void *grad, int grad_dtype, float *master,
+                       float *mom, int64_t count, float alpha,
+                       float grad_scale, const kfb_sgd_hyper *h, int blocks,
+                       int threads, void *stream);
+
+/* PairAveraging fused step (K16+K21): one-sided pull of the target peer's
+ * published snapshot (seqlock + double buffer), v <- 0.5 (v + v_t), SGD with
+ * the local gradient, publish own new snapshot. No barrier, no NCCL.
+ * snap_peer: peer-mapped base of the target's 2-slot snapshot area
+ * (2 * slot_bytes); snap_self: own area; seq words live in the pads.
+ * torn_out (device int32, may be NULL) counts snapshots that were overwritten
+ * while being read. (srcs/python/kungfu/tensorflow/optimizers/async_sgd.py:110-142) */
+int kfb_pair_avg_step(const kfb_comm *comm, int target, const void *snap_peer,
+                      void *snap_self, int64_t slot_bytes, void *param,
+                      int param_dtype, const void *grad, int grad_dtype,
+                      float *master, float *mom, int64_t count,
+                      float grad_scale, const kfb_sgd_hyper *h,
+                      int32_t *torn_out, int blocks, int threads,
+                      void *stream);
+/* Publish the current parameters as snapshot version (seq+1) (init_store). */
+int kfb_pair_publish(const kfb_comm *comm, const void *param, void *snap_self,
+                     int64_t slot_bytes, int64_t bytes, int blocks,
+                     int threads, void *stream);
+
+/* ---- monitors -------------------------------------------------------------- */
+
+/* Gradient variance (K18): one pass over every rank's gradients with two
+ * accumulators. For each segment (tensor) s this rank adds, over its shard,
+ * sum((E[g^2] - E[g]^2)^2) into seg_out[s] (device float[n_seg], zeroed by the
+ * caller); all-reducing seg_out and summing sqrt() over s gives the
+ * reference's "sum of per-tensor norms". seg_ends_dev: device int64[n_seg]
+ * cumulative end offsets (elements).
+ * (srcs/python/kungfu/tensorflow/optimizers/grad_variance.py:46-59) */
+int kfb_grad_variance(const kfb_comm *comm, void *const *grads, int dtype,
+                      int64_t count, const int64_t *seg_ends_dev, int n_seg,
+                      float *seg_out, int blocks, int threads, void *stream);
+
+/* Gradient noise scale finalize (K17+K19) on device scalars: state[0..3] =
+ * {g_ema, s_ema, initialised, last_noise_scale}.
+ * (srcs/cpp/src/tensorflow/ops/cpu/collective.cpp:223-258) */
+int kfb_gns_finalize(const float *sumsq_local, const float *sumsq_global,
+                     float batch_small, float batch_big, float alpha,
+                     float *state, void *stream);
+
+/* ---- symmetric memory (replaces C5-C8) ------------------------------------- */
+
+/* VMM allocation that can be exported as a POSIX fd and mapped by peers. */
+typedef struct kfb_symm_block kfb_symm_block;
+int kfb_symm_alloc(int device, size_t bytes, kfb_symm_block **out);
+int kfb_symm_export_fd(kfb_symm_block *b, int *fd_out);
+int kfb_symm_import_fd(int device, int fd, size_t bytes,
+                       kfb_symm_block **out);
+void *kfb_symm_ptr(kfb_symm_block *b);
+size_t kfb_symm_size(kfb_symm_block *b);
+int kfb_symm_free(kfb_symm_block *b);
+/* Legacy CUDA-IPC fallback (64-byte handles through any byte transport). */
+int kfb_ipc_alloc(int device, size_t bytes, void **ptr_out,
+                  unsigned char handle_out[64]);
+int kfb_ipc_open(int device, const unsigned char handle[64], void **ptr_out);
+int kfb_ipc_close(void *ptr);
+int kfb_ipc_free(void *ptr);
+/* Multicast object over `np` devices of the node (NVLS). Rank 0 creates and
+ * exports; others import; every rank adds its device, then binds its block. */
+typedef struct kfb_mc_object kfb_mc_object;
+int kfb_mc_create(int device, int np, size_t bytes, kfb_mc_object **out,
+                  int *fd_out);
+int kfb_mc_import(int device, int np, int fd, size_t bytes,
+                  kfb_mc_object **out);
+int kfb_mc_add_device(kfb_mc_object *mc);
+int kfb_mc_bind(kfb_mc_object *mc, kfb_symm_block *mem, void **mc_ptr_out);
+int kfb_mc_free(kfb_mc_object *mc);
+size_t kfb_symm_granularity(int device, int multicast);
+
+/* ---- model kernels (channels-last bf16 training blocks) ------------------- */
+
+/* y = relu?(bn(x) [+ residual]) forward/backward for NHWC bf16 activations
+ * with fp32 statistics: two passes over x instead of torch's four or five. */
+int kfb_bn_act_fwd(const void *x, const void *residual, void *y,
+                   const float *weight, const float *bias, float *running_mean,
+                   float *running_var, float *save_mean, float *save_invstd,
+                   int64_t rows, int channels, float eps, float momentum,
+                   int relu, int training, float *scratch, void *stream);
+int kfb_bn_act_bwd(const void *dy, const void *x, const void *y,
+                   const float *weight, const float *save_mean,
+                   const float *save_invstd, void *dx, void *dresidual,
+                   float *dweight, float *dbias, int64_t rows, int channels,
+                   int relu, float *scratch, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KUNGFU_B200_H */

@@ -1,0 +1,91 @@
+/* kungfu_b200 host runtime — C ABI (libkungfu_host.so).
+ *
+ * One kf_peer per process. Functions return 0 on success unless stated; the
+ * text of the last error is kf_last_error(). dtype codes are KungFu_Datatype
+ * compatible (srcs/cpp/include/kungfu/dtype.h:21-39) plus bf16 = (4<<16|2<<8|8);
+ * op: 0 sum, 1 min, 2 max, 3 prod (srcs/cpp/include/kungfu/op.h:8-13).
+ * Reference surface: /root/reference/srcs/go/libkungfu-comm/{main.go,
+ * collective.go,adapt.go,monitoring.go}, /root/reference/srcs/cpp/include/
+ * kungfu/python/init.h:4-31.
+ */
+#ifndef KUNGFU_HOST_H
+#define KUNGFU_HOST_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct kf_peer kf_peer;
+
+const char *kf_last_error(void);
+kf_peer *kf_peer_create_from_env(void);
+int kf_peer_start(kf_peer *p);
+void kf_peer_close(kf_peer *p);
+
+int kf_rank(kf_peer *p);
+int kf_size(kf_peer *p);
+int kf_local_rank(kf_peer *p);
+int kf_local_size(kf_peer *p);
+int kf_host_count(kf_peer *p);
+int kf_detached(kf_peer *p);
+int kf_cluster_version(kf_peer *p);
+uint64_t kf_uid(kf_peer *p);
+int kf_peer_addr(kf_peer *p, int rank, char *buf, int cap);
+
+int kf_barrier(kf_peer *p);
+int kf_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
+int kf_monitored_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op,
+                            const int32_t *tree, int tree_len, const char *name);
+int kf_cross_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
+int kf_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
+int kf_broadcast(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
+int kf_local_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
+int kf_local_broadcast(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
+int kf_all_gather(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
+int kf_gather(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
+int kf_consensus(kf_peer *p, const void *data, int64_t nbytes, const char *name, int *agree);
+
+/* async: returns a handle (>0) or -1; kf_wait_handle returns 0 iff the op succeeded */
+int64_t kf_all_reduce_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
+int64_t kf_broadcast_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
+int kf_wait_handle(kf_peer *p, int64_t handle);
+
+/* p2p model store; version may be NULL (unversioned). kf_request returns 0 iff found. */
+int kf_save(kf_peer *p, const char *version, const char *name, const void *data, int64_t nbytes);
+int kf_request(kf_peer *p, int target_rank, const char *version, const char *name, void *buf, int64_t nbytes);
+
+/* elastic control */
+int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached);
+int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached);
+int kf_propose_new_size(kf_peer *p, int new_size);
+
+/* adaptation / monitoring */
+int kf_set_tree(kf_peer *p, const int32_t *forest, int n);
+int kf_set_strategy(kf_peer *p, const char *name);
+int kf_calc_stats(kf_peer *p);
+int kf_log_stats(kf_peer *p);
+int kf_print_strategy_stats(kf_peer *p);
+int kf_check_interference(kf_peer *p); /* 1 = majority voted to switch */
+int kf_get_peer_latencies(kf_peer *p, float *out, int n);
+int kf_egress_rates(kf_peer *p, float *out, int n);
+
+/* descriptor passing between colocated workers (CUDA VMM handles) */
+int kf_send_fd(kf_peer *p, int target_rank, const char *tag, int fd);
+int kf_recv_fd(kf_peer *p, int src_rank, const char *tag, int *fd);
+
+/* planner utilities exposed for tests / tools */
+int kf_gen_strategy_graphs(const char *peers_csv, const char *strategy, char *out, int cap);
+int kf_minimum_spanning_tree(const float *weights, int n, int32_t *edges_out);
+void kf_transform2(const void *x, const void *y, void *z, int64_t n, int dtype, int op);
+int kf_cluster_resize(const char *cluster_json, int new_size, char *out, int cap);
+int kf_parse_hostfile(const char *text, char *out, int cap);
+int kf_gen_peer_list(const char *hostlist, int np, const char *port_range, char *out, int cap);
+
+/* tools */
+int kf_run_main(int argc, char **argv);            /* kungfu-run */
+int kf_config_server_main(int argc, char **argv);  /* kungfu-config-server */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

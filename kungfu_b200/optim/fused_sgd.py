@@ -1,0 +1,170 @@
+"""FusedSGD: torch.optim.SGD semantics on flat arenas with fp32 master weights.
+
+One kernel per (param group, dtype) does the whole update; when driven by
+``SynchronousSGDOptimizer`` the same kernel also performs the gradient
+all-reduce over peer memory (reduce-scatter -> update of the owned shard ->
+all-gather of the new parameters), see csrc/kernels/optim.cu:k_ssgd_fused.
+
+Update rule = torch.optim.SGD (weight decay, momentum, dampening, nesterov),
+which is what the reference's benchmarks wrap
+(/root/reference/benchmarks/system/benchmark_kungfu_torch.py:76-83).
+"""
+import ctypes as C
+
+import torch
+
+from ..ops import _cuda as K
+from ..parallel import comm as _comm
+from ..parallel.flat import build_arenas
+
+
+class FusedSGD(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, momentum=0.0, dampening=0.0, weight_decay=0.0,
+                 nesterov=False, comm=None, blocks=None, threads=None):
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError('Nesterov momentum requires a momentum and zero dampening')
+        defaults = dict(lr=lr, momentum=momentum, dampening=dampening,
+                        weight_decay=weight_decay, nesterov=nesterov)
+        super().__init__(params, defaults)
+        self._comm = comm
+        self._arenas = None  # list of (group, [Arena])
+        self._steps = 0
+        self._blocks = blocks
+        self._threads = threads
+        self._local = None
+        self.sumsq_global = None  # ||averaged grad||^2 of the last sync step (device float)
+        self.sumsq_local = None  # ||local grad||^2 of the last step (device float)
+        self.monitor_norms = False
+
+    # -- arenas -------------------------------------------------------------------------
+    @property
+    def comm(self):
+        if self._comm is None:
+            self._comm = _comm.default_comm()
+        return self._comm
+
+    def arenas(self):
+        if self._arenas is None:
+            out = []
+            for gi, g in enumerate(self.param_groups):
+                named = [('g%d.p%d' % (gi, i), p) for i, p in enumerate(g['params']) if p.is_cuda]
+                if len(named) != len(g['params']):
+                    raise K.KungFuCudaError('FusedSGD only handles CUDA parameters')
+                out.append((g, build_arenas(self.comm, named)))
+            self._arenas = out
+            dev = self.comm.device
+            n = sum(len(a) for _, a in out)
+            self._ss_local_parts = torch.zeros(max(n, 1), dtype=torch.float32, device=dev)
+            self._ss_global_parts = torch.zeros(max(n, 1), dtype=torch.float32, device=dev)
+        return self._arenas
+
+    def rebuild(self, comm=None):
+        """Re-create the arenas on a new communicator (after resize_cluster).
+        Parameter values, master weights and momentum are carried over."""
+        old = self._arenas
+        self._comm = comm
+        self._arenas = None
+        if old is None:
+            return
+        olds = [a for _, ars in old for a in ars]
+        news = [a for _, ars in self.arenas() for a in ars]
+        for o, n in zip(olds, news):
+            if o.master is not None:
+                n.ensure_master()
+                n.master.copy_(o.master)
+                n.mom.copy_(o.mom)
+
+    def _hyper(self, g):
+        h = K.SgdHyper()
+        h.lr = float(g['lr'])
+        h.momentum = float(g['momentum'])
+        h.dampening = float(g['dampening'])
+        h.weight_decay = float(g['weight_decay'])
+        h.nesterov = 1 if g['nesterov'] else 0
+        h.first_step = 1 if self._steps == 0 else 0
+        return h
+
+    def _local_struct(self):
+        # np == 1 view of this rank for purely local steps
+        if self._local is None:
+            c = self.comm
+            s = K.KfbComm()
+            s.rank = 0
+            s.np = 1
+            s.pads[0] = c._struct.pads[max(c.rank, 0)]
+            s.local_epoch = c._struct.local_epoch
+            s.scratch = c._struct.scratch
+            self._local = s
+        return C.byref(self._local)
+
+    # -- steps ------------------------------------------------------------------------------
+    def _run(self, sync, grad_scale):
+        comm = self.comm
+        blocks = self._blocks or comm.default_blocks
+        threads = self._threads or comm.default_threads
+        k = 0
+        for g, arenas in self.arenas():
+            h = self._hyper(g)
+            for a in arenas:
+                a.ensure_master()
+                ss_l = self._ss_local_parts[k:k + 1] if self.monitor_norms else None
+                ss_g = self._ss_global_parts[k:k + 1] if self.monitor_norms else None
+                a.fuse_grads(sumsq_out=ss_l)
+                if sync and comm.np > 1:
+                    ga, _k1 = a.grads_buf.ptr_array()
+                    pa, _k2 = a.params_buf.ptr_array()
+                    cs = comm.cstruct
+                else:
+                    me = max(comm.rank, 0)
+                    ga, _k1 = K.ptr_array([a.grads_buf.ptrs[me]])
+                    pa, _k2 = K.ptr_array([a.params_buf.ptrs[me]])
+                    cs = self._local_struct()
+                K.call('kfb_ssgd_fused_step', cs, ga, a.code, pa, a.code,
+                       a.master.data_ptr(), a.mom.data_ptr(), a.count, float(grad_scale),
+                       C.byref(h), ss_g.data_ptr() if ss_g is not None else None,
+                       blocks, threads, K.stream_ptr())
+                k += 1
+        if self.monitor_norms:
+            self.sumsq_local = self._ss_local_parts[:k].sum()
+            self.sumsq_global = self._ss_global_parts[:k].sum()
+        self._steps += 1
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        self._run(sync=False, grad_scale=1.0)
+        return loss
+
+    @torch.no_grad()
+    def sync_step(self, average=True):
+        """All-reduce gradients over peer memory and apply the update, fused."""
+        scale = 1.0 / self.comm.np if average else 1.0
+        self._run(sync=True, grad_scale=scale)
+
+    # -- state ------------------------------------------------------------------------------
+    def consolidate(self):
+        """Make master weights / momentum complete on every rank (each rank only
+        maintains the shard it owns during fused sync steps)."""
+        comm = self.comm
+        if comm.np <= 1 or self._arenas is None:
+            return
+        from ..ops import collective as coll
+        for _, arenas in self._arenas:
+            for a in arenas:
+                if a.master is None:
+                    continue
+                npk = a.count // 8
+                per = (npk + comm.np - 1) // comm.np * 8
+                stage = comm.alloc(per * 4 * comm.np)
+                sv = stage.view(torch.float32)
+                for t in (a.master, a.mom):
+                    lo = min(comm.rank * per, a.count)
+                    hi = min(lo + per, a.count)
+                    tmp = comm.alloc(per * 4)
+                    tmp.view(torch.float32)[:hi - lo].copy_(t[lo:hi])
+                    coll.all_gather(comm, tmp, stage, per * 4)
+                    t.copy_(sv[:per * comm.np][:a.count])
+        torch.cuda.synchronize()

@@ -1,0 +1,279 @@
+"""Device communicators over symmetric (peer-mapped) memory.
+
+Three flavours share one interface:
+
+* ``LocalComm``     np == 1, plain device memory (kernels skip the barriers).
+* ``EmulatedComm``  np "ranks" on ONE GPU: every collective is a single
+                    cooperative launch whose blockIdx.y plays the rank. Used
+                    by GPU tests when fewer GPUs than ranks are available
+                    (rank-waiting kernels must never be run as separate
+                    launches on one GPU).
+* ``PeerComm``      one process per GPU; buffers are CUDA VMM allocations whose
+                    POSIX fds are passed over the control plane's unix sockets
+                    and mapped by every peer (CUDA-IPC handles as fallback),
+                    plus an optional NVLS multicast alias.
+
+This replaces the reference's NCCLController/NCCLHelper/CudaStream stack
+(/root/reference/srcs/cpp/src/nccl/controller.cpp:8-53,
+/root/reference/srcs/cpp/src/nccl/gpu_collective.cpp:59-152): there is no
+communicator library underneath, only mapped pointers and flags.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from ..ops import _cuda as K
+
+
+def _align(n, a):
+    return (n + a - 1) // a * a
+
+
+class SymmBuffer(object):
+    """A buffer that exists at the same size on every rank.
+
+    ``local``  uint8 tensor aliasing this rank's copy (emulation: rank 0's)
+    ``ptrs``   device addresses of every rank's copy as mapped HERE
+    ``mc_ptr`` multicast alias (NVLS) or None
+    """
+
+    def __init__(self, comm, nbytes, locals_, ptrs, mc_ptr=None, handles=None):
+        self.comm = comm
+        self.nbytes = nbytes
+        self.locals = locals_  # list of uint8 tensors (len np for emulation, else 1)
+        self.local = locals_[0]
+        self.ptrs = ptrs
+        self.mc_ptr = mc_ptr
+        self._handles = handles or []
+
+    def view(self, dtype, rank=None):
+        """Typed tensor over this rank's copy (or emulated rank `rank`)."""
+        t = self.local if rank is None else self.locals[rank]
+        return t.view(dtype)
+
+    def ptr_array(self, byte_offset=0):
+        return K.ptr_array([p + byte_offset for p in self.ptrs])
+
+
+class _CommBase(object):
+    rank = 0
+    np = 1
+    emulated = False
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self._struct = K.KfbComm()
+        self._keep = []
+        self.default_blocks = int(os.environ.get('KUNGFU_COMM_BLOCKS', '32'))
+        self.default_threads = int(os.environ.get('KUNGFU_COMM_THREADS', '512'))
+
+    def _init_struct(self, rank, np, pad_ptrs, n_state):
+        s = self._struct
+        s.rank = rank
+        s.np = np
+        for r in range(K.MAX_RANKS):
+            s.pads[r] = pad_ptrs[r] if r < len(pad_ptrs) else None
+        self._epoch = torch.zeros(K.STATE_EPOCH_WORDS * n_state, dtype=torch.int32, device=self.device)
+        self._scratch = torch.zeros(K.SCRATCH_FLOATS * n_state, dtype=torch.float32, device=self.device)
+        self._fuse_scratch = torch.zeros(K.FUSE_SCRATCH_FLOATS, dtype=torch.float32, device=self.device)
+        s.local_epoch = self._epoch.data_ptr()
+        s.scratch = self._scratch.data_ptr()
+        s.mc_pad = None
+
+    @property
+    def cstruct(self):
+        return C.byref(self._struct)
+
+    @property
+    def n_local_ranks(self):
+        """How many ranks' worth of state live in this process (np when emulated)."""
+        return self.np if self.emulated else 1
+
+    def alloc(self, nbytes, multicast=False):
+        raise NotImplementedError
+
+    def barrier(self, stream=None):
+        if self.np > 1:
+            K.call('kfb_barrier', self.cstruct, K.stream_ptr(stream))
+
+    def close(self):
+        pass
+
+
+class LocalComm(_CommBase):
+    def __init__(self, device='cuda'):
+        super().__init__(device)
+        self._pad = torch.zeros(K.PAD_BYTES, dtype=torch.uint8, device=self.device)
+        self._init_struct(0, 1, [self._pad.data_ptr()], 1)
+
+    def alloc(self, nbytes, multicast=False):
+        nbytes = _align(nbytes, 256)
+        t = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+        return SymmBuffer(self, nbytes, [t], [t.data_ptr()])
+
+
+class EmulatedComm(_CommBase):
+    emulated = True
+
+    def __init__(self, np, device='cuda'):
+        super().__init__(device)
+        assert 1 <= np <= K.MAX_RANKS
+        self.np = np
+        self.rank = -1
+        self._pads = [torch.zeros(K.PAD_BYTES, dtype=torch.uint8, device=self.device) for _ in range(np)]
+        self._init_struct(-1, np, [p.data_ptr() for p in self._pads], np)
+        # every (block, rank) CTA must be co-resident
+        sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self.default_blocks = max(1, min(self.default_blocks, sms // np))
+
+    def alloc(self, nbytes, multicast=False):
+        nbytes = _align(nbytes, 256)
+        ts = [torch.zeros(nbytes, dtype=torch.uint8, device=self.device) for _ in range(self.np)]
+        return SymmBuffer(self, nbytes, ts, [t.data_ptr() for t in ts])
+
+
+class PeerComm(_CommBase):
+    """Real multi-GPU communicator. `xchg` is the control-plane exchange:
+
+        xchg.rank, xchg.size
+        xchg.all_gather_bytes(b: bytes) -> [bytes] * size
+        xchg.exchange_fds(fd: int, tag: str) -> [fd or None] * size   (own slot None)
+        xchg.barrier()
+    """
+
+    def __init__(self, xchg, device, mode=None):
+        super().__init__(device)
+        self.xchg = xchg
+        self.rank = xchg.rank
+        self.np = xchg.size
+        assert self.np <= K.MAX_RANKS, 'one NVSwitch domain holds at most %d ranks' % K.MAX_RANKS
+        self.mode = mode or os.environ.get('KUNGFU_SYMM_MODE', 'vmm')
+        self._seq = 0
+        self.multicast_ok = False
+        if os.environ.get('KUNGFU_DISABLE_NVLS', '0') != '1' and self.mode == 'vmm':
+            ok = K.lib().kfb_multicast_supported(self.device.index or 0)
+            oks = xchg.all_gather_bytes(bytes([1 if ok else 0]))
+            self.multicast_ok = all(b == b'\x01' for b in oks)
+        self._pad_buf = self.alloc(K.PAD_BYTES)
+        self._init_struct(self.rank, self.np, self._pad_buf.ptrs, 1)
+
+    def _alloc_vmm(self, nbytes):
+        lib = K.lib()
+        dev = self.device.index or 0
+        h = C.c_void_p()
+        K.check(lib.kfb_symm_alloc(dev, nbytes, C.byref(h)))
+        size = lib.kfb_symm_size(h)
+        fd = C.c_int(-1)
+        K.check(lib.kfb_symm_export_fd(h, C.byref(fd)))
+        self._seq += 1
+        fds = self.xchg.exchange_fds(fd.value, 'symm%d' % self._seq)
+        handles, ptrs = [], []
+        for r in range(self.np):
+            if r == self.rank:
+                handles.append(h)
+                ptrs.append(lib.kfb_symm_ptr(h))
+            else:
+                ph = C.c_void_p()
+                K.check(lib.kfb_symm_import_fd(dev, fds[r], size, C.byref(ph)))
+                lib.kfb_close_fd(fds[r])
+                handles.append(ph)
+                ptrs.append(lib.kfb_symm_ptr(ph))
+        lib.kfb_close_fd(fd.value)
+        return size, handles, ptrs
+
+    def _alloc_ipc(self, nbytes):
+        lib = K.lib()
+        dev = self.device.index or 0
+        p = C.c_void_p()
+        hb = C.create_string_buffer(64)
+        K.check(lib.kfb_ipc_alloc(dev, nbytes, C.byref(p), hb))
+        all_h = self.xchg.all_gather_bytes(hb.raw)
+        ptrs = []
+        for r in range(self.np):
+            if r == self.rank:
+                ptrs.append(p.value)
+            else:
+                q = C.c_void_p()
+                K.check(lib.kfb_ipc_open(dev, all_h[r], C.byref(q)))
+                ptrs.append(q.value)
+        return nbytes, [('ipc', p.value)], ptrs
+
+    def alloc(self, nbytes, multicast=False):
+        """Collective: every rank must call with the same size, in the same order."""
+        gran = 2 << 20
+        nbytes = _align(max(nbytes, 1), gran)
+        if self.mode == 'vmm':
+            size, handles, ptrs = self._alloc_vmm(nbytes)
+        else:
+            size, handles, ptrs = self._alloc_ipc(nbytes)
+        mc_ptr = None
+        if multicast and self.multicast_ok:
+            mc_ptr = self._bind_multicast(size, handles[self.rank])
+        local = K.tensor_from_ptr(ptrs[self.rank], size, self.device, owner=handles)
+        self.xchg.barrier()
+        buf = SymmBuffer(self, size, [local], ptrs, mc_ptr, handles)
+        self._keep.append(buf)
+        return buf
+
+    def _bind_multicast(self, size, my_handle):
+        lib = K.lib()
+        dev = self.device.index or 0
+        mc = C.c_void_p()
+        self._seq += 1
+        tag = 'mc%d' % self._seq
+        try:
+            if self.rank == 0:
+                fd = C.c_int(-1)
+                K.check(lib.kfb_mc_create(dev, self.np, size, C.byref(mc), C.byref(fd)))
+                self.xchg.broadcast_fd(fd.value, tag, root=0)
+                lib.kfb_close_fd(fd.value)
+            else:
+                rfd = self.xchg.broadcast_fd(None, tag, root=0)
+                K.check(lib.kfb_mc_import(dev, self.np, rfd, size, C.byref(mc)))
+                lib.kfb_close_fd(rfd)
+            K.check(lib.kfb_mc_add_device(mc))
+            self.xchg.barrier()
+            p = C.c_void_p()
+            K.check(lib.kfb_mc_bind(mc, my_handle, C.byref(p)))
+            self.xchg.barrier()
+            self._keep.append(('mc', mc))
+            return p.value
+        except K.KungFuCudaError:
+            # a failed bind must fail on every rank or on none; ranks agree below
+            self.multicast_ok = False
+            raise
+
+    def close(self):
+        self._keep = []
+
+
+_default = None
+
+
+def default_comm():
+    """The process-wide communicator, created on first use from the runtime's
+    view of the cluster (np == 1 -> LocalComm)."""
+    global _default
+    if _default is None:
+        from .. import python as kfpy
+        dev = torch.device('cuda', torch.cuda.current_device())
+        if kfpy.current_cluster_size() <= 1:
+            _default = LocalComm(dev)
+        else:
+            _default = PeerComm(kfpy.control_exchange(), dev)
+    return _default
+
+
+def set_default_comm(comm):
+    global _default
+    _default = comm
+
+
+def reset_default_comm():
+    """Drop the communicator (after a resize the next use re-maps peer memory
+    for the new membership; surviving processes are not restarted)."""
+    global _default
+    if _default is not None:
+        _default.close()
+    _default = None

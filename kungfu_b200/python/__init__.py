@@ -1,0 +1,182 @@
+"""Process-level API: rank / size / barrier / elastic control.
+
+Same surface as the reference's ``kungfu.python``
+(/root/reference/srcs/python/kungfu/python/__init__.py:35-107), backed by the
+C++ control plane in libkungfu_host.so (csrc/ctrl, csrc/elastic). A process
+that was not started by ``kungfu-run`` (or torchrun) runs in single mode:
+rank 0 of 1 (/root/reference/srcs/go/kungfu/env/config.go:59-68).
+"""
+import atexit
+import os
+
+from .. import _host
+
+_peer = None
+
+
+def _p():
+    global _peer
+    if _peer is None:
+        _peer = _host.Peer.from_env()
+        atexit.register(_finalize)
+    return _peer
+
+
+def _finalize():
+    global _peer
+    if _peer is not None:
+        _peer.close()
+        _peer = None
+
+
+def init():
+    """Start the control plane now (otherwise it starts on first use)."""
+    _p()
+
+
+def finalize():
+    _finalize()
+
+
+def uid():
+    """ip:port:init-version packed into an int, unique per worker incarnation."""
+    return _p().uid()
+
+
+def detached():
+    """True once this worker is no longer part of the cluster (after a shrink)."""
+    return _p().detached()
+
+
+def current_rank():
+    return _p().rank()
+
+
+def current_local_rank():
+    return _p().local_rank()
+
+
+def current_cluster_size():
+    return _p().size()
+
+
+def current_local_size():
+    return _p().local_size()
+
+
+def host_count():
+    return _p().host_count()
+
+
+def run_barrier():
+    _p().barrier()
+
+
+def propose_new_size(new_size):
+    """Ask the config server for a new cluster size (takes effect at the next
+    resize_cluster_from_url on every worker)."""
+    _p().propose_new_size(int(new_size))
+
+
+def resize_cluster(new_size):
+    """Returns (changed, detached). Surviving workers are NOT restarted: the
+    runtime re-connects the control plane and the device layer re-maps peer
+    memory (reference: /root/reference/srcs/go/kungfu/peer/peer.go:227-263)."""
+    changed, det = _p().resize_cluster(int(new_size))
+    if changed:
+        _on_membership_change()
+    return changed, det
+
+
+def resize_cluster_from_url():
+    changed, det = _p().resize_cluster_from_url()
+    if changed:
+        _on_membership_change()
+    return changed, det
+
+
+def _on_membership_change():
+    try:
+        from ..parallel import comm
+        comm.reset_default_comm()
+    except Exception:  # device layer not in use
+        pass
+
+
+def check_interference():
+    return _p().check_interference()
+
+
+def calc_stats():
+    _p().calc_stats()
+
+
+def log_stats():
+    _p().log_stats()
+
+
+def print_strategy_stats():
+    _p().print_strategy_stats()
+
+
+def set_tree(forest):
+    """Install a broadcast tree given as a father array (forest[i] = parent of
+    i, root points to itself) on every rank after digest consensus."""
+    _p().set_tree([int(x) for x in forest])
+
+
+def set_strategy(name):
+    _p().set_strategy(name)
+
+
+def get_peer_latencies():
+    return _p().peer_latencies()
+
+
+def egress_rates():
+    return _p().egress_rates()
+
+
+def _get_cuda_index():
+    """GPU this worker should use: KUNGFU_CUDA_VISIBLE_DEVICES if the launcher
+    pinned one, else the local rank
+    (/root/reference/srcs/cpp/src/python/cuda.cpp:29-47)."""
+    v = os.environ.get('KUNGFU_CUDA_VISIBLE_DEVICES')
+    if v not in (None, ''):
+        first = int(v.split(',')[0])
+        if first < 0:
+            return -1
+        visible = os.environ.get('CUDA_VISIBLE_DEVICES')
+        if visible:  # launcher already narrowed the visible set to one device
+            return 0 if len(visible.split(',')) == 1 else first
+        return first
+    if 'LOCAL_RANK' in os.environ:
+        return int(os.environ['LOCAL_RANK'])
+    return current_local_rank()
+
+
+def _get_other_ranks():
+    self_rank = current_rank()
+    return [r for r in range(current_cluster_size()) if r != self_rank]
+
+
+def show_cuda_version():
+    import torch
+    print('CUDA (torch build): %s' % torch.version.cuda)
+
+
+def show_nccl_version():
+    import torch
+    try:
+        print('NCCL (torch bundled, baseline only): %s' % '.'.join(map(str, torch.cuda.nccl.version())))
+    except Exception:
+        print('NCCL: unavailable')
+
+
+def control_exchange():
+    """The control-plane exchange object the device layer bootstraps from."""
+    return _p().exchange()
+
+
+def peer():
+    return _p()
