@@ -1,0 +1,272 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 S-SGD training throughput (img/s), bf16,
+synthetic ImageNet-shaped data, 1..8 B200 (one process per GPU).
+
+    python bench.py --gpus 1 --steps 30 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29511 bench.py --gpus 8 --steps 30 --warmup 5
+
+Protocol mirrors the reference's synthetic benchmark
+(/root/reference/benchmarks/system/benchmark_kungfu_torch.py:61-135: fixed fake
+batch, SGD lr 0.01 x np, optimizer wrapped by SynchronousSGDOptimizer) with the
+timing rules of this project: device-timed with CUDA events, barrier +
+synchronize on both sides, max over ranks, >= 3 warm-up steps, clocks sampled
+during the timed region. The per-GPU batch (256) is the reference's largest
+published point (global batch 4096 over 16 GPUs).
+
+`value`  : device-timed steps on resident synthetic data (the reference's protocol)
+`e2e`    : same steps, but every step copies its batch from pinned host memory
+           and reads the loss back to the host.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_IMG_S = 5507.0  # KungFu S-SGD, ResNet-50, global batch 4096, 16 x V100
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=30)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--model', default='resnet50')
+    ap.add_argument('--batch-size', type=int, default=256, help='per-GPU batch')
+    ap.add_argument('--image-size', type=int, default=224)
+    ap.add_argument('--no-graph', action='store_true', help='eager launches instead of a captured CUDA graph')
+    ap.add_argument('--fused-bn', type=int, default=int(os.environ.get('KUNGFU_FUSED_BN', '0')))
+    ap.add_argument('--momentum', type=float, default=0.0)
+    ap.add_argument('--skip-e2e', action='store_true')
+    return ap.parse_args()
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        # "under load": drop idle samples taken before the first kernel landed
+        load = [s for s in sm if s > 0]
+        return {'sm_mhz': statistics.median(load) if load else None,
+                'sm_max_mhz': max(mx) if mx else None, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def reference_arm(args):
+    # The one allowed offline install was attempted ("Reference
+    # arm"): the reference's build needs Go >= 1.11 for its runtime and
+    # TensorFlow headers for its op library; neither exists in this image.
+    if os.path.isdir(os.path.join(ROOT, 'baseline', '_ref', 'kungfu')):
+        pass  # would run the unmodified reference here; it never installed
+    print(json.dumps({'impl': 'reference',
+                      'unavailable': 'reference does not build offline: setup.py needs TensorFlow '
+                                     '(import tensorflow) and a Go toolchain for libkungfu-comm; neither is in the image'}))
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        return reference_arm(args)
+
+    import torch
+    import torch.nn.functional as F
+
+    import kungfu_b200.torch as kf
+    from kungfu_b200 import models
+    from kungfu_b200.ops import _cuda as K
+    from kungfu_b200.optim import FusedSGD
+
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    rank, np_ = kf.current_rank(), kf.current_cluster_size()
+    if np_ != args.gpus and rank == 0:
+        print('[bench] warning: --gpus %d but cluster size is %d' % (args.gpus, np_), file=sys.stderr)
+    torch.backends.cudnn.benchmark = True
+
+    torch.manual_seed(1234)
+    model = getattr(models, args.model)(fused_bn=bool(args.fused_bn))
+    model = models.to_b200_layout(model.to(dev), torch.bfloat16)
+    model.train()
+    opt = FusedSGD(model.parameters(), lr=0.01 * np_, momentum=args.momentum)
+    opt = kf.optimizers.SynchronousSGDOptimizer(opt, named_parameters=model.named_parameters())
+    opt.arenas()  # move the parameters into symmetric memory before anything captures their addresses
+    kf.broadcast_parameters(model.state_dict())
+
+    B, S = args.batch_size, args.image_size
+    # resident synthetic batch (the reference's "fixed fake data")
+    x_dev = torch.randn(B, 3, S, S, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y_dev = torch.randint(0, 1000, (B, ), device=dev)
+    loss_dev = torch.zeros((), device=dev)
+
+    def train_step():
+        opt.zero_grad(set_to_none=True)
+        out = model(x_dev)
+        loss = F.cross_entropy(out.float(), y_dev)
+        loss.backward()
+        opt.step()
+        loss_dev.copy_(loss.detach())
+
+    # ---- warm-up (eager; also cuDNN autotune and first-step momentum init) ---------------
+    eager_warm = max(3, args.warmup) if args.no_graph else 3
+    for _ in range(eager_warm):
+        train_step()
+    torch.cuda.synchronize()
+
+    launches_per_step = None
+    if args.no_graph:
+        run_step = train_step
+    else:
+        kf.run_barrier()
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            train_step()  # one more eager step on the capture stream's allocator state
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        kf.run_barrier()
+        before = K.launch_count
+        with torch.cuda.graph(graph):
+            train_step()
+        launches_per_step = K.launch_count - before
+        run_step = graph.replay
+        for _ in range(max(0, args.warmup - 3) + 3):
+            run_step()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        kf.run_barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        before = K.launch_count
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        kf.run_barrier()
+        ms = e0.elapsed_time(e1)
+        mx = kf.ops.all_reduce_fn(torch.tensor([ms], dtype=torch.float64), 'max')
+        return float(mx[0]), K.launch_count - before
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    total_ms, eager_launches = timed(run_step, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = total_ms / args.steps
+    value = B * np_ / (ms_per_step / 1e3)
+    gpu_launches = eager_launches if args.no_graph else launches_per_step * args.steps
+
+    # ---- end to end through the public API: pinned host batch in, loss out, every step ----
+    e2e = None
+    if not args.skip_e2e:
+        x_host = torch.randn(B, 3, S, S).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).pin_memory()
+        y_host = torch.randint(0, 1000, (B, )).pin_memory()
+        loss_host = torch.zeros(()).pin_memory()
+        copy_stream = torch.cuda.Stream()
+        x_next = torch.empty_like(x_dev)
+        y_next = torch.empty_like(y_dev)
+        ready = torch.cuda.Event()
+        consumed = torch.cuda.Event()
+        consumed.record()
+
+        def prefetch():
+            # next batch travels over PCIe on its own stream while this step computes
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed)
+                x_next.copy_(x_host, non_blocking=True)
+                y_next.copy_(y_host, non_blocking=True)
+                ready.record(copy_stream)
+
+        prefetch()
+
+        def e2e_step():
+            cur = torch.cuda.current_stream()
+            cur.wait_event(ready)
+            x_dev.copy_(x_next, non_blocking=True)  # device-side hand-over into the graph's static input
+            y_dev.copy_(y_next, non_blocking=True)
+            consumed.record(cur)
+            prefetch()
+            run_step()
+            loss_host.copy_(loss_dev, non_blocking=True)
+            cur.synchronize()  # the loss is on the host when the step returns
+
+        for _ in range(3):
+            e2e_step()
+        e2e_ms, _ = timed(e2e_step, args.steps)
+        e2e = {'value': B * np_ / (e2e_ms / args.steps / 1e3), 'unit': 'img/s',
+               'h2d_bytes_per_step': x_host.numel() * x_host.element_size() + y_host.numel() * y_host.element_size(),
+               'd2h_bytes_per_step': loss_host.element_size(), 'ms_per_step': e2e_ms / args.steps,
+               'loss': float(loss_host)}
+
+    if rank == 0:
+        out = {
+            'metric': 'ResNet-50 S-SGD training throughput',
+            'value': value, 'unit': 'img/s', 'n_gpus': np_, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+            'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': value / BASELINE_IMG_S, 'dtype': 'bf16', 'data': 'synthetic', 'impl': 'ours',
+            'config': {'model': args.model, 'global_batch': B * np_, 'per_gpu_batch': B, 'seq_len': None,
+                       'image_size': S, 'parallelism': 'dp%d' % np_, 'optimizer': 'SynchronousSGDOptimizer(FusedSGD)',
+                       'cuda_graph': not args.no_graph, 'fused_bn': bool(args.fused_bn),
+                       'l2': 'working set per step (activations, bs%d) exceeds the 126 MB L2' % B,
+                       'baseline': 'KungFu S-SGD ResNet-50 global batch 4096 on 16xV100 = 5507 img/s'},
+            'clocks': clocks, 'e2e': e2e, 'gpu_launches': gpu_launches, 'loss': float(loss_dev),
+        }
+        print(json.dumps(out))
+    kf.run_barrier()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -38,7 +38,7 @@ class Arena(object):
       count                    padded element count (multiple of 16)
     """
 
-    def __init__(self, comm, named_params, dtype, need_grads=True, multicast=True):
+    def __init__(self, comm, named_params, dtype, need_grads=True, multicast=True, repoint=True):
         self.comm = comm
         self.dtype = dtype
         self.code = K.dtype_code(dtype)
@@ -52,11 +52,13 @@ class Arena(object):
         self.count = _align(off, ALIGN_ELEMS * 8)
         esize = torch.empty(0, dtype=dtype).element_size()
         self.nbytes = self.count * esize
-        self.params_buf = comm.alloc(self.nbytes, multicast=multicast)
+        self._cl = [_is_channels_last(p.data) for p in self.params]
+        self.params_buf = comm.alloc(self.nbytes, multicast=multicast) if repoint else None
         self.grads_buf = comm.alloc(self.nbytes, multicast=multicast) if need_grads else None
-        self.flat_params = self.params_buf.view(dtype)[:self.count]
+        self.flat_params = self.params_buf.view(dtype)[:self.count] if repoint else None
         self.flat_grads = self.grads_buf.view(dtype)[:self.count] if need_grads else None
-        self._repoint()
+        if repoint:
+            self._repoint()
         self.master = None
         self.mom = None
         self._src_cache = None
@@ -75,10 +77,13 @@ class Arena(object):
             view.copy_(p.data)
             p.data = view
 
+    def is_cl(self, i):
+        return self._cl[i]
+
     def grad_view(self, i):
         p, off = self.params[i], self.offsets[i]
         flat = self.flat_grads[off:off + p.numel()]
-        if _is_channels_last(p.data):
+        if self._cl[i]:
             N, Cc, H, W = p.shape
             return flat.view(N, H, W, Cc).permute(0, 3, 1, 2)
         return flat.view(p.shape)
@@ -106,13 +111,13 @@ class Arena(object):
         """Copy every p.grad into its slot of the flat gradient buffer (one or
         a few multi-tensor launches); optionally ||g||^2 -> sumsq_out[0]."""
         srcs, counts, offs = [], [], []
-        for p, off in zip(self.params, self.offsets):
+        for i, (p, off) in enumerate(zip(self.params, self.offsets)):
             g = p.grad
             if g is None:
                 continue
             if g.dtype != self.dtype:
                 raise K.KungFuCudaError('gradient dtype %s != arena dtype %s' % (g.dtype, self.dtype))
-            if _is_channels_last(p.data):
+            if self._cl[i]:
                 if not g.is_contiguous(memory_format=torch.channels_last):
                     g = g.contiguous(memory_format=torch.channels_last)
             elif not g.is_contiguous():
