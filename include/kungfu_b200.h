@@ -255,18 +255,23 @@ size_t kfb_symm_granularity(int device, int multicast);
 
 /* ---- model kernels (channels-last bf16 training blocks) ------------------- */
 
-/* y = relu?(bn(x) [+ residual]) forward/backward for NHWC bf16 activations
- * with fp32 statistics: two passes over x instead of torch's four or five. */
+/* y = relu?(bn(x) [+ residual]) forward/backward for NHWC bf16/f16 activations
+ * (dtype) with fp32 statistics. rows = N*H*W; channels % 8 == 0, <= 2048.
+ * scratch: device float[kfb_bn_scratch_floats(rows, channels)], private to the
+ * call. training == 0 normalises with the running statistics. y (the forward
+ * output) is only read by the backward when relu != 0. dresidual may be NULL. */
+int kfb_bn_scratch_floats(long long rows, int channels);
 int kfb_bn_act_fwd(const void *x, const void *residual, void *y,
                    const float *weight, const float *bias, float *running_mean,
                    float *running_var, float *save_mean, float *save_invstd,
                    int64_t rows, int channels, float eps, float momentum,
-                   int relu, int training, float *scratch, void *stream);
+                   int relu, int training, int dtype, float *scratch,
+                   void *stream);
 int kfb_bn_act_bwd(const void *dy, const void *x, const void *y,
                    const float *weight, const float *save_mean,
                    const float *save_invstd, void *dx, void *dresidual,
                    float *dweight, float *dbias, int64_t rows, int channels,
-                   int relu, float *scratch, void *stream);
+                   int relu, int dtype, float *scratch, void *stream);
 
 #ifdef __cplusplus
 }

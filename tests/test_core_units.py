@@ -1,0 +1,186 @@
+"""Unit tests of the C++ core through its C ABI (no processes, no GPU).
+Mirrors the reference's Go/C++ unit tests: /root/reference/srcs/go/plan/*_test.go,
+/root/reference/tests/cpp/unit/test_{dtype,mst,op}.cpp."""
+import ctypes as C
+import json
+
+import numpy as np
+import pytest
+
+from kungfu_b200 import _host as H
+
+
+def _s(fn, *args, cap=1 << 16):
+    buf = C.create_string_buffer(cap)
+    n = fn(*args, buf, cap)
+    assert n >= 0, H.lib().kf_last_error().decode()
+    return buf.value.decode()
+
+
+def _lib():
+    l = H.lib()
+    l.kf_gen_strategy_graphs.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+    l.kf_minimum_spanning_tree.argtypes = [C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_int32)]
+    l.kf_transform2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int]
+    l.kf_transform2.restype = None
+    l.kf_cluster_resize.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    l.kf_parse_hostfile.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    l.kf_gen_peer_list.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_char_p, C.c_int]
+    return l
+
+
+PEERS_1HOST = b'127.0.0.1:10000,127.0.0.1:10001,127.0.0.1:10002,127.0.0.1:10003'
+PEERS_2HOST = b'10.0.0.1:10000,10.0.0.1:10001,10.0.0.2:10000,10.0.0.2:10001,10.0.0.3:10000'
+
+
+def _edges(s):
+    import re
+    return set((int(a), int(b)) for a, b in re.findall(r'\((\d+)->(\d+)\)', s))
+
+
+def _loops(s):
+    import re
+    return set(int(a) for a in re.findall(r'\((\d+)\)', s))
+
+
+def test_star_and_auto_single_host():
+    l = _lib()
+    for name in (b'STAR', b'AUTO'):
+        out = _s(l.kf_gen_strategy_graphs, PEERS_1HOST, name).strip().split('\n')
+        assert len(out) == 1
+        red, bc = out[0].split(' bcast=')
+        assert _edges(bc) == {(0, 1), (0, 2), (0, 3)}
+        assert _edges(red) == {(1, 0), (2, 0), (3, 0)}
+        assert _loops(red) == {0, 1, 2, 3}
+
+
+def test_ring_has_np_rotations_and_each_is_a_chain():
+    l = _lib()
+    out = _s(l.kf_gen_strategy_graphs, PEERS_1HOST, b'RING').strip().split('\n')
+    assert len(out) == 4
+    for line in out:
+        red, bc = line.split(' bcast=')
+        assert len(_edges(red)) == 3 and len(_edges(bc)) == 3
+        # reduce chain ends where the broadcast chain starts
+        sinks = {b for _, b in _edges(red)} - {a for a, _ in _edges(red)}
+        roots = {a for a, _ in _edges(bc)} - {b for _, b in _edges(bc)}
+        assert sinks == roots and len(sinks) == 1
+
+
+def test_clique_tree_binary_tree_star_multi():
+    l = _lib()
+    assert len(_s(l.kf_gen_strategy_graphs, PEERS_1HOST, b'CLIQUE').strip().split('\n')) == 4
+    bt = _s(l.kf_gen_strategy_graphs, PEERS_1HOST, b'BINARY_TREE')
+    assert _edges(bt.split(' bcast=')[1]) == {(0, 1), (0, 2), (1, 3)}
+    # two-level shapes on 3 hosts: masters are ranks 0, 2, 4
+    tree = _s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'TREE').split(' bcast=')[1]
+    assert _edges(tree) == {(0, 1), (2, 3), (0, 2), (0, 4)}
+    bts = _s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'BINARY_TREE_STAR').split(' bcast=')[1]
+    assert _edges(bts) == {(0, 1), (2, 3), (0, 2), (0, 4)}
+    assert len(_s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'MULTI_BINARY_TREE_STAR').strip().split('\n')) == 3
+    assert len(_s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'MULTI_STAR').strip().split('\n')) == 3
+    # AUTO on several hosts = BINARY_TREE_STAR
+    assert _s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'AUTO') == _s(l.kf_gen_strategy_graphs, PEERS_2HOST, b'BINARY_TREE_STAR')
+    assert l.kf_gen_strategy_graphs(PEERS_1HOST, b'NOPE', C.create_string_buffer(16), 16) < 0
+
+
+def test_every_bcast_graph_is_a_spanning_tree():
+    l = _lib()
+    for peers, n in ((PEERS_1HOST, 4), (PEERS_2HOST, 5)):
+        for name in (b'STAR', b'TREE', b'BINARY_TREE', b'BINARY_TREE_STAR', b'MULTI_STAR', b'CLIQUE', b'RING',
+                     b'MULTI_BINARY_TREE_STAR'):
+            for line in _s(l.kf_gen_strategy_graphs, peers, name).strip().split('\n'):
+                e = _edges(line.split(' bcast=')[1])
+                assert len(e) == n - 1
+                children = [b for _, b in e]
+                assert len(set(children)) == n - 1  # every non-root has exactly one parent
+
+
+def test_minimum_spanning_tree_total_weight():
+    l = _lib()
+    rng = np.random.RandomState(0)
+    for n in (2, 5, 9):
+        w = rng.rand(n, n).astype(np.float32)
+        edges = (C.c_int32 * (2 * (n - 1)))()
+        k = l.kf_minimum_spanning_tree(w.ctypes.data_as(C.POINTER(C.c_float)), n, edges)
+        assert k == n - 1
+        sym = (w + w.T) / 2
+        got = sum(sym[edges[2 * i], edges[2 * i + 1]] for i in range(k))
+        # Kruskal oracle
+        parent = list(range(n))
+
+        def find(a):
+            while parent[a] != a:
+                a = parent[a]
+            return a
+        tot = 0.0
+        for wt, i, j in sorted((sym[i, j], i, j) for i in range(n) for j in range(i + 1, n)):
+            a, b = find(i), find(j)
+            if a != b:
+                parent[a] = b
+                tot += wt
+        assert abs(got - tot) < 1e-5
+
+
+@pytest.mark.parametrize('np_dt,code', [(np.float32, H.F32), (np.float64, H.F64), (np.int32, H.I32), (np.int64, H.I64),
+                                        (np.uint8, H.U8), (np.int8, H.I8), (np.int16, H.I16), (np.float16, H.F16)])
+def test_transform2_all_ops(np_dt, code):
+    l = _lib()
+    rng = np.random.RandomState(1)
+    x = (rng.rand(1003) * 4 + 1).astype(np_dt)
+    y = (rng.rand(1003) * 4 + 1).astype(np_dt)
+    for op, f in ((0, np.add), (1, np.minimum), (2, np.maximum), (3, np.multiply)):
+        z = np.zeros_like(x)
+        l.kf_transform2(x.ctypes.data, y.ctypes.data, z.ctypes.data, x.size, code, op)
+        ref = f(x, y)
+        if np_dt == np.float16:
+            assert np.allclose(z.astype(np.float32), ref.astype(np.float32), rtol=2e-3)
+        else:
+            assert np.array_equal(z, ref)
+
+
+def test_transform2_bf16_sum_rounds_to_nearest_even():
+    import torch
+    l = _lib()
+    a = torch.randn(1000).bfloat16()
+    b = torch.randn(1000).bfloat16()
+    z = torch.zeros(1000, dtype=torch.bfloat16)
+    l.kf_transform2(a.data_ptr(), b.data_ptr(), z.data_ptr(), 1000, H.BF16, 0)
+    assert torch.equal(z, (a.float() + b.float()).bfloat16())
+
+
+def test_cluster_resize_grow_and_shrink():
+    l = _lib()
+    c = json.dumps({'Runners': ['10.0.0.1:38080', '10.0.0.2:38080'], 'Workers': ['10.0.0.1:10000']}).encode()
+    grown = json.loads(_s(l.kf_cluster_resize, c, 4))
+    # growth goes to the least loaded runner, on the next free port
+    assert grown['Workers'] == ['10.0.0.1:10000', '10.0.0.2:10000', '10.0.0.1:10001', '10.0.0.2:10001']
+    shrunk = json.loads(_s(l.kf_cluster_resize, json.dumps(grown).encode(), 2))
+    assert shrunk['Workers'] == grown['Workers'][:2]
+    assert shrunk['Runners'] == grown['Runners']
+    bad = json.dumps({'Runners': [], 'Workers': ['10.0.0.9:1']}).encode()
+    assert l.kf_cluster_resize(bad, 2, C.create_string_buffer(64), 64) < 0
+
+
+def test_hostfile_and_peer_list_generation():
+    l = _lib()
+    text = b"# comment\n10.0.0.1 slots=4\n10.0.0.2 slots=2 public_addr=gw.example\n\n"
+    assert _s(l.kf_parse_hostfile, text) == '10.0.0.1:4:10.0.0.1,10.0.0.2:2:gw.example'
+    assert l.kf_parse_hostfile(b"not-an-ip slots=1\n", C.create_string_buffer(64), 64) < 0
+    peers = _s(l.kf_gen_peer_list, b'10.0.0.1:2,10.0.0.2:2', 3, b'10000-10010')
+    assert peers == '10.0.0.1:10000,10.0.0.1:10001,10.0.0.2:10000'
+    assert l.kf_gen_peer_list(b'10.0.0.1:2', 3, b'10000-10010', C.create_string_buffer(64), 64) < 0  # over capacity
+
+
+def test_single_process_mode_and_ema():
+    import kungfu_b200.python as kfpy
+    assert kfpy.current_rank() == 0 and kfpy.current_cluster_size() == 1
+    assert kfpy.current_local_rank() == 0 and kfpy.current_local_size() == 1
+    assert not kfpy.detached()
+    kfpy.run_barrier()
+    assert kfpy.resize_cluster(1) == (False, False)
+    from kungfu_b200.utils import ExponentialMovingAverage
+    ema = ExponentialMovingAverage(0.9)
+    vals = [round(ema.update(x), 4) for x in (2, 3, 4, 5, 6)]
+    # the reference's unit test values (tests/python/unit, alpha 0.9)
+    assert vals == [2.0, 2.1, 2.29, 2.561, 2.9049]

@@ -1,0 +1,60 @@
+"""Loopback multi-process tests launched with our own kungfu-run, np = 1..4 x
+every strategy, the way the reference tests itself
+(/root/reference/scripts/tests/run-integration-tests.sh:30-38,
+/root/reference/scripts/tests/run-op-tests.sh)."""
+import os
+
+import pytest
+import torch
+
+from conftest import ROOT, run_workers
+
+W = os.path.join(ROOT, 'tests', 'workers')
+STRATEGIES = ['STAR', 'MULTI_STAR', 'RING', 'CLIQUE', 'TREE', 'BINARY_TREE', 'BINARY_TREE_STAR',
+              'MULTI_BINARY_TREE_STAR', 'AUTO']
+
+
+def _ok(res, np_):
+    assert res.returncode == 0, res.stdout[-4000:]
+    assert res.stdout.count('OK') >= np_, res.stdout[-4000:]
+
+
+@pytest.mark.parametrize('np_', [1, 2, 3, 4])
+def test_ops_auto(np_):
+    _ok(run_workers(np_, os.path.join(W, 'ops_worker.py')), np_)
+
+
+@pytest.mark.parametrize('strategy', STRATEGIES)
+def test_ops_every_strategy(strategy):
+    _ok(run_workers(4, os.path.join(W, 'ops_worker.py'), strategy=strategy), 4)
+
+
+@pytest.mark.parametrize('kind', ['ssgd', 'sma', 'pair', 'monitors'])
+@pytest.mark.parametrize('np_', [1, 2, 4])
+def test_optimizers(kind, np_):
+    _ok(run_workers(np_, os.path.join(W, 'optim_worker.py'), args=[kind]), np_)
+
+
+def test_mnist_slp_np_invariance(tmp_path):
+    outs = []
+    for np_ in (1, 2, 4):
+        out = str(tmp_path / ('slp%d.pt' % np_))
+        _ok(run_workers(np_, os.path.join(W, 'mnist_slp_worker.py'), args=['48', '40', out]), np_)
+        outs.append(torch.load(out))
+    for o in outs[1:]:
+        # same mathematics, different fp32 summation order across the splits
+        assert torch.allclose(o['w'], outs[0]['w'], atol=2e-4)
+        assert torch.allclose(o['b'], outs[0]['b'], atol=2e-4)
+        assert abs(o['acc'] - outs[0]['acc']) <= 1e-3
+    assert outs[0]['acc'] > 0.3
+
+
+def test_bad_worker_tears_down_job(tmp_path):
+    """One failing worker fails the whole job quickly (reference: kungfu-bad-worker)."""
+    script = tmp_path / 'bad.py'
+    script.write_text("import sys, time\nimport kungfu_b200.torch as kf\n"
+                      "r = kf.current_rank()\n"
+                      "if r == 0:\n    sys.exit(3)\n"
+                      "time.sleep(60)\n")
+    res = run_workers(3, str(script), timeout=40)
+    assert res.returncode != 0

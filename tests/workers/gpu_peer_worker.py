@@ -1,0 +1,207 @@
+"""Multi-GPU checks of the peer-memory path: one process per GPU, launched by
+kungfu-run -allow-nvlink. Every result is compared with a local fp32 oracle
+built from the other ranks' (deterministically seeded) inputs."""
+import ctypes as C
+import sys
+
+import torch
+
+import kungfu_b200.python as kfpy
+import kungfu_b200.torch as kf
+from kungfu_b200.ops import _cuda as K
+from kungfu_b200.ops import collective as coll
+from kungfu_b200.parallel import comm as pc
+
+rank, np_ = kf.current_rank(), kf.current_cluster_size()
+torch.cuda.set_device(kf.get_cuda_index())
+dev = torch.device('cuda', torch.cuda.current_device())
+comm = pc.default_comm()
+assert comm.np == np_ and comm.rank == rank
+
+
+def inputs(n, dtype, tag):
+    out = []
+    for r in range(np_):
+        g = torch.Generator().manual_seed(1000 * tag + r)
+        out.append((torch.randn(n, generator=g) * 2).to(dtype))
+    return out
+
+
+def check_allreduce():
+    algos = [K.ALGO_ONESHOT, K.ALGO_TWOSHOT]
+    n = 1 << 20
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2)):
+        es = torch.empty(0, dtype=dtype).element_size()
+        buf = comm.alloc(n * es, multicast=True)
+        out = comm.alloc(n * es, multicast=True)
+        these = list(algos) + ([K.ALGO_NVLS] if buf.mc_ptr else [])
+        xs = inputs(n, dtype, 1)
+        ref = torch.stack([x.float() for x in xs]).sum(0) / np_
+        for algo in these:
+            buf.view(dtype)[:n].copy_(xs[rank])
+            ss = torch.zeros(1, device=dev)
+            coll.all_reduce(comm, buf, n, dtype, 'sum', scale=1.0 / np_, algo=algo, out=out, sumsq_out=ss)
+            torch.cuda.synchronize()
+            got = out.view(dtype)[:n].float().cpu()
+            assert torch.allclose(got, ref, rtol=tol, atol=tol), (algo, dtype, (got - ref).abs().max())
+            assert abs(float(ss) - float((ref * ref).sum())) < 2e-2 * float((ref * ref).sum()), (algo, float(ss))
+            # every rank holds identical bits / norms
+            sums = kf.ops.all_gather(torch.tensor([float(ss), float(got.double().sum())], dtype=torch.float64))
+            assert (sums == sums[0]).all(), (algo, sums)
+        if rank == 0:
+            print('allreduce ok', dtype, 'algos', these, flush=True)
+    # in place two-shot, repeated (epoch flags), min/max
+    buf = comm.alloc(4096 * 4)
+    for it in range(20):
+        buf.view(torch.float32)[:4096].fill_(float(rank + it))
+        coll.all_reduce(comm, buf, 4096, torch.float32, 'max', algo=K.ALGO_TWOSHOT)
+        torch.cuda.synchronize()
+        assert (buf.view(torch.float32)[:4096] == np_ - 1 + it).all()
+
+
+def check_movers():
+    n = 100000
+    buf = comm.alloc(n * 4, multicast=True)
+    for use_mc in (False, True):
+        buf.view(torch.float32)[:n].fill_(float(rank + 1))
+        coll.broadcast(comm, buf, n * 4, root=np_ - 1, use_multicast=use_mc)
+        torch.cuda.synchronize()
+        assert (buf.view(torch.float32)[:n] == np_).all(), use_mc
+    src, dst = comm.alloc(1024), comm.alloc(1024 * np_)
+    src.local[:1024].fill_(rank + 1)
+    coll.all_gather(comm, src, dst, 1024)
+    torch.cuda.synchronize()
+    got = dst.local[:1024 * np_].view(np_, 1024)
+    for r in range(np_):
+        assert (got[r] == r + 1).all()
+    agree = torch.zeros(1, dtype=torch.int32, device=dev)
+    coll.consensus(comm, src, 1024, agree)
+    torch.cuda.synchronize()
+    assert int(agree) == (1 if np_ == 1 else 0)
+    # tensor API on CUDA tensors
+    x = torch.full((1000, ), float(rank), device=dev)
+    assert (kf.ops.all_reduce_fn(x) == sum(range(np_))).all()
+    assert kf.ops.all_gather(x).shape == (np_, 1000)
+    h = kf.ops.inplace_all_reduce_async_op(x, 'x', 'max')
+    kf.ops.wait_handle(h)
+    torch.cuda.synchronize()
+    assert (x == np_ - 1).all()
+    sd = {'a': torch.full((33, ), float(rank), device=dev)}
+    kf.broadcast_parameters(sd)
+    torch.cuda.synchronize()
+    assert (sd['a'] == 0).all()
+
+
+def check_fused_optimizers():
+    from kungfu_b200.optim import FusedSGD
+    torch.manual_seed(0)
+
+    def make():
+        torch.manual_seed(0)
+        return torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 16)).to(dev)
+
+    def batch(r, step):
+        g = torch.Generator().manual_seed(77 + 13 * r + step)
+        return torch.randn(32, 64, generator=g).to(dev), torch.randint(0, 16, (32, ), generator=g).to(dev)
+
+    # S-SGD fused == single process on the concatenated batch
+    m = make()
+    opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.1, momentum=0.9), m.named_parameters())
+    ref = make()
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+    for step in range(4):
+        x, y = batch(rank, step)
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+        ropt.zero_grad()
+        xs, ys = zip(*[batch(r, step) for r in range(np_)])
+        torch.nn.functional.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
+        ropt.step()
+    torch.cuda.synchronize()
+    for p, q in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, rtol=1e-4, atol=1e-5), (p - q).abs().max()
+    opt.consolidate()
+    if rank == 0:
+        print('fused S-SGD ok', flush=True)
+
+    # generic optimizer (Adam) through GradSync, plain and overlapped
+    for overlap in (False, True):
+        m = make()
+        opt = kf.optimizers.SynchronousSGDOptimizer(torch.optim.Adam(m.parameters(), lr=1e-2), m.named_parameters(), overlap=overlap)
+        ref = make()
+        ropt = torch.optim.Adam(ref.parameters(), lr=1e-2)
+        for step in range(3):
+            x, y = batch(rank, step)
+            opt.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+            ropt.zero_grad()
+            xs, ys = zip(*[batch(r, step) for r in range(np_)])
+            torch.nn.functional.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
+            ropt.step()
+        torch.cuda.synchronize()
+        for p, q in zip(m.parameters(), ref.parameters()):
+            assert torch.allclose(p, q, rtol=1e-3, atol=1e-4), (overlap, (p - q).abs().max())
+    if rank == 0:
+        print('GradSync ok', flush=True)
+
+    # SMA fused: replicas stay finite and get closer
+    m = make()
+    for p in m.parameters():
+        p.data += 0.1 * rank
+    opt = kf.optimizers.SynchronousAveragingOptimizer(FusedSGD(m.parameters(), lr=0.05), m.named_parameters(), alpha=0.5)
+    w0 = kf.ops.all_gather(next(m.parameters()).data.clone())
+    for step in range(5):
+        x, y = batch(rank, step)
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+    w1 = kf.ops.all_gather(next(m.parameters()).data.clone())
+    torch.cuda.synchronize()
+    if np_ > 1:
+        assert float((w1[0] - w1[-1]).abs().max()) < 0.2 * float((w0[0] - w0[-1]).abs().max())
+    # PairAveraging fused: one-sided pulls, no barrier
+    m = make()
+    opt = kf.optimizers.PairAveragingOptimizer(FusedSGD(m.parameters(), lr=0.05), m.named_parameters())
+    for step in range(6):
+        x, y = batch(rank, step)
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    assert all(torch.isfinite(p).all() for p in m.parameters())
+    kf.run_barrier()
+    if rank == 0:
+        print('SMA / PairAveraging ok; torn reads', int(opt.torn_reads), flush=True)
+    # monitors
+    m = make()
+    opt = kf.optimizers.MonitorGradientNoiseScaleOptimizer(FusedSGD(m.parameters(), lr=0.05), m.named_parameters(), device_batch_size=32)
+    for step in range(3):
+        x, y = batch(rank, step)
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+    if np_ > 1:
+        assert opt.noise_scale is not None and torch.isfinite(opt.noise_scale)
+    m = make()
+    opt = kf.optimizers.MonitorGradientVarianceOptimizer(torch.optim.SGD(m.parameters(), lr=0.05), m.named_parameters())
+    x, y = batch(rank, 0)
+    torch.nn.functional.cross_entropy(m(x), y).backward()
+    gs = kf.ops.all_gather(torch.cat([p.grad.reshape(-1) for p in m.parameters()]))
+    opt.step()
+    exp, off = 0.0, 0
+    for p in m.parameters():
+        st = gs[:, off:off + p.numel()]
+        exp += float(torch.norm((st * st).mean(0) - st.mean(0) ** 2))
+        off += p.numel()
+    assert abs(float(opt.variance) - exp) < 1e-3 * max(exp, 1e-6), (float(opt.variance), exp)
+    if rank == 0:
+        print('monitors ok', flush=True)
+
+
+check_allreduce()
+check_movers()
+check_fused_optimizers()
+kf.run_barrier()
+print('OK rank %d/%d multicast=%s' % (rank, np_, getattr(comm, 'multicast_ok', None)), flush=True)
