@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument('--batch-size', type=int, default=256, help='per-GPU batch')
     ap.add_argument('--image-size', type=int, default=224)
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of a captured CUDA graph')
-    ap.add_argument('--fused-bn', type=int, default=int(os.environ.get('KUNGFU_FUSED_BN', '0')))
+    ap.add_argument('--fused-bn', type=int, default=int(os.environ.get('KUNGFU_FUSED_BN', '1')))
     ap.add_argument('--momentum', type=float, default=0.0)
     ap.add_argument('--skip-e2e', action='store_true')
     return ap.parse_args()

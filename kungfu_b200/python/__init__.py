@@ -97,6 +97,9 @@ def resize_cluster_from_url():
 
 def _on_membership_change():
     try:
+        from ..torch.ops import collective as tops
+        tops._reset_names()
+        tops.reset_staging()
         from ..parallel import comm
         comm.reset_default_comm()
     except Exception:  # device layer not in use

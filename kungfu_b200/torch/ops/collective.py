@@ -37,11 +37,23 @@ def _host_dtype(t):
         raise TypeError('unsupported dtype %s' % t.dtype)
 
 
-def _name(name, kind):
+def _name(name, kind, concurrent=False):
+    """Wire name of a collective. Messages of one name between two peers are
+    FIFO, so unnamed synchronous ops can share a constant name (every rank must
+    issue them in the same order anyway). Unnamed ASYNC ops may be in flight
+    together and get a sequence number, which restarts whenever the membership
+    changes so that joiners and survivors count from the same point."""
     if name is None:
-        _anon[0] += 1
-        name = 'kungfu::%s::%d' % (kind, _anon[0])
+        if concurrent:
+            _anon[0] += 1
+            name = 'kungfu::%s::%d' % (kind, _anon[0])
+        else:
+            name = 'kungfu::%s' % kind
     return name.encode()
+
+
+def _reset_names():
+    _anon[0] = 0
 
 
 def _check(rc, what):
@@ -190,7 +202,7 @@ def inplace_all_reduce_async_op(x, name=None, op=None):
     if not x.is_contiguous():
         raise ValueError('in-place all-reduce needs a contiguous tensor')
     h = H.lib().kf_all_reduce_async(kfpy.peer()._h, x.data_ptr(), x.data_ptr(), x.numel(),
-                                    _host_dtype(x), H.OPS[op], _name(name, 'all_reduce'))
+                                    _host_dtype(x), H.OPS[op], _name(name, 'all_reduce', True))
     if h < 0:
         _check(-1, 'all_reduce_async')
     return _new_handle(('cpu', h, x))
@@ -211,7 +223,7 @@ def inplace_broadcast_async_op(x, name=None):
     if not x.is_contiguous():
         raise ValueError('in-place broadcast needs a contiguous tensor')
     h = H.lib().kf_broadcast_async(kfpy.peer()._h, x.data_ptr(), x.data_ptr(), x.numel(),
-                                   _host_dtype(x), _name(name, 'broadcast'))
+                                   _host_dtype(x), _name(name, 'broadcast', True))
     if h < 0:
         _check(-1, 'broadcast_async')
     return _new_handle(('cpu', h, x))

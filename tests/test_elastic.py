@@ -1,0 +1,94 @@
+"""Elastic resize on loopback: kungfu-run -w with the builtin config server,
+sizes 1 -> 2 -> 4 -> 2 -> 1 (the reference's bench-adaptation / step-based
+schedule tests, /root/reference/tests/python/integration/test_step_based_schedule.py:7-13,
+/root/reference/benchmarks/adaptation/bench-adaptation.sh)."""
+import collections
+import os
+import subprocess
+import sys
+import time
+import urllib.request
+
+import pytest
+
+from conftest import ROOT, run_workers
+
+W = os.path.join(ROOT, 'tests', 'workers')
+
+
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize('schedule,steps', [('1:3,2:3,4:3,2:3,1:3', 15), ('2:2,1:2,3:2', 6)])
+def test_resize_schedule(tmp_path, schedule, steps):
+    log = str(tmp_path / 'steps.log')
+    np0 = int(schedule.split(':')[0])
+    cfg_port = _free_port()
+    res = run_workers(np0, os.path.join(W, 'elastic_worker.py'), args=[schedule, str(steps), log], timeout=150,
+                      extra_flags=['-w', '-builtin-config-port', str(cfg_port)])
+    assert res.returncode == 0, res.stdout[-6000:]
+    sizes = collections.defaultdict(set)
+    pids = collections.defaultdict(set)
+    for line in open(log):
+        if line.startswith('detached'):
+            continue
+        step, rank, np_, pid = map(int, line.split())
+        sizes[step].add(np_)
+        pids[step].add(pid)
+    off = 0
+    for part in schedule.split(','):
+        size, n = map(int, part.split(':'))
+        for s in range(off, off + n):
+            assert sizes[s] == {size}, (s, sizes[s], schedule)
+            assert len(pids[s]) == size
+        off += n
+    # the worker that started as rank 0 survives every resize: it was never restarted
+    first = next(iter(pids[0])) if np0 == 1 else None
+    if first is not None:
+        assert all(first in pids[s] for s in range(steps))
+
+
+def test_config_server_rest_api(tmp_path):
+    port = _free_port()
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-config-server')
+    p = subprocess.Popen([exe, '-port', str(port)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    url = 'http://127.0.0.1:%d/config' % port
+    try:
+        for _ in range(50):
+            try:
+                urllib.request.urlopen(url)
+            except urllib.error.HTTPError as e:
+                assert e.code == 404  # nothing stored yet
+                break
+            except Exception:
+                time.sleep(0.1)
+        good = b'{"Runners":["127.0.0.1:38080"],"Workers":["127.0.0.1:10000","127.0.0.1:10001"]}'
+        req = urllib.request.Request(url, data=good, method='PUT')
+        assert urllib.request.urlopen(req).status == 200
+        got = urllib.request.urlopen(url).read().decode()
+        assert '"127.0.0.1:10001"' in got
+        bad = b'{"Runners":[],"Workers":["127.0.0.1:10000"]}'  # worker without a runner on its host
+        with pytest.raises(urllib.error.HTTPError):
+            urllib.request.urlopen(urllib.request.Request(url, data=bad, method='PUT'))
+        # clearing to zero workers freezes the config (PUT -> 403)
+        empty = b'{"Runners":["127.0.0.1:38080"],"Workers":[]}'
+        assert urllib.request.urlopen(urllib.request.Request(url, data=empty, method='PUT')).status == 200
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            urllib.request.urlopen(urllib.request.Request(url, data=good, method='PUT'))
+        assert ei.value.code == 403
+        # POST resets
+        assert urllib.request.urlopen(urllib.request.Request(url, data=b'', method='POST')).status == 200
+        with pytest.raises(urllib.error.HTTPError) as ei:
+            urllib.request.urlopen(url)
+        assert ei.value.code == 404
+        urllib.request.urlopen('http://127.0.0.1:%d/stop' % port)
+        assert p.wait(timeout=10) == 0
+    finally:
+        if p.poll() is None:
+            p.kill()
