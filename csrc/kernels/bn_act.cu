@@ -91,17 +91,44 @@ __global__ void __launch_bounds__(BN_THREADS)
     block_channel_reduce<2>(acc, tx, ty, C8, RY, active, smem, partial + (size_t)blockIdx.x * 2 * C, C);
 }
 
-__global__ void k_bn_finalize(const float *__restrict__ partial, int nblocks, int C, long long rows, float eps,
-                              float momentum, float *running_mean, float *running_var, float *save_mean,
-                              float *save_invstd)
+// Partials are combined by CTAs of 32 channels x 8 slices: coalesced 128-byte
+// reads, 8-way parallel over the partial blocks, fp64, fixed order.
+constexpr int FIN_TX = 32, FIN_TY = 8;
+__device__ __forceinline__ bool
+reduce_partials(const float *__restrict__ partial, int nblocks, int C, double *s_out, double *q_out)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    __shared__ double sh[2][FIN_TY][FIN_TX];
+    const int tx = threadIdx.x % FIN_TX, ty = threadIdx.x / FIN_TX;
+    const int c  = blockIdx.x * FIN_TX + tx;
     double s = 0.0, q = 0.0;
-    for (int b = 0; b < nblocks; ++b) {
-        s += (double)partial[(size_t)b * 2 * C + c];
-        q += (double)partial[(size_t)b * 2 * C + C + c];
+    if (c < C) {
+        for (int b = ty; b < nblocks; b += FIN_TY) {
+            s += (double)partial[(size_t)b * 2 * C + c];
+            q += (double)partial[(size_t)b * 2 * C + C + c];
+        }
     }
+    sh[0][ty][tx] = s;
+    sh[1][ty][tx] = q;
+    __syncthreads();
+    if (ty != 0 || c >= C) return false;
+    s = q = 0.0;
+#pragma unroll
+    for (int k = 0; k < FIN_TY; ++k) {
+        s += sh[0][k][tx];
+        q += sh[1][k][tx];
+    }
+    *s_out = s;
+    *q_out = q;
+    return true;
+}
+
+__global__ void __launch_bounds__(FIN_TX *FIN_TY)
+    k_bn_finalize(const float *__restrict__ partial, int nblocks, int C, long long rows, float eps, float momentum,
+                  float *running_mean, float *running_var, float *save_mean, float *save_invstd)
+{
+    double s, q;
+    if (!reduce_partials(partial, nblocks, C, &s, &q)) return;
+    const int c       = blockIdx.x * FIN_TX + threadIdx.x % FIN_TX;
     const double mean = s / (double)rows;
     double var        = q / (double)rows - mean * mean;
     if (var < 0.0) var = 0.0;
@@ -127,7 +154,8 @@ template <typename T, bool RELU, bool RES>
 __global__ void __launch_bounds__(BN_THREADS)
     k_bn_apply(const uint4 *__restrict__ x, const uint4 *__restrict__ res, uint4 *__restrict__ y,
                const float *__restrict__ weight, const float *__restrict__ bias,
-               const float *__restrict__ mean, const float *__restrict__ invstd, long long rows, int C)
+               const float *__restrict__ mean, const float *__restrict__ invstd, long long rows, int C,
+               uint8_t *__restrict__ mask)
 {
     const int C8 = C >> 3, RY = BN_THREADS / C8;
     const int tx = threadIdx.x % C8, ty = threadIdx.x / C8;
@@ -151,28 +179,38 @@ __global__ void __launch_bounds__(BN_THREADS)
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
+            unsigned bits = 0;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 float o = fmaf(v[u][k], scale[k], shift[k]);
                 if (RES) o += r[u][k];
-                if (RELU) o = fmaxf(o, 0.f);
+                if (RELU) {
+                    bits |= (o > 0.f ? 1u : 0u) << k;
+                    o = fmaxf(o, 0.f);
+                }
                 v[u][k] = o;
             }
             Ld8<T>::store(y + (row + u * stride) * C8 + tx, v[u]);
+            if (RELU && mask) mask[(row + u * stride) * C8 + tx] = (uint8_t)bits;
         }
     }
     for (; row < rows; row += stride) {
         float v[8], r[8];
         Ld8<T>::load(x + row * C8 + tx, v);
         if (RES) Ld8<T>::load(res + row * C8 + tx, r);
+        unsigned bits = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             float o = fmaf(v[k], scale[k], shift[k]);
             if (RES) o += r[k];
-            if (RELU) o = fmaxf(o, 0.f);
+            if (RELU) {
+                bits |= (o > 0.f ? 1u : 0u) << k;
+                o = fmaxf(o, 0.f);
+            }
             v[k] = o;
         }
         Ld8<T>::store(y + row * C8 + tx, v);
+        if (RELU && mask) mask[row * C8 + tx] = (uint8_t)bits;
     }
 }
 
@@ -180,7 +218,7 @@ __global__ void __launch_bounds__(BN_THREADS)
 // partial[b][0][c] = sum dz, partial[b][1][c] = sum dz * xhat
 template <typename T, bool RELU>
 __global__ void __launch_bounds__(BN_THREADS)
-    k_bn_bwd_stats(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint4 *__restrict__ y,
+    k_bn_bwd_stats(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint8_t *__restrict__ mask,
                    const float *__restrict__ mean, const float *__restrict__ invstd, long long rows, int C,
                    float *__restrict__ partial)
 {
@@ -201,30 +239,32 @@ __global__ void __launch_bounds__(BN_THREADS)
         const long long stride = (long long)gridDim.x * RY;
         long long row          = (long long)blockIdx.x * RY + ty;
         for (; row + stride < rows; row += 2 * stride) {
-            float g[2][8], v[2][8], o[2][8];
+            float g[2][8], v[2][8];
+            unsigned o[2] = {0xffu, 0xffu};
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 Ld8<T>::load(dy + (row + u * stride) * C8 + tx, g[u]);
                 Ld8<T>::load(x + (row + u * stride) * C8 + tx, v[u]);
-                if (RELU) Ld8<T>::load(y + (row + u * stride) * C8 + tx, o[u]);
+                if (RELU) o[u] = mask[(row + u * stride) * C8 + tx];
             }
 #pragma unroll
             for (int u = 0; u < 2; ++u)
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    const float dz = (RELU && !(o[u][k] > 0.f)) ? 0.f : g[u][k];
+                    const float dz = (RELU && !((o[u] >> k) & 1u)) ? 0.f : g[u][k];
                     acc[0][k] += dz;
                     acc[1][k] = fmaf(dz, (v[u][k] - mu[k]) * is[k], acc[1][k]);
                 }
         }
         for (; row < rows; row += stride) {
-            float g[8], v[8], o[8];
+            float g[8], v[8];
+            unsigned o = 0xffu;
             Ld8<T>::load(dy + row * C8 + tx, g);
             Ld8<T>::load(x + row * C8 + tx, v);
-            if (RELU) Ld8<T>::load(y + row * C8 + tx, o);
+            if (RELU) o = mask[row * C8 + tx];
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                const float dz = (RELU && !(o[k] > 0.f)) ? 0.f : g[k];
+                const float dz = (RELU && !((o >> k) & 1u)) ? 0.f : g[k];
                 acc[0][k] += dz;
                 acc[1][k] = fmaf(dz, (v[k] - mu[k]) * is[k], acc[1][k]);
             }
@@ -233,16 +273,13 @@ __global__ void __launch_bounds__(BN_THREADS)
     block_channel_reduce<2>(acc, tx, ty, C8, RY, active, smem, partial + (size_t)blockIdx.x * 2 * C, C);
 }
 
-__global__ void k_bn_bwd_finalize(const float *__restrict__ partial, int nblocks, int C, float *dweight,
-                                  float *dbias, float *sums /* [2][C] */)
+__global__ void __launch_bounds__(FIN_TX *FIN_TY)
+    k_bn_bwd_finalize(const float *__restrict__ partial, int nblocks, int C, float *dweight, float *dbias,
+                      float *sums /* [2][C] */)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    double s = 0.0, q = 0.0;
-    for (int b = 0; b < nblocks; ++b) {
-        s += (double)partial[(size_t)b * 2 * C + c];
-        q += (double)partial[(size_t)b * 2 * C + C + c];
-    }
+    double s, q;
+    if (!reduce_partials(partial, nblocks, C, &s, &q)) return;
+    const int c = blockIdx.x * FIN_TX + threadIdx.x % FIN_TX;
     sums[c]     = (float)s;
     sums[C + c] = (float)q;
     if (dbias) dbias[c] = (float)s;
@@ -251,7 +288,7 @@ __global__ void k_bn_bwd_finalize(const float *__restrict__ partial, int nblocks
 
 template <typename T, bool RELU, bool RES>
 __global__ void __launch_bounds__(BN_THREADS)
-    k_bn_bwd_apply(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint4 *__restrict__ y,
+    k_bn_bwd_apply(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint8_t *__restrict__ mask,
                    const float *__restrict__ weight, const float *__restrict__ mean,
                    const float *__restrict__ invstd, const float *__restrict__ sums, uint4 *__restrict__ dx,
                    uint4 *__restrict__ dres, long long rows, int C)
@@ -273,18 +310,19 @@ __global__ void __launch_bounds__(BN_THREADS)
     const long long stride = (long long)gridDim.x * RY;
     long long row          = (long long)blockIdx.x * RY + ty;
     for (; row + stride < rows; row += 2 * stride) {
-        float g[2][8], v[2][8], o[2][8];
+        float g[2][8], v[2][8];
+            unsigned o[2] = {0xffu, 0xffu};
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
             Ld8<T>::load(dy + (row + u * stride) * C8 + tx, g[u]);
             Ld8<T>::load(x + (row + u * stride) * C8 + tx, v[u]);
-            if (RELU) Ld8<T>::load(y + (row + u * stride) * C8 + tx, o[u]);
+            if (RELU) o[u] = mask[(row + u * stride) * C8 + tx];
         }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                const float dz   = (RELU && !(o[u][k] > 0.f)) ? 0.f : g[u][k];
+                const float dz   = (RELU && !((o[u] >> k) & 1u)) ? 0.f : g[u][k];
                 const float xhat = (v[u][k] - mu[k]) * is[k];
                 g[u][k]          = dz;
                 v[u][k]          = sc[k] * (dz - a[k] - xhat * b[k]);
@@ -294,13 +332,14 @@ __global__ void __launch_bounds__(BN_THREADS)
         }
     }
     for (; row < rows; row += stride) {
-        float g[8], v[8], o[8];
+        float g[8], v[8];
+            unsigned o = 0xffu;
         Ld8<T>::load(dy + row * C8 + tx, g);
         Ld8<T>::load(x + row * C8 + tx, v);
-        if (RELU) Ld8<T>::load(y + row * C8 + tx, o);
+        if (RELU) o = mask[row * C8 + tx];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float dz   = (RELU && !(o[k] > 0.f)) ? 0.f : g[k];
+            const float dz   = (RELU && !((o >> k) & 1u)) ? 0.f : g[k];
             const float xhat = (v[k] - mu[k]) * is[k];
             g[k]             = dz;
             v[k]             = sc[k] * (dz - a[k] - xhat * b[k]);
@@ -343,7 +382,7 @@ template <typename T>
 static int bn_fwd_t(const void *x, const void *residual, void *y, const float *weight, const float *bias,
                     float *running_mean, float *running_var, float *save_mean, float *save_invstd,
                     long long rows, int C, float eps, float momentum, int relu, int training, float *scratch,
-                    cudaStream_t s)
+                    uint8_t *mask, cudaStream_t s)
 {
     const int grid = bn_grid(rows, C);
     const int RY   = BN_THREADS / (C >> 3);
@@ -351,7 +390,7 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
         const size_t smem = (size_t)RY * C * sizeof(float);
         k_bn_stats<T><<<grid, BN_THREADS, smem, s>>>(reinterpret_cast<const uint4 *>(x), rows, C, scratch);
         KFB_CUDA_OK(cudaGetLastError());
-        k_bn_finalize<<<(C + 127) / 128, 128, 0, s>>>(scratch, grid, C, rows, eps, momentum, running_mean,
+        k_bn_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, grid, C, rows, eps, momentum, running_mean,
                                                        running_var, save_mean, save_invstd);
     } else {
         k_bn_eval_prep<<<(C + 127) / 128, 128, 0, s>>>(running_mean, running_var, C, eps, save_mean, save_invstd);
@@ -360,7 +399,7 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
     const uint4 *xp = reinterpret_cast<const uint4 *>(x), *rp = reinterpret_cast<const uint4 *>(residual);
     uint4 *yp       = reinterpret_cast<uint4 *>(y);
 #define KFB_BN_APPLY(R, S)                                                                                  \
-    k_bn_apply<T, R, S><<<grid, BN_THREADS, 0, s>>>(xp, rp, yp, weight, bias, save_mean, save_invstd, rows, C)
+    k_bn_apply<T, R, S><<<grid, BN_THREADS, 0, s>>>(xp, rp, yp, weight, bias, save_mean, save_invstd, rows, C, mask)
     if (relu && residual) KFB_BN_APPLY(true, true);
     else if (relu) KFB_BN_APPLY(true, false);
     else if (residual) KFB_BN_APPLY(false, true);
@@ -373,23 +412,24 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
 extern "C" int kfb_bn_act_fwd(const void *x, const void *residual, void *y, const float *weight,
                               const float *bias, float *running_mean, float *running_var, float *save_mean,
                               float *save_invstd, int64_t rows, int channels, float eps, float momentum, int relu,
-                              int training, int dtype, float *scratch, void *stream)
+                              int training, int dtype, float *scratch, void *relu_mask, void *stream)
 {
     int rc = bn_check(rows, channels);
     if (rc) return rc;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (dtype == KFB_BF16)
         return bn_fwd_t<__nv_bfloat16>(x, residual, y, weight, bias, running_mean, running_var, save_mean,
-                                       save_invstd, rows, channels, eps, momentum, relu, training, scratch, s);
+                                       save_invstd, rows, channels, eps, momentum, relu, training, scratch,
+                                       reinterpret_cast<uint8_t *>(relu_mask), s);
     if (dtype == KFB_F16)
         return bn_fwd_t<__half>(x, residual, y, weight, bias, running_mean, running_var, save_mean, save_invstd,
-                                rows, channels, eps, momentum, relu, training, scratch, s);
+                                rows, channels, eps, momentum, relu, training, scratch, reinterpret_cast<uint8_t *>(relu_mask), s);
     set_last_error("bn_act supports bf16 / f16 activations");
     return KFB_ERR_UNSUPP;
 }
 
 template <typename T>
-static int bn_bwd_t(const void *dy, const void *x, const void *y, const float *weight, const float *save_mean,
+static int bn_bwd_t(const void *dy, const void *x, const void *mask, const float *weight, const float *save_mean,
                     const float *save_invstd, void *dx, void *dres, float *dweight, float *dbias, long long rows,
                     int C, int relu, float *scratch, cudaStream_t s)
 {
@@ -397,14 +437,15 @@ static int bn_bwd_t(const void *dy, const void *x, const void *y, const float *w
     const int RY      = BN_THREADS / (C >> 3);
     const size_t smem = (size_t)RY * C * sizeof(float);
     float *sums       = scratch + (size_t)grid * 2 * C;
-    const uint4 *gp = reinterpret_cast<const uint4 *>(dy), *xp = reinterpret_cast<const uint4 *>(x),
-                *yp = reinterpret_cast<const uint4 *>(y);
+    const uint4 *gp = reinterpret_cast<const uint4 *>(dy), *xp = reinterpret_cast<const uint4 *>(x)
+                ;
+    const uint8_t *yp = reinterpret_cast<const uint8_t *>(mask);
     if (relu)
         k_bn_bwd_stats<T, true><<<grid, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
     else
         k_bn_bwd_stats<T, false><<<grid, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
     KFB_CUDA_OK(cudaGetLastError());
-    k_bn_bwd_finalize<<<(C + 127) / 128, 128, 0, s>>>(scratch, grid, C, dweight, dbias, sums);
+    k_bn_bwd_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, grid, C, dweight, dbias, sums);
     KFB_CUDA_OK(cudaGetLastError());
     uint4 *dxp = reinterpret_cast<uint4 *>(dx), *drp = reinterpret_cast<uint4 *>(dres);
 #define KFB_BN_BWD(R, S)                                                                                    \
@@ -418,19 +459,23 @@ static int bn_bwd_t(const void *dy, const void *x, const void *y, const float *w
     return KFB_OK;
 }
 
-extern "C" int kfb_bn_act_bwd(const void *dy, const void *x, const void *y, const float *weight,
+extern "C" int kfb_bn_act_bwd(const void *dy, const void *x, const void *relu_mask, const float *weight,
                               const float *save_mean, const float *save_invstd, void *dx, void *dresidual,
                               float *dweight, float *dbias, int64_t rows, int channels, int relu, int dtype,
                               float *scratch, void *stream)
 {
     int rc = bn_check(rows, channels);
     if (rc) return rc;
+    if (relu && !relu_mask) {
+        set_last_error("bn_act backward with relu needs the mask written by the forward");
+        return KFB_ERR_ARG;
+    }
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     if (dtype == KFB_BF16)
-        return bn_bwd_t<__nv_bfloat16>(dy, x, y, weight, save_mean, save_invstd, dx, dresidual, dweight, dbias, rows,
+        return bn_bwd_t<__nv_bfloat16>(dy, x, relu_mask, weight, save_mean, save_invstd, dx, dresidual, dweight, dbias, rows,
                                        channels, relu, scratch, s);
     if (dtype == KFB_F16)
-        return bn_bwd_t<__half>(dy, x, y, weight, save_mean, save_invstd, dx, dresidual, dweight, dbias, rows,
+        return bn_bwd_t<__half>(dy, x, relu_mask, weight, save_mean, save_invstd, dx, dresidual, dweight, dbias, rows,
                                 channels, relu, scratch, s);
     set_last_error("bn_act supports bf16 / f16 activations");
     return KFB_ERR_UNSUPP;

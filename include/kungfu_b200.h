@@ -258,20 +258,30 @@ size_t kfb_symm_granularity(int device, int multicast);
 /* y = relu?(bn(x) [+ residual]) forward/backward for NHWC bf16/f16 activations
  * (dtype) with fp32 statistics. rows = N*H*W; channels % 8 == 0, <= 2048.
  * scratch: device float[kfb_bn_scratch_floats(rows, channels)], private to the
- * call. training == 0 normalises with the running statistics. y (the forward
- * output) is only read by the backward when relu != 0. dresidual may be NULL. */
+ * call. training == 0 normalises with the running statistics. relu_mask:
+ * uint8[rows * channels / 8], one bit per element (y > 0), written by the
+ * forward when relu != 0 and read by the backward instead of re-reading y.
+ * dresidual may be NULL. */
 int kfb_bn_scratch_floats(long long rows, int channels);
 int kfb_bn_act_fwd(const void *x, const void *residual, void *y,
                    const float *weight, const float *bias, float *running_mean,
                    float *running_var, float *save_mean, float *save_invstd,
                    int64_t rows, int channels, float eps, float momentum,
                    int relu, int training, int dtype, float *scratch,
-                   void *stream);
-int kfb_bn_act_bwd(const void *dy, const void *x, const void *y,
+                   void *relu_mask, void *stream);
+int kfb_bn_act_bwd(const void *dy, const void *x, const void *relu_mask,
                    const float *weight, const float *save_mean,
                    const float *save_invstd, void *dx, void *dresidual,
                    float *dweight, float *dbias, int64_t rows, int channels,
                    int relu, int dtype, float *scratch, void *stream);
+
+/* 3x3 / stride 2 / pad 1 max pooling, NHWC bf16/f16. idx: uint8[N*OH*OW*C]
+ * window slot (0..8) of the maximum, written by fwd, read by bwd (a gather:
+ * deterministic, no atomics). OH = (H-1)/2+1, OW = (W-1)/2+1. */
+int kfb_maxpool3x3s2_fwd(const void *x, void *y, void *idx, int N, int H, int W,
+                         int C, int dtype, void *stream);
+int kfb_maxpool3x3s2_bwd(const void *dy, const void *idx, void *dx, int N, int H,
+                         int W, int C, int dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -31,6 +31,7 @@ CUDA_SOURCES = [
     'csrc/kernels/collectives.cu',
     'csrc/kernels/optim.cu',
     'csrc/kernels/bn_act.cu',
+    'csrc/kernels/pool.cu',
     'csrc/device/symm.cu',
 ]
 HOST_LIB_DIRS = ['csrc/core', 'csrc/ctrl', 'csrc/elastic', 'csrc/capi']

@@ -98,7 +98,8 @@ class ResNet(nn.Module):
         self.fused_bn = fused_bn
         self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
         self.bn1 = BNAct(64, relu=True, fused=fused_bn)
-        self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
+        from ..ops.pool import MaxPool3x3s2
+        self.maxpool = MaxPool3x3s2(fused=fused_bn)
         self.layer1 = self._make_layer(block, 64, layers[0])
         self.layer2 = self._make_layer(block, 128, layers[1], stride=2)
         self.layer3 = self._make_layer(block, 256, layers[2], stride=2)

@@ -37,6 +37,8 @@ class _BNAct(torch.autograd.Function):
         floats = K.lib().kfb_bn_scratch_floats(rows, Cc)
         # scratch is private to this call: the backward of another layer may run concurrently on another stream
         scratch = torch.empty(floats, dtype=torch.float32, device=x.device)
+        # one bit per element (y > 0): the backward reads this instead of y
+        mask = torch.empty(rows * (Cc // 8), dtype=torch.uint8, device=x.device) if relu else None
         if residual is not None and not residual.is_contiguous(memory_format=torch.channels_last):
             residual = residual.contiguous(memory_format=torch.channels_last)
         K.call('kfb_bn_act_fwd', x.data_ptr(), residual.data_ptr() if residual is not None else None,
@@ -46,8 +48,9 @@ class _BNAct(torch.autograd.Function):
                (running_mean.data_ptr() if running_mean is not None else None),
                running_var.data_ptr() if running_var is not None else None,
                save_mean.data_ptr(), save_invstd.data_ptr(), rows, Cc, float(eps), float(momentum),
-               1 if relu else 0, 1 if training else 0, K.dtype_code(x.dtype), scratch.data_ptr(), K.stream_ptr())
-        ctx.save_for_backward(x, y if relu else None, weight, save_mean, save_invstd)
+               1 if relu else 0, 1 if training else 0, K.dtype_code(x.dtype), scratch.data_ptr(),
+               mask.data_ptr() if mask is not None else None, K.stream_ptr())
+        ctx.save_for_backward(x, mask, weight, save_mean, save_invstd)
         ctx.relu = relu
         ctx.has_res = residual is not None
         ctx.training = training
@@ -55,7 +58,7 @@ class _BNAct(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, weight, save_mean, save_invstd = ctx.saved_tensors
+        x, mask, weight, save_mean, save_invstd = ctx.saved_tensors
         N, Cc, H, W = x.shape
         rows = N * H * W
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -65,7 +68,7 @@ class _BNAct(torch.autograd.Function):
         dweight = torch.empty(Cc, dtype=torch.float32, device=x.device)
         dbias = torch.empty(Cc, dtype=torch.float32, device=x.device)
         scratch = torch.empty(K.lib().kfb_bn_scratch_floats(rows, Cc), dtype=torch.float32, device=x.device)
-        K.call('kfb_bn_act_bwd', dy.data_ptr(), x.data_ptr(), y.data_ptr() if y is not None else None,
+        K.call('kfb_bn_act_bwd', dy.data_ptr(), x.data_ptr(), mask.data_ptr() if mask is not None else None,
                weight.data_ptr() if weight is not None else None, save_mean.data_ptr(), save_invstd.data_ptr(),
                dx.data_ptr(), dres.data_ptr() if dres is not None else None, dweight.data_ptr(), dbias.data_ptr(),
                rows, Cc, 1 if ctx.relu else 0, K.dtype_code(x.dtype), scratch.data_ptr(), K.stream_ptr())

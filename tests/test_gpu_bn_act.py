@@ -95,3 +95,19 @@ def test_resnet_fused_matches_unfused():
         ga = dict(a.named_parameters())[n].grad.float()
         gb = dict(b.named_parameters())[n].grad.float()
         assert float((ga - gb).norm() / ga.norm()) < 0.15, n
+
+
+@pytest.mark.parametrize('shape', [(4, 64, 56, 56), (2, 8, 7, 9), (3, 16, 112, 112), (2, 32, 5, 4)])
+def test_maxpool3x3s2(shape):
+    from kungfu_b200.ops.pool import max_pool_3x3s2
+    torch.manual_seed(0)
+    x = torch.randn(shape, device='cuda').bfloat16().contiguous(memory_format=torch.channels_last)
+    xa = x.clone().requires_grad_()
+    xr = x.float().requires_grad_()
+    y = max_pool_3x3s2(xa)
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    assert y.shape == yr.shape and torch.equal(y.float(), yr)
+    dy = torch.randn_like(yr)
+    y.backward(dy.bfloat16())
+    yr.backward(dy.bfloat16().float())
+    assert torch.allclose(xa.grad.float(), xr.grad, rtol=1e-2, atol=1e-2)
