@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(BN_THREADS)
 
 // Partials are combined by CTAs of 32 channels x 8 slices: coalesced 128-byte
 // reads, 8-way parallel over the partial blocks, fp64, fixed order.
-constexpr int FIN_TX = 32, FIN_TY = 8;
+constexpr int FIN_TX = 32, FIN_TY = 32;
 __device__ __forceinline__ bool
 reduce_partials(const float *__restrict__ partial, int nblocks, int C, double *s_out, double *q_out)
 {
@@ -102,6 +102,7 @@ reduce_partials(const float *__restrict__ partial, int nblocks, int C, double *s
     const int c  = blockIdx.x * FIN_TX + tx;
     double s = 0.0, q = 0.0;
     if (c < C) {
+#pragma unroll 4
         for (int b = ty; b < nblocks; b += FIN_TY) {
             s += (double)partial[(size_t)b * 2 * C + c];
             q += (double)partial[(size_t)b * 2 * C + C + c];

@@ -148,3 +148,90 @@ extern "C" int kfb_maxpool3x3s2_bwd(const void *dy, const void *idx, void *dx, i
     KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
+
+// ---- global average pooling (N,H,W,C) -> (N,C), and its broadcast backward ----
+namespace kfb {
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_gap_fwd(const uint4 *__restrict__ x, uint4 *__restrict__ y, int N, int HW, int C8)
+{
+    // one thread per (n, c8): HW is small (49 for ResNet), consecutive threads read consecutive packets
+    const long long total = (long long)N * C8;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C8);
+        const long long n = i / C8;
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        for (int p = 0; p < HW; ++p) {
+            float v[8];
+            Pack<T>::unpack(ld_stream16(x + (n * HW + p) * C8 + c), v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        }
+        const float inv = 1.f / (float)HW;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] *= inv;
+        st_stream16(y + i, Pack<T>::pack(acc));
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_gap_bwd(const uint4 *__restrict__ dy, uint4 *__restrict__ dx, int N, int HW, int C8)
+{
+    const long long total = (long long)N * HW * C8;
+    const float inv       = 1.f / (float)HW;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c       = (int)(i % C8);
+        const long long n = i / ((long long)HW * C8);
+        float v[8];
+        Pack<T>::unpack(__ldg(dy + n * C8 + c), v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] *= inv;
+        st_stream16(dx + i, Pack<T>::pack(v));
+    }
+}
+
+}  // namespace kfb
+
+extern "C" int kfb_gap_fwd(const void *x, void *y, int N, int HW, int C, int dtype, void *stream)
+{
+    if (C % 8) {
+        kfb::set_last_error("global avg pool: channels must be a multiple of 8");
+        return KFB_ERR_UNSUPP;
+    }
+    const long long total = (long long)N * (C / 8);
+    const int blocks      = (int)std::min<long long>((total + 255) / 256, 148LL * 8);
+    cudaStream_t s        = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == KFB_BF16) kfb::k_gap_fwd<__nv_bfloat16><<<blocks, 256, 0, s>>>((const uint4 *)x, (uint4 *)y, N, HW, C / 8);
+    else if (dtype == KFB_F16) kfb::k_gap_fwd<__half><<<blocks, 256, 0, s>>>((const uint4 *)x, (uint4 *)y, N, HW, C / 8);
+    else {
+        kfb::set_last_error("global avg pool supports bf16 / f16");
+        return KFB_ERR_UNSUPP;
+    }
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+extern "C" int kfb_gap_bwd(const void *dy, void *dx, int N, int HW, int C, int dtype, void *stream)
+{
+    if (C % 8) {
+        kfb::set_last_error("global avg pool: channels must be a multiple of 8");
+        return KFB_ERR_UNSUPP;
+    }
+    const long long total = (long long)N * HW * (C / 8);
+    const int blocks      = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
+    cudaStream_t s        = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == KFB_BF16) kfb::k_gap_bwd<__nv_bfloat16><<<blocks, 256, 0, s>>>((const uint4 *)dy, (uint4 *)dx, N, HW, C / 8);
+    else if (dtype == KFB_F16) kfb::k_gap_bwd<__half><<<blocks, 256, 0, s>>>((const uint4 *)dy, (uint4 *)dx, N, HW, C / 8);
+    else {
+        kfb::set_last_error("global avg pool supports bf16 / f16");
+        return KFB_ERR_UNSUPP;
+    }
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}

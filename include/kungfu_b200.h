@@ -283,6 +283,13 @@ int kfb_maxpool3x3s2_fwd(const void *x, void *y, void *idx, int N, int H, int W,
 int kfb_maxpool3x3s2_bwd(const void *dy, const void *idx, void *dx, int N, int H,
                          int W, int C, int dtype, void *stream);
 
+/* Global average pooling (N,H,W,C)->(N,C), NHWC bf16/f16, and its backward
+ * (broadcast of dy/HW) written directly in channels-last layout. */
+int kfb_gap_fwd(const void *x, void *y, int N, int HW, int C, int dtype,
+                void *stream);
+int kfb_gap_bwd(const void *dy, void *dx, int N, int HW, int C, int dtype,
+                void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -129,7 +129,11 @@ class ResNet(nn.Module):
     def forward(self, x):
         x = self.maxpool(self.bn1(self.conv1(x)))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
-        x = torch.flatten(self.avgpool(x), 1)
+        if self.fused_bn:
+            from ..ops.pool import global_avg_pool
+            x = global_avg_pool(x)
+        else:
+            x = torch.flatten(self.avgpool(x), 1)
         return self.fc(x)
 
 

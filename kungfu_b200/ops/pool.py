@@ -51,3 +51,32 @@ class MaxPool3x3s2(torch.nn.Module):
 
     def forward(self, x):
         return max_pool_3x3s2(x) if self.fused else F.max_pool2d(x, 3, 2, 1)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    """(N,C,H,W) channels-last -> (N,C); the backward writes a channels-last
+    gradient directly (PyTorch's produces an NCHW expand that then has to be
+    re-laid out by a slow strided copy)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        N, Cc, H, W = x.shape
+        y = torch.empty((N, Cc), dtype=x.dtype, device=x.device)
+        K.call('kfb_gap_fwd', x.data_ptr(), y.data_ptr(), N, H * W, Cc, K.dtype_code(x.dtype), K.stream_ptr())
+        ctx.shape = (N, Cc, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, Cc, H, W = ctx.shape
+        dy = dy.contiguous()
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        K.call('kfb_gap_bwd', dy.data_ptr(), dx.data_ptr(), N, H * W, Cc, K.dtype_code(dy.dtype), K.stream_ptr())
+        return dx
+
+
+def global_avg_pool(x):
+    """Flattened global average pool: (N,C,H,W) -> (N,C)."""
+    if supported(x):
+        return _GlobalAvgPool.apply(x)
+    return torch.flatten(F.adaptive_avg_pool2d(x, (1, 1)), 1)
