@@ -14,7 +14,10 @@
 // (one 16-byte packet) and walks rows, so its per-channel scale/shift stay in
 // registers. Channel sums are reduced block-wise in shared memory, written as
 // per-block partials and combined in fp64 in a fixed order (deterministic).
+#include <algorithm>
 #include <cstring>
+#include <map>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -359,6 +362,27 @@ static int bn_grid(long long rows, int C)
     return (int)blocks;
 }
 
+// Grid = at most one resident wave (SMs x CTAs/SM): rows are walked grid-stride,
+// so a partial second wave would only add a tail.
+template <typename Kern> static int one_wave(Kern kern, size_t smem)
+{
+    static std::mutex mu;
+    static std::map<const void *, int> cache;
+    const void *key = reinterpret_cast<const void *>(kern);
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    int dev = 0, sms = 148, occ = 1;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, BN_THREADS, smem) != cudaSuccess || occ < 1) occ = 1;
+    if (occ > 4) occ = 4;
+    int g = sms * occ;
+    if (g > BN_MAX_BLOCKS) g = BN_MAX_BLOCKS;
+    cache[key] = g;
+    return g;
+}
+
 static int bn_check(long long rows, int C)
 {
     if (C % 8 || C < 8 || (C >> 3) > BN_THREADS || rows < 1) {
@@ -389,9 +413,10 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
     const int RY   = BN_THREADS / (C >> 3);
     if (training) {
         const size_t smem = (size_t)RY * C * sizeof(float);
-        k_bn_stats<T><<<grid, BN_THREADS, smem, s>>>(reinterpret_cast<const uint4 *>(x), rows, C, scratch);
+        const int gs      = std::min(grid, one_wave(k_bn_stats<T>, smem));
+        k_bn_stats<T><<<gs, BN_THREADS, smem, s>>>(reinterpret_cast<const uint4 *>(x), rows, C, scratch);
         KFB_CUDA_OK(cudaGetLastError());
-        k_bn_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, grid, C, rows, eps, momentum, running_mean,
+        k_bn_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, gs, C, rows, eps, momentum, running_mean,
                                                        running_var, save_mean, save_invstd);
     } else {
         k_bn_eval_prep<<<(C + 127) / 128, 128, 0, s>>>(running_mean, running_var, C, eps, save_mean, save_invstd);
@@ -400,7 +425,7 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
     const uint4 *xp = reinterpret_cast<const uint4 *>(x), *rp = reinterpret_cast<const uint4 *>(residual);
     uint4 *yp       = reinterpret_cast<uint4 *>(y);
 #define KFB_BN_APPLY(R, S)                                                                                  \
-    k_bn_apply<T, R, S><<<grid, BN_THREADS, 0, s>>>(xp, rp, yp, weight, bias, save_mean, save_invstd, rows, C, mask)
+    k_bn_apply<T, R, S><<<std::min(grid, one_wave(k_bn_apply<T, R, S>, 0)), BN_THREADS, 0, s>>>(xp, rp, yp, weight, bias, save_mean, save_invstd, rows, C, mask)
     if (relu && residual) KFB_BN_APPLY(true, true);
     else if (relu) KFB_BN_APPLY(true, false);
     else if (residual) KFB_BN_APPLY(false, true);
@@ -441,16 +466,17 @@ static int bn_bwd_t(const void *dy, const void *x, const void *mask, const float
     const uint4 *gp = reinterpret_cast<const uint4 *>(dy), *xp = reinterpret_cast<const uint4 *>(x)
                 ;
     const uint8_t *yp = reinterpret_cast<const uint8_t *>(mask);
+    const int gs = std::min(grid, relu ? one_wave(k_bn_bwd_stats<T, true>, smem) : one_wave(k_bn_bwd_stats<T, false>, smem));
     if (relu)
-        k_bn_bwd_stats<T, true><<<grid, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
+        k_bn_bwd_stats<T, true><<<gs, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
     else
-        k_bn_bwd_stats<T, false><<<grid, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
+        k_bn_bwd_stats<T, false><<<gs, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);
     KFB_CUDA_OK(cudaGetLastError());
-    k_bn_bwd_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, grid, C, dweight, dbias, sums);
+    k_bn_bwd_finalize<<<(C + FIN_TX - 1) / FIN_TX, FIN_TX * FIN_TY, 0, s>>>(scratch, gs, C, dweight, dbias, sums);
     KFB_CUDA_OK(cudaGetLastError());
     uint4 *dxp = reinterpret_cast<uint4 *>(dx), *drp = reinterpret_cast<uint4 *>(dres);
 #define KFB_BN_BWD(R, S)                                                                                    \
-    k_bn_bwd_apply<T, R, S><<<grid, BN_THREADS, 0, s>>>(gp, xp, yp, weight, save_mean, save_invstd, sums, dxp, drp, rows, C)
+    k_bn_bwd_apply<T, R, S><<<std::min(grid, one_wave(k_bn_bwd_apply<T, R, S>, 0)), BN_THREADS, 0, s>>>(gp, xp, yp, weight, save_mean, save_invstd, sums, dxp, drp, rows, C)
     if (relu && dres) KFB_BN_BWD(true, true);
     else if (relu) KFB_BN_BWD(true, false);
     else if (dres) KFB_BN_BWD(false, true);

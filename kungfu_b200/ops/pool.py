@@ -16,7 +16,7 @@ class _MaxPool3x3s2(torch.autograd.Function):
     def forward(ctx, x):
         N, Cc, H, W = x.shape
         OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
-        y = torch.empty((N, Cc, OH, OW), dtype=x.dtype, device=x.device).contiguous(memory_format=torch.channels_last)
+        y = torch.empty((N, Cc, OH, OW), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
         idx = torch.empty(N * OH * OW * Cc, dtype=torch.uint8, device=x.device)
         K.call('kfb_maxpool3x3s2_fwd', x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, Cc,
                K.dtype_code(x.dtype), K.stream_ptr())
@@ -30,7 +30,7 @@ class _MaxPool3x3s2(torch.autograd.Function):
         N, Cc, H, W = ctx.shape
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
         K.call('kfb_maxpool3x3s2_bwd', dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc,
                K.dtype_code(dy.dtype), K.stream_ptr())
         return dx
@@ -70,7 +70,7 @@ class _GlobalAvgPool(torch.autograd.Function):
     def backward(ctx, dy):
         N, Cc, H, W = ctx.shape
         dy = dy.contiguous()
-        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device).contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=torch.channels_last)
         K.call('kfb_gap_bwd', dy.data_ptr(), dx.data_ptr(), N, H * W, Cc, K.dtype_code(dy.dtype), K.stream_ptr())
         return dx
 
