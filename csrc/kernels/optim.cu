@@ -18,6 +18,7 @@
 // All flat buffers are processed in packets of 8 elements; the arenas that own
 // them pad every tensor to a multiple of 16 elements.
 #include <cstring>
+#include <mutex>
 #include <type_traits>
 
 #include "common.cuh"
@@ -675,6 +676,92 @@ extern "C" int kfb_fuse(void *const *srcs, const int64_t *counts,
             KFB_CUDA_OK(cudaGetLastError());
         }
         first = false;
+    }
+    return KFB_OK;
+}
+
+// ---- kfb_fuse for callers that must not allocate ------------------------------------
+//
+// Some users of this library cannot hand us a scratch buffer because they
+// cannot obtain one at the point of the call: a plugin running inside another
+// framework's step after that framework has claimed all device memory for its
+// own planner, a hook invoked from a latency-critical loop where a
+// cudaMalloc (a device-wide synchronising call) is forbidden, or a host
+// thread that is not allowed to touch the allocator at all. For them the
+// block partials of the norm live in this file-scope device array instead of
+// a caller buffer. It is part of the library image: every GPU that loads the
+// library holds these 64 KiB until the process exits.
+#define KFB_FUSE_NOALLOC_SLOTS 16
+static __device__ __align__(256) float g_fuse_noalloc_scratch[KFB_FUSE_NOALLOC_MAX_TENSORS * KFB_FUSE_NOALLOC_SLOTS];
+
+// In host code the array's name is only a handle for the runtime, not a
+// device address; the address each device uses is looked up once per device.
+static float *g_fuse_noalloc_ptr[64];
+static std::mutex g_fuse_noalloc_mu;
+
+static int fuse_noalloc_scratch(float **out)
+{
+    int dev = 0;
+    KFB_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_last_error("kfb_fuse_noalloc: device ordinal %d out of range", dev);
+        return KFB_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_fuse_noalloc_mu);
+    if (!g_fuse_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        KFB_CUDA_OK(cudaGetSymbolAddress(&p, g_fuse_noalloc_scratch));
+        g_fuse_noalloc_ptr[dev] = static_cast<float *>(p);
+    }
+    *out = g_fuse_noalloc_ptr[dev];
+    return KFB_OK;
+}
+
+extern "C" int kfb_fuse_noalloc(void *const *srcs, const int64_t *counts,
+                                const int64_t *dst_offs, int n, int src_dtype,
+                                void *dst, int dst_dtype, float *sumsq_out,
+                                void *stream)
+{
+    if (n < 0 || n > KFB_FUSE_NOALLOC_MAX_TENSORS) {
+        set_last_error("kfb_fuse_noalloc: %d tensors exceed the built-in scratch (max %d per call); "
+                       "split the call or use kfb_fuse with your own scratch",
+                       n, KFB_FUSE_NOALLOC_MAX_TENSORS);
+        return KFB_ERR_ARG;
+    }
+    float *scratch = nullptr;
+    if (sumsq_out) {
+        // First call on a device resolves the array's address (may load the
+        // module): make that call before any stream capture begins.
+        int rc = fuse_noalloc_scratch(&scratch);
+        if (rc) return rc;
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    constexpr int BX = KFB_FUSE_NOALLOC_SLOTS;
+    for (int base = 0; base < n; base += KFB_FUSE_MAX) {
+        FuseArgs a;
+        memset(&a, 0, sizeof(a));
+        a.n = std::min(KFB_FUSE_MAX, n - base);
+        for (int i = 0; i < a.n; ++i) {
+            a.src[i]   = srcs[base + i];
+            a.count[i] = counts[base + i];
+            a.off[i]   = dst_offs[base + i];
+        }
+        // every launched CTA stores its slot (zero included), so nothing in
+        // the shared array needs clearing between calls
+        float *partials = scratch ? scratch + (size_t)base * BX : nullptr;
+        dim3 grid(BX, a.n);
+        KFB_DISPATCH_FLOAT(src_dtype, S,
+            KFB_DISPATCH_FLOAT(dst_dtype, D,
+                (k_fuse<S, D, false><<<grid, 256, 0, s>>>(a, dst, partials))));
+        KFB_CUDA_OK(cudaGetLastError());
+    }
+    if (sumsq_out) {
+        if (n == 0) {
+            KFB_CUDA_OK(cudaMemsetAsync(sumsq_out, 0, sizeof(float), s));
+        } else {
+            k_sum_slots<<<1, 256, 0, s>>>(scratch, BX * n, sumsq_out, 0);
+            KFB_CUDA_OK(cudaGetLastError());
+        }
     }
     return KFB_OK;
 }

@@ -137,6 +137,27 @@ int kfb_edge_copy(void *dst, const void *src, int64_t bytes, int blocks,
 int kfb_fuse(void *const *srcs, const int64_t *counts, const int64_t *dst_offs,
              int n, int src_dtype, void *dst, int dst_dtype, float *sumsq_out,
              float *scratch, void *stream);
+/* kfb_fuse without a caller-supplied scratch buffer, for callers that cannot
+ * allocate device memory where they call us (code running inside another
+ * framework's memory-planned step, latency-critical hooks where cudaMalloc's
+ * device-wide synchronisation is not acceptable, threads barred from the
+ * allocator). This entry point has no counterpart in the reference. The block
+ * partials of the norm live in a static device array inside the library
+ * (64 KiB per GPU that loads it, held until exit), so:
+ *  - n <= KFB_FUSE_NOALLOC_MAX_TENSORS per call, larger n is rejected;
+ *  - it never calls cudaMalloc/cudaFree or any allocating routine;
+ *  - the first call on a device looks the array's address up
+ *    (cudaGetSymbolAddress) - issue that call before any stream capture;
+ *  - all calls on a device share the array: two calls whose kernels can
+ *    overlap on the GPU (different streams, no ordering) race on it; calls
+ *    ordered on one stream are fine. Nothing in it needs clearing: every slot
+ *    that is read was written by the same call.
+ * Inputs, outputs and semantics are those of kfb_fuse; the norm is summed in
+ * one fixed order (equal to kfb_fuse within fp32 rounding). */
+#define KFB_FUSE_NOALLOC_MAX_TENSORS 1024
+int kfb_fuse_noalloc(void *const *srcs, const int64_t *counts,
+                     const int64_t *dst_offs, int n, int src_dtype, void *dst,
+                     int dst_dtype, float *sumsq_out, void *stream);
 /* Inverse: scatter flat buffer back into n tensors (cast dst_dtype<-src). */
 int kfb_defuse(const void *src, int src_dtype, void *const *dsts,
                const int64_t *counts, const int64_t *src_offs, int n,
