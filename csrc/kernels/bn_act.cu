@@ -154,6 +154,9 @@ __global__ void k_bn_eval_prep(const float *running_mean, const float *running_v
     save_invstd[c] = rsqrtf(running_var[c] + eps);
 }
 
+// The apply passes walk the rows from the END: the statistics pass that ran
+// just before swept them front to back, so the tail of the tensor is what the
+// 126 MB L2 still holds.
 template <typename T, bool RELU, bool RES>
 __global__ void __launch_bounds__(BN_THREADS)
     k_bn_apply(const uint4 *__restrict__ x, const uint4 *__restrict__ res, uint4 *__restrict__ y,
@@ -178,8 +181,8 @@ __global__ void __launch_bounds__(BN_THREADS)
         float v[4][8], r[4][8];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            Ld8<T>::load(x + (row + u * stride) * C8 + tx, v[u]);
-            if (RES) Ld8<T>::load(res + (row + u * stride) * C8 + tx, r[u]);
+            Ld8<T>::load(x + (rows - 1 - (row + u * stride)) * C8 + tx, v[u]);
+            if (RES) Ld8<T>::load(res + (rows - 1 - (row + u * stride)) * C8 + tx, r[u]);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -194,14 +197,14 @@ __global__ void __launch_bounds__(BN_THREADS)
                 }
                 v[u][k] = o;
             }
-            Ld8<T>::store(y + (row + u * stride) * C8 + tx, v[u]);
-            if (RELU && mask) mask[(row + u * stride) * C8 + tx] = (uint8_t)bits;
+            Ld8<T>::store(y + (rows - 1 - (row + u * stride)) * C8 + tx, v[u]);
+            if (RELU && mask) mask[(rows - 1 - (row + u * stride)) * C8 + tx] = (uint8_t)bits;
         }
     }
     for (; row < rows; row += stride) {
         float v[8], r[8];
-        Ld8<T>::load(x + row * C8 + tx, v);
-        if (RES) Ld8<T>::load(res + row * C8 + tx, r);
+        Ld8<T>::load(x + (rows - 1 - row) * C8 + tx, v);
+        if (RES) Ld8<T>::load(res + (rows - 1 - row) * C8 + tx, r);
         unsigned bits = 0;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -213,8 +216,8 @@ __global__ void __launch_bounds__(BN_THREADS)
             }
             v[k] = o;
         }
-        Ld8<T>::store(y + row * C8 + tx, v);
-        if (RELU && mask) mask[row * C8 + tx] = (uint8_t)bits;
+        Ld8<T>::store(y + (rows - 1 - row) * C8 + tx, v);
+        if (RELU && mask) mask[(rows - 1 - row) * C8 + tx] = (uint8_t)bits;
     }
 }
 
@@ -318,9 +321,9 @@ __global__ void __launch_bounds__(BN_THREADS)
             unsigned o[2] = {0xffu, 0xffu};
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-            Ld8<T>::load(dy + (row + u * stride) * C8 + tx, g[u]);
-            Ld8<T>::load(x + (row + u * stride) * C8 + tx, v[u]);
-            if (RELU) o[u] = mask[(row + u * stride) * C8 + tx];
+            Ld8<T>::load(dy + (rows - 1 - (row + u * stride)) * C8 + tx, g[u]);
+            Ld8<T>::load(x + (rows - 1 - (row + u * stride)) * C8 + tx, v[u]);
+            if (RELU) o[u] = mask[(rows - 1 - (row + u * stride)) * C8 + tx];
         }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
@@ -331,16 +334,16 @@ __global__ void __launch_bounds__(BN_THREADS)
                 g[u][k]          = dz;
                 v[u][k]          = sc[k] * (dz - a[k] - xhat * b[k]);
             }
-            Ld8<T>::store(dx + (row + u * stride) * C8 + tx, v[u]);
-            if (RES) Ld8<T>::store(dres + (row + u * stride) * C8 + tx, g[u]);
+            Ld8<T>::store(dx + (rows - 1 - (row + u * stride)) * C8 + tx, v[u]);
+            if (RES) Ld8<T>::store(dres + (rows - 1 - (row + u * stride)) * C8 + tx, g[u]);
         }
     }
     for (; row < rows; row += stride) {
         float g[8], v[8];
             unsigned o = 0xffu;
-        Ld8<T>::load(dy + row * C8 + tx, g);
-        Ld8<T>::load(x + row * C8 + tx, v);
-        if (RELU) o = mask[row * C8 + tx];
+        Ld8<T>::load(dy + (rows - 1 - row) * C8 + tx, g);
+        Ld8<T>::load(x + (rows - 1 - row) * C8 + tx, v);
+        if (RELU) o = mask[(rows - 1 - row) * C8 + tx];
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             const float dz   = (RELU && !((o >> k) & 1u)) ? 0.f : g[k];
@@ -348,8 +351,8 @@ __global__ void __launch_bounds__(BN_THREADS)
             g[k]             = dz;
             v[k]             = sc[k] * (dz - a[k] - xhat * b[k]);
         }
-        Ld8<T>::store(dx + row * C8 + tx, v);
-        if (RES) Ld8<T>::store(dres + row * C8 + tx, g);
+        Ld8<T>::store(dx + (rows - 1 - row) * C8 + tx, v);
+        if (RES) Ld8<T>::store(dres + (rows - 1 - row) * C8 + tx, g);
     }
 }
 
