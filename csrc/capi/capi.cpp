@@ -265,6 +265,16 @@ int kf_send_fd(kf_peer *p, int target_rank, const char *tag, int fd)
 
 int kf_recv_fd(kf_peer *p, int src_rank, const char *tag, int *fd) { return done(p, p->peer->recv_fd(src_rank, tag, fd)); }
 
+int kf_current_strategies(kf_peer *p, char *out, int cap)
+{
+    return copy_out(p->peer->session()->strategies_text(), out, cap);
+}
+
+int kf_current_strategy_name(kf_peer *p, char *out, int cap)
+{
+    return copy_out(strategy_name(p->peer->session()->strategy()), out, cap);
+}
+
 // ---- planner utilities ---------------------------------------------------------------
 int kf_gen_strategy_graphs(const char *peers_csv, const char *strategy, char *out, int cap)
 {

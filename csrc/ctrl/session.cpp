@@ -379,6 +379,13 @@ bool Session::check_interference()
     return total > size() / 2;
 }
 
+std::string Session::strategies_text() const
+{
+    std::string text;
+    for (auto &sg : global_) text += "reduce=" + sg.reduce.debug_string() + " bcast=" + sg.bcast.debug_string() + "\n";
+    return text;
+}
+
 std::vector<float> Session::peer_latencies()
 {
     std::vector<float> out(size(), 0.f);

@@ -84,6 +84,9 @@ class Session
     bool set_tree(const std::vector<int32_t> &forest);
     bool set_strategy(Strategy s);
     int num_strategies() const { return (int)global_.size(); }
+    // text form of the active global strategies, one "reduce=... bcast=..." line each
+    std::string strategies_text() const;
+    Strategy strategy() const { return strategy_; }
     void calc_stats();
     void log_stats();
     void print_strategy_stats();

@@ -62,6 +62,9 @@ int kf_propose_new_size(kf_peer *p, int new_size);
 /* adaptation / monitoring */
 int kf_set_tree(kf_peer *p, const int32_t *forest, int n);
 int kf_set_strategy(kf_peer *p, const char *name);
+/* active global strategies as text, one "reduce=[n]{(i)(i->j)...} bcast=[n]{...}" line per graph pair */
+int kf_current_strategies(kf_peer *p, char *out, int cap);
+int kf_current_strategy_name(kf_peer *p, char *out, int cap);
 int kf_calc_stats(kf_peer *p);
 int kf_log_stats(kf_peer *p);
 int kf_print_strategy_stats(kf_peer *p);

@@ -87,6 +87,8 @@ def _declare(l):
     f('kf_propose_new_size', C.c_int, _VP, C.c_int)
     f('kf_set_tree', C.c_int, _VP, C.POINTER(C.c_int32), C.c_int)
     f('kf_set_strategy', C.c_int, _VP, C.c_char_p)
+    f('kf_current_strategies', C.c_int, _VP, C.c_char_p, C.c_int)
+    f('kf_current_strategy_name', C.c_int, _VP, C.c_char_p, C.c_int)
     f('kf_get_peer_latencies', C.c_int, _VP, C.POINTER(C.c_float), C.c_int)
     f('kf_egress_rates', C.c_int, _VP, C.POINTER(C.c_float), C.c_int)
     f('kf_send_fd', C.c_int, _VP, C.c_int, C.c_char_p, C.c_int)
@@ -256,6 +258,26 @@ class Peer(object):
 
     def set_strategy(self, name):
         _check(lib().kf_set_strategy(self._h, name.encode()), 'set_strategy')
+
+    def strategies(self):
+        """Active (reduce, bcast) graph pairs: list of dicts with 'loops' (set of
+        ranks that reduce), 'reduce' and 'bcast' edge lists."""
+        import re
+        buf = C.create_string_buffer(1 << 20)
+        if lib().kf_current_strategies(self._h, buf, len(buf)) < 0:
+            raise KungFuHostError(lib().kf_last_error().decode())
+        out = []
+        for line in buf.value.decode().strip().split('\n'):
+            red, bc = line.split(' bcast=')
+            edges = lambda t: [(int(a), int(b)) for a, b in re.findall(r'\((\d+)->(\d+)\)', t)]
+            out.append({'loops': set(int(a) for a in re.findall(r'\((\d+)\)', red)),
+                        'reduce': edges(red), 'bcast': edges(bc)})
+        return out
+
+    def strategy_name(self):
+        buf = C.create_string_buffer(64)
+        lib().kf_current_strategy_name(self._h, buf, 64)
+        return buf.value.decode()
 
     def peer_latencies(self):
         n = self.size()

@@ -1,0 +1,94 @@
+"""BERT (base / large) for masked-LM + next-sentence pre-training.
+
+BASELINE.json config 4: BERT-base pre-training with PairAveragingOptimizer.
+The reference only knows BERT as a list of gradient sizes
+(/root/reference/srcs/python/kungfu/tensorflow/v1/benchmarks/model_sizes.py:27-81);
+this is the architecture itself, bf16-friendly, attention through
+torch.nn.functional.scaled_dot_product_attention (library flash kernels: model
+math stays a library call, like in the reference)."""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class BertConfig(object):
+    def __init__(self, vocab_size=30522, hidden=768, layers=12, heads=12, intermediate=3072, max_pos=512,
+                 type_vocab=2, dropout=0.1, eps=1e-12):
+        self.vocab_size, self.hidden, self.layers, self.heads = vocab_size, hidden, layers, heads
+        self.intermediate, self.max_pos, self.type_vocab, self.dropout, self.eps = intermediate, max_pos, type_vocab, dropout, eps
+
+
+class _Layer(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.heads = c.heads
+        self.qkv = nn.Linear(c.hidden, 3 * c.hidden)
+        self.proj = nn.Linear(c.hidden, c.hidden)
+        self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.fc1 = nn.Linear(c.hidden, c.intermediate)
+        self.fc2 = nn.Linear(c.intermediate, c.hidden)
+        self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.drop = c.dropout
+
+    def forward(self, x, mask=None):
+        B, S, H = x.shape
+        q, k, v = self.qkv(x).view(B, S, 3, self.heads, H // self.heads).permute(2, 0, 3, 1, 4)
+        a = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=self.drop if self.training else 0.0)
+        a = a.transpose(1, 2).reshape(B, S, H)
+        x = self.ln1(x + F.dropout(self.proj(a), self.drop, self.training))
+        h = self.fc2(F.gelu(self.fc1(x)))
+        return self.ln2(x + F.dropout(h, self.drop, self.training))
+
+
+class BertForPreTraining(nn.Module):
+    def __init__(self, config=None):
+        super().__init__()
+        c = config or BertConfig()
+        self.config = c
+        self.tok = nn.Embedding(c.vocab_size, c.hidden)
+        self.pos = nn.Embedding(c.max_pos, c.hidden)
+        self.typ = nn.Embedding(c.type_vocab, c.hidden)
+        self.ln = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.layers = nn.ModuleList([_Layer(c) for _ in range(c.layers)])
+        self.pooler = nn.Linear(c.hidden, c.hidden)
+        self.mlm_dense = nn.Linear(c.hidden, c.hidden)
+        self.mlm_ln = nn.LayerNorm(c.hidden, eps=c.eps)
+        self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_size))
+        self.nsp = nn.Linear(c.hidden, 2)
+        self.apply(self._init)
+
+    @staticmethod
+    def _init(m):
+        if isinstance(m, (nn.Linear, nn.Embedding)):
+            nn.init.normal_(m.weight, std=0.02)
+        if isinstance(m, nn.Linear) and m.bias is not None:
+            nn.init.zeros_(m.bias)
+
+    def forward(self, ids, token_type=None, mlm_labels=None, nsp_labels=None):
+        B, S = ids.shape
+        pos = torch.arange(S, device=ids.device).unsqueeze(0)
+        x = self.tok(ids) + self.pos(pos) + self.typ(token_type if token_type is not None else torch.zeros_like(ids))
+        x = F.dropout(self.ln(x), self.config.dropout, self.training)
+        for layer in self.layers:
+            x = layer(x)
+        h = self.mlm_ln(F.gelu(self.mlm_dense(x)))
+        logits = F.linear(h, self.tok.weight, self.mlm_bias.to(h.dtype))  # tied decoder
+        pooled = torch.tanh(self.pooler(x[:, 0]))
+        nsp_logits = self.nsp(pooled)
+        if mlm_labels is None:
+            return logits, nsp_logits
+        loss = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1), ignore_index=-100)
+        if nsp_labels is not None:
+            loss = loss + F.cross_entropy(nsp_logits.float(), nsp_labels)
+        return loss
+
+
+def bert_base(**kw):
+    return BertForPreTraining(BertConfig(**kw))
+
+
+def bert_large(**kw):
+    kw = dict(dict(hidden=1024, layers=24, heads=16, intermediate=4096), **kw)
+    return BertForPreTraining(BertConfig(**kw))

@@ -18,11 +18,18 @@ _ESIZE = {K.F32: 4, K.BF16: 2, K.F16: 2, K.I32: 4, K.F64: 8, K.I64: 8, K.U8: 1}
 ONESHOT_MAX_BYTES = 256 << 10
 
 
+# large-message variant installed by parallel.planner.VariantChooser (None = built-in preference)
+PREFERRED_LARGE = None
+
+
 def choose_algo(comm, nbytes, buf=None, op=K.OP_SUM, dtype=K.F32):
     if comm.np == 1:
         return K.ALGO_ONESHOT
-    if (buf is not None and buf.mc_ptr and op == K.OP_SUM and dtype in (K.F32, K.BF16, K.F16)
-            and nbytes > ONESHOT_MAX_BYTES):
+    nvls_ok = (buf is not None and buf.mc_ptr and op == K.OP_SUM and dtype in (K.F32, K.BF16, K.F16))
+    if nbytes > ONESHOT_MAX_BYTES and PREFERRED_LARGE is not None:
+        if PREFERRED_LARGE != K.ALGO_NVLS or nvls_ok:
+            return PREFERRED_LARGE
+    if nvls_ok and nbytes > ONESHOT_MAX_BYTES:
         return K.ALGO_NVLS
     return K.ALGO_ONESHOT if nbytes <= ONESHOT_MAX_BYTES else K.ALGO_TWOSHOT
 

@@ -200,8 +200,43 @@ def check_fused_optimizers():
         print('monitors ok', flush=True)
 
 
+def check_planner():
+    """Strategy graphs executed on the device + online variant chooser."""
+    from kungfu_b200.parallel.planner import GraphExecutor, VariantChooser
+    n = 300000
+    buf = comm.alloc(n * 4)
+    xs = inputs(n, torch.float32, 9)
+    ref = torch.stack(xs).sum(0)
+    for s in ('STAR', 'RING', 'BINARY_TREE', 'CLIQUE', 'TREE'):
+        kfpy.set_strategy(s)
+        ex = GraphExecutor(comm)
+        buf.view(torch.float32)[:n].copy_(xs[rank])
+        ex.all_reduce(buf, n, torch.float32, 'sum', monitored=True)
+        torch.cuda.synchronize()
+        got = buf.view(torch.float32)[:n].cpu()
+        assert torch.allclose(got, ref, rtol=1e-5, atol=1e-5), (s, (got - ref).abs().max())
+        assert ex.throughput() > 0
+    # set_tree: a chain rooted at the last rank
+    father = [min(r + 1, np_ - 1) for r in range(np_)]
+    kfpy.set_tree(father)
+    ex = GraphExecutor(comm)
+    buf.view(torch.float32)[:n].copy_(xs[rank])
+    ex.all_reduce(buf, n, torch.float32, 'max')
+    torch.cuda.synchronize()
+    assert torch.equal(buf.view(torch.float32)[:n].cpu(), torch.stack(xs).max(0).values)
+    kfpy.set_strategy('AUTO')
+    ch = VariantChooser(comm)
+    ch.probe(sizes=(64 << 10, 4 << 20))
+    assert ch.choose(4 << 20) in (K.ALGO_TWOSHOT, K.ALGO_NVLS, K.ALGO_ONESHOT)
+    switched = ch.check_interference()
+    assert switched in (False, True)
+    if rank == 0:
+        print('planner ok: best', ch.best, 'busbw', {a: round(v) for a, v in ch.reference.items()}, flush=True)
+
+
 check_allreduce()
 check_movers()
 check_fused_optimizers()
+check_planner()
 kf.run_barrier()
 print('OK rank %d/%d multicast=%s' % (rank, np_, getattr(comm, 'multicast_ok', None)), flush=True)
