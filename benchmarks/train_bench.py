@@ -99,8 +99,17 @@ def step():
     return loss
 
 
-for _ in range(args.warmup):
-    loss = step()
+if args.graph and args.optimizer != 'pair':
+    # warm up on a side stream: autograd must not tie the capture to the legacy stream
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(args.warmup):
+            loss = step()
+    torch.cuda.current_stream().wait_stream(side)
+else:
+    for _ in range(args.warmup):
+        loss = step()
 torch.cuda.synchronize()
 run = step
 if args.graph and args.optimizer != 'pair':
