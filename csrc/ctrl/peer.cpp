@@ -1,5 +1,6 @@
 #include "ctrl/peer.hpp"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -114,7 +115,9 @@ bool Peer::start()
                 monitor_thread_ = std::thread([this] {
                     while (!closing_) {
                         monitor_.sample();
-                        std::this_thread::sleep_for(std::chrono::duration<double>(cfg_.monitoring_period));
+                        // sleep in slices so close() never waits a whole period
+                        for (double left = cfg_.monitoring_period; left > 0 && !closing_; left -= 0.05)
+                            std::this_thread::sleep_for(std::chrono::duration<double>(std::min(left, 0.05)));
                     }
                 });
             } else {

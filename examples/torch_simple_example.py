@@ -1,0 +1,9 @@
+"""kungfu-run -np 4 python examples/torch_simple_example.py
+Reference: /root/reference/examples/torch_simple_example.py:1-10."""
+import torch
+
+import kungfu_b200.torch as kf
+
+x = torch.ones([2, 3])
+y = kf.ops.all_reduce_fn(x)
+print('rank %d/%d' % (kf.current_rank(), kf.current_cluster_size()), y)

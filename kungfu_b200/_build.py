@@ -38,6 +38,8 @@ HOST_LIB_DIRS = ['csrc/core', 'csrc/ctrl', 'csrc/elastic', 'csrc/capi']
 HOST_BINARIES = {
     'kungfu-run': 'csrc/launch/kungfu_run_main.cpp',
     'kungfu-config-server': 'csrc/launch/config_server_main.cpp',
+    'kungfu-rrun': 'csrc/launch/remote_tools.cpp',
+    'kungfu-distribute': 'csrc/launch/remote_tools.cpp',
 }
 
 

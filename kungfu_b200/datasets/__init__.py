@@ -1,0 +1,91 @@
+"""Data helpers: synthetic datasets of the shapes the reference's loaders
+return (there is no network for the real files), an idx-format reader for MNIST
+files when present, and the elastic dataset adaptor.
+Reference: /root/reference/srcs/python/kungfu/tensorflow/v1/helpers/{mnist.py,cifar.py,
+imagenet.py,idx.py}, /root/reference/srcs/python/kungfu/tensorflow/v1/datasets/adaptor.py:4-45."""
+import gzip
+import os
+import struct
+
+import numpy as np
+import torch
+
+
+def read_idx(path):
+    """Read an idx file (optionally .gz): the MNIST on-disk format."""
+    op = gzip.open if path.endswith('.gz') else open
+    with op(path, 'rb') as f:
+        magic = struct.unpack('>I', f.read(4))[0]
+        dtype = {0x08: np.uint8, 0x09: np.int8, 0x0B: np.int16, 0x0C: np.int32, 0x0D: np.float32, 0x0E: np.float64}[(magic >> 8) & 0xff]
+        dims = struct.unpack('>' + 'I' * (magic & 0xff), f.read(4 * (magic & 0xff)))
+        return np.frombuffer(f.read(), dtype=np.dtype(dtype).newbyteorder('>')).reshape(dims)
+
+
+def write_idx(path, arr):
+    arr = np.asarray(arr)
+    code = {np.dtype(np.uint8): 0x08, np.dtype(np.int32): 0x0C, np.dtype(np.float32): 0x0D}[arr.dtype]
+    with open(path, 'wb') as f:
+        f.write(struct.pack('>I', (code << 8) | arr.ndim))
+        f.write(struct.pack('>' + 'I' * arr.ndim, *arr.shape))
+        f.write(arr.astype(arr.dtype.newbyteorder('>')).tobytes())
+
+
+def load_mnist(data_dir=None, n_train=60000, n_test=10000, seed=2020):
+    """MNIST as (x_train, y_train, x_test, y_test); real idx files if found
+    under data_dir, else a deterministic synthetic set of the same shape whose
+    labels are a fixed random linear function of the pixels (learnable)."""
+    names = ['train-images-idx3-ubyte', 'train-labels-idx1-ubyte', 't10k-images-idx3-ubyte', 't10k-labels-idx1-ubyte']
+    if data_dir and all(os.path.exists(os.path.join(data_dir, n)) or os.path.exists(os.path.join(data_dir, n + '.gz')) for n in names):
+        arrs = []
+        for n in names:
+            p = os.path.join(data_dir, n)
+            arrs.append(read_idx(p if os.path.exists(p) else p + '.gz'))
+        xt, yt, xe, ye = arrs
+        return (torch.from_numpy(xt.astype(np.float32) / 255).view(-1, 1, 28, 28), torch.from_numpy(yt.astype(np.int64)),
+                torch.from_numpy(xe.astype(np.float32) / 255).view(-1, 1, 28, 28), torch.from_numpy(ye.astype(np.int64)))
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(784, 10, generator=g)
+    x = torch.rand(n_train + n_test, 784, generator=g)
+    y = (x @ w).argmax(1)
+    x = x.view(-1, 1, 28, 28)
+    return x[:n_train], y[:n_train], x[n_train:], y[n_train:]
+
+
+def synthetic_images(n, size=224, classes=1000, seed=0, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(n, 3, size, size, generator=g).to(dtype), torch.randint(0, classes, (n, ), generator=g)
+
+
+def synthetic_cifar10(n=50000, seed=0):
+    return synthetic_images(n, 32, 10, seed)
+
+
+class ElasticShardedDataset(object):
+    """Batches of a dataset for THIS worker under a changing cluster size.
+
+    State is three integers -- global sample offset, global batch size,
+    (rank, size) -- exactly what the reference's adaptor keeps in tf.Variables:
+    after a resize call ``reshard()`` and the stream continues from the same
+    global offset with the new sharding, so no sample is skipped or repeated."""
+
+    def __init__(self, xs, ys, global_batch_size, rank=0, size=1, offset=0):
+        self.xs, self.ys = xs, ys
+        self.global_batch_size = global_batch_size
+        self.offset = offset
+        self.reshard(rank, size)
+
+    def reshard(self, rank, size, global_batch_size=None, offset=None):
+        self.rank, self.size = rank, size
+        if global_batch_size is not None:
+            self.global_batch_size = global_batch_size
+        if offset is not None:
+            self.offset = offset
+        if self.global_batch_size % size:
+            raise ValueError('global batch %d is not divisible by %d workers' % (self.global_batch_size, size))
+
+    def next_batch(self):
+        n = len(self.xs)
+        local = self.global_batch_size // self.size
+        idx = [(self.offset + self.rank * local + i) % n for i in range(local)]
+        self.offset += self.global_batch_size
+        return self.xs[idx], self.ys[idx]

@@ -1,0 +1,86 @@
+"""Elastic training helpers (live state transfer, no checkpoint round trip).
+
+Reference: KungFuElasticTrainHook
+(/root/reference/srcs/python/kungfu/tensorflow/hooks/elastic.py:14-87), ElasticHook +
+ResizeProfiler (/root/reference/srcs/python/kungfu/tensorflow/experimental/hook/elastic.py:11-116).
+After a membership change every member all-reduces (max) the progress counters
+and receives the model from rank 0; detached workers stop.
+"""
+import time
+
+import torch
+
+from .. import python as kfpy
+from ..utils import step_based_schedule
+from .ops import collective as tops
+
+
+class ResizeProfiler(object):
+    def __init__(self):
+        self.records = []
+        self._t0 = None
+
+    def begin(self):
+        self._t0 = time.time()
+
+    def end(self, old, new):
+        self.records.append((old, new, time.time() - self._t0))
+
+    def report(self):
+        return ['resize %d -> %d took %.3fs' % r for r in self.records]
+
+
+class ElasticState(object):
+    """Tracks step / trained samples and re-synchronises them with the model."""
+
+    def __init__(self, model, optimizer=None, max_step=None):
+        self.model, self.optimizer = model, optimizer
+        self.step = 0
+        self.trained_samples = 0
+        self.max_step = max_step
+        self.profiler = ResizeProfiler()
+        self.stopped = False
+        self.sync()
+
+    def sync(self):
+        v = torch.tensor([self.step, self.trained_samples], dtype=torch.int64)
+        v = tops.all_reduce_fn(v, 'max', name='kungfu::elastic-progress')
+        self.step, self.trained_samples = int(v[0]), int(v[1])
+        tops.broadcast_parameters(self.model.state_dict())
+        if self.optimizer is not None and hasattr(self.optimizer, 'rebuild'):
+            self.optimizer.rebuild()
+
+    def end_step(self, batch_size=0):
+        self.step += 1
+        self.trained_samples += batch_size * kfpy.current_cluster_size()
+
+    def resize(self, new_size):
+        """Returns True if this worker keeps training."""
+        old = kfpy.current_cluster_size()
+        if new_size == old:
+            return True
+        self.profiler.begin()
+        changed, detached = kfpy.resize_cluster(new_size)
+        if detached:
+            self.stopped = True
+            return False
+        if changed:
+            self.sync()
+            self.profiler.end(old, new_size)
+        return True
+
+    def should_stop(self):
+        return self.stopped or (self.max_step is not None and self.step >= self.max_step)
+
+
+class ElasticTrainHook(object):
+    """Follow a "size:steps,size:steps,..." schedule (KungFuElasticTrainHook)."""
+
+    def __init__(self, schedule, max_step, model, optimizer=None):
+        self.schedule = schedule
+        self.state = ElasticState(model, optimizer, max_step)
+
+    def after_step(self, batch_size=0):
+        self.state.end_step(batch_size)
+        want = step_based_schedule(self.schedule, self.state.step, default=kfpy.current_cluster_size(), strict=False)
+        return self.state.resize(want) and not self.state.should_stop()

@@ -1,5 +1,34 @@
+from .adapt import (calc_stats, check_interference, log_stats, print_strategy_stats,  # noqa: F401
+                    resize, resize_cluster, resize_cluster_from_url, set_tree, step_based_schedule)
 from .collective import (all_gather, all_reduce_fn, barrier, broadcast,  # noqa: F401
                          broadcast_parameters, consensus, inplace_all_reduce_async_op,
                          inplace_all_reduce_op, inplace_broadcast_async_op,
                          monitored_all_reduce, request_variable, save_variable,
                          wait_all_handles, wait_handle)
+from .local import request_model, request_variable_with_template, save_model, save_variables  # noqa: F401
+from .monitor import egress_rates, global_noise_scale  # noqa: F401
+from .state import counter, exponential_moving_average  # noqa: F401
+from .topology import (cluster_size, get_neighbour_mask, get_peer_latencies,  # noqa: F401
+                       global_minimum_spanning_tree, minimum_spanning_tree, mst_to_tree,
+                       peer_info, rank, round_robin)
+
+
+def group_all_reduce(tensors, op='sum'):
+    """All-reduce a list of tensors (entries may be None, which stay None)."""
+    return [None if t is None else all_reduce_fn(t, op, name='group::%d' % i) for i, t in enumerate(tensors)]
+
+
+def fuse(tensors):
+    """Concatenate flattened tensors (reference: ops/__init__.py:29-31)."""
+    import torch
+    return torch.cat([t.reshape(-1) for t in tensors])
+
+
+def defuse(flat, shapes):
+    import torch
+    out, off = [], 0
+    for s in shapes:
+        n = int(torch.Size(s).numel())
+        out.append(flat[off:off + n].view(s))
+        off += n
+    return out

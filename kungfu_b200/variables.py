@@ -1,0 +1,44 @@
+"""Process-wide training variables the policies and monitors share.
+Reference: /root/reference/srcs/python/kungfu/tensorflow/variables.py:84-122
+(GraphKeys.{BATCH_SIZE,GRADIENT_NOISE_SCALE,TOTAL_SAMPLES,TRAINED_SAMPLES})."""
+
+
+class GraphKeys(object):
+    BATCH_SIZE = 'kungfu_batch_size'
+    GRADIENT_NOISE_SCALE = 'kungfu_gradient_noise_scale'
+    TOTAL_SAMPLES = 'kungfu_total_samples'
+    TRAINED_SAMPLES = 'kungfu_trained_samples'
+
+
+_vars = {}
+
+
+def get_or_create(key, init=0):
+    return _vars.setdefault(key, init)
+
+
+def set_value(key, value):
+    _vars[key] = value
+
+
+def get_value(key, default=None):
+    return _vars.get(key, default)
+
+
+def create_setter(key):
+    return lambda v: set_value(key, v)
+
+
+def get_or_create_batch_size(init=None):
+    if init is not None and GraphKeys.BATCH_SIZE not in _vars:
+        _vars[GraphKeys.BATCH_SIZE] = init
+    return _vars.get(GraphKeys.BATCH_SIZE)
+
+
+def eval_batch_size():
+    return _vars.get(GraphKeys.BATCH_SIZE)
+
+
+def eval_gradient_noise_scale():
+    v = _vars.get(GraphKeys.GRADIENT_NOISE_SCALE)
+    return float(v) if v is not None else None

@@ -1,0 +1,101 @@
+// C++ integration test of the kungfu::Peer API, run under kungfu-run for
+// np = 1..4 and every strategy (the reference's fake-agent,
+// /root/reference/tests/cpp/integration/fake_agent.cpp:15-205).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <numeric>
+#include <vector>
+
+#include <kungfu/peer.hpp>
+
+#define CHECK(cond)                                                            \
+    do {                                                                       \
+        if (!(cond)) {                                                         \
+            fprintf(stderr, "CHECK failed %s:%d: %s\n", __FILE__, __LINE__, #cond); \
+            exit(1);                                                           \
+        }                                                                      \
+    } while (0)
+
+int main()
+{
+    kungfu::Peer peer;
+    const int np = peer.Size(), rank = peer.Rank();
+    // AllReduce: y[i] = i * np
+    {
+        const int n = 1 << 18;
+        std::vector<int32_t> x(n), y(n);
+        std::iota(x.begin(), x.end(), 0);
+        CHECK(peer.AllReduce(x.data(), y.data(), n, kungfu::I32, kungfu::SUM, "ar-int") == 0);
+        for (int i = 0; i < n; ++i) CHECK(y[i] == i * np);
+    }
+    // Reduce / AllReduce x100 with changing names
+    for (int k = 0; k < 100; ++k) {
+        float x = (float)(rank + k), y = 0;
+        char name[32];
+        snprintf(name, sizeof(name), "loop%d", k);
+        CHECK(peer.AllReduce(&x, &y, 1, kungfu::F32, kungfu::SUM, name) == 0);
+        CHECK(std::fabs(y - (np * (np - 1) / 2.0f + (float)k * np)) < 1e-3);
+        float r = 0;
+        CHECK(peer.Reduce(&x, &r, 1, kungfu::F32, kungfu::MAX, name) == 0);
+        if (rank == 0) CHECK(r == (float)(np - 1 + k));
+    }
+    // async AllReduce with callback
+    {
+        std::vector<float> x(1000, 1.0f), y(1000, 0.0f);
+        volatile bool done = false;
+        peer.AllReduce(x.data(), y.data(), 1000, kungfu::F32, kungfu::SUM, "async", [&] { done = true; });
+        while (!done) std::this_thread::yield();
+        CHECK(y[999] == (float)np);
+    }
+    // Gather / AllGather
+    {
+        std::vector<int32_t> x(3, rank), g(3 * np, -1), a(3 * np, -1);
+        CHECK(peer.Gather(x.data(), g.data(), 3, kungfu::I32, "gather") == 0);
+        CHECK(peer.AllGather(x.data(), a.data(), 3, kungfu::I32, "allgather") == 0);
+        for (int r = 0; r < np; ++r) {
+            CHECK(a[3 * r] == r);
+            if (rank == 0) CHECK(g[3 * r + 2] == r);
+        }
+    }
+    // AllGatherTransform: sum of every rank's value computed on rank 0, delivered to all
+    {
+        float in = (float)(rank + 1), out = 0;
+        CHECK(peer.AllGatherTransform(&in, 1, &out, 1, "agt", [](const float *all, int n, int, float *o, int) {
+                  *o = 0;
+                  for (int i = 0; i < n; ++i) *o += all[i];
+              }) == 0);
+        CHECK(out == np * (np + 1) / 2.0f);
+    }
+    // Broadcast, Consensus, p2p store (success and expected failure)
+    {
+        int32_t v = rank == 0 ? 42 : -1;
+        CHECK(peer.Broadcast(&v, &v, 1, kungfu::I32, "bcast") == 0);
+        CHECK(v == 42);
+        CHECK(peer.Consensus(&v, sizeof(v), "same"));
+        int32_t mine = rank;
+        CHECK(peer.Consensus(&mine, sizeof(mine), "diff") == (np == 1));
+        float model[4] = {(float)rank, 1, 2, 3};
+        CHECK(peer.Save("m", model, sizeof(model)) == 0);
+        CHECK(peer.Barrier() == 0);
+        float other[4] = {-1, -1, -1, -1};
+        const int target = (rank + 1) % np;
+        CHECK(peer.Request(target, "m", other, sizeof(other)) == 0);
+        CHECK(other[0] == (float)target);
+        CHECK(peer.Request(target, "m!", other, sizeof(other)) != 0);
+        CHECK(peer.Barrier() == 0);
+    }
+    // latencies + set_tree
+    {
+        std::vector<float> lat(np);
+        CHECK(peer.GetPeerLatencies(lat.data(), np) == 0);
+        std::vector<int32_t> tree(np, 0);
+        CHECK(peer.SetTree(tree.data()) == 0);
+        int32_t one = 1, sum = 0;
+        CHECK(peer.AllReduce(&one, &sum, 1, kungfu::I32, kungfu::SUM, "after-set-tree") == 0);
+        CHECK(sum == np);
+    }
+    peer.Barrier();
+    printf("OK fake-agent rank %d/%d\n", rank, np);
+    return 0;
+}
