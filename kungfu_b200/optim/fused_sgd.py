@@ -64,6 +64,9 @@ class FusedSGD(torch.optim.Optimizer):
         old = self._arenas
         self._comm = comm
         self._arenas = None
+        self._local = None
+        if hasattr(self, '_kf_stage'):
+            self._kf_stage = {}  # SMA staging buffers belong to the old communicator
         if old is None:
             return
         olds = [a for _, ars in old for a in ars]
@@ -167,4 +170,20 @@ class FusedSGD(torch.optim.Optimizer):
                     tmp.view(torch.float32)[:hi - lo].copy_(t[lo:hi])
                     coll.all_gather(comm, tmp, stage, per * 4)
                     t.copy_(sv[:per * comm.np][:a.count])
+        torch.cuda.synchronize()
+
+    def broadcast_state(self):
+        """Master weights, momentum and the step counter := rank 0's (after a
+        resize: rank 0 consolidated before the membership changed, joiners
+        start from its state)."""
+        from ..torch.ops import collective as tops
+        steps = torch.tensor([self._steps], dtype=torch.int64)
+        self._steps = int(tops.all_reduce_fn(steps, 'max', name='kungfu::fused-sgd-steps')[0])
+        if self.comm.np <= 1:
+            return
+        for gi, (_, arenas) in enumerate(self.arenas()):
+            for ai, a in enumerate(arenas):
+                a.ensure_master()
+                tops.broadcast(a.master, name='kungfu::master.%d.%d' % (gi, ai))
+                tops.broadcast(a.mom, name='kungfu::mom.%d.%d' % (gi, ai))
         torch.cuda.synchronize()

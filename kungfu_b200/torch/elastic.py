@@ -46,9 +46,13 @@ class ElasticState(object):
         v = torch.tensor([self.step, self.trained_samples], dtype=torch.int64)
         v = tops.all_reduce_fn(v, 'max', name='kungfu::elastic-progress')
         self.step, self.trained_samples = int(v[0]), int(v[1])
-        tops.broadcast_parameters(self.model.state_dict())
         if self.optimizer is not None and hasattr(self.optimizer, 'rebuild'):
+            # move the flat arenas (parameters, gradients) into the new
+            # membership's symmetric memory before anything is broadcast into them
             self.optimizer.rebuild()
+        tops.broadcast_parameters(self.model.state_dict())
+        if self.optimizer is not None and hasattr(self.optimizer, 'broadcast_state'):
+            self.optimizer.broadcast_state()
 
     def end_step(self, batch_size=0):
         self.step += 1
@@ -60,6 +64,10 @@ class ElasticState(object):
         if new_size == old:
             return True
         self.profiler.begin()
+        if self.optimizer is not None and hasattr(self.optimizer, 'consolidate'):
+            # fused optimizers shard their fp32 state over the ranks: make it whole
+            # on every (old) member while all of them are still here
+            self.optimizer.consolidate()
         changed, detached = kfpy.resize_cluster(new_size)
         if detached:
             self.stopped = True

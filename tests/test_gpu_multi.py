@@ -29,3 +29,35 @@ def test_peer_memory_path_ipc_fallback():
     res = run_workers(2, os.path.join(ROOT, 'tests', 'workers', 'gpu_peer_worker.py'), timeout=300,
                       extra_flags=['-allow-nvlink'], env={'KUNGFU_SYMM_MODE': 'ipc'})
     assert res.returncode == 0, res.stdout[-6000:]
+
+
+def test_gpu_elastic_resize(tmp_path):
+    """resize_cluster on GPUs: peer memory is re-mapped for every new membership,
+    fused optimizer state is consolidated / re-broadcast, survivors keep running."""
+    import collections
+    import socket
+    n = _ngpu()
+    if n < 2:
+        pytest.skip('needs 2 GPUs')
+    schedule, steps = ('1:2,2:3,4:3,2:2,1:2', 12) if n >= 4 else ('1:2,2:3,1:2', 7)
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    log = str(tmp_path / 'steps.log')
+    res = run_workers(1, os.path.join(ROOT, 'tests', 'workers', 'gpu_elastic_worker.py'), args=[schedule, str(steps), log],
+                      timeout=400, extra_flags=['-w', '-builtin-config-port', str(port), '-allow-nvlink'])
+    assert res.returncode == 0, res.stdout[-6000:]
+    sizes, pids = collections.defaultdict(set), collections.defaultdict(set)
+    for line in open(log):
+        step, rank, np_, pid, loss = line.split()
+        sizes[int(step)].add(int(np_))
+        pids[int(step)].add(int(pid))
+    off = 0
+    for part in schedule.split(','):
+        size, k = map(int, part.split(':'))
+        for st in range(off, off + k):
+            assert sizes[st] == {size}, (st, sizes[st])
+        off += k
+    first = next(iter(pids[0]))
+    assert all(first in pids[st] for st in range(steps))
