@@ -67,10 +67,12 @@ class FusedSGD(torch.optim.Optimizer):
         self._local = None
         if hasattr(self, '_kf_stage'):
             self._kf_stage = {}  # SMA staging buffers belong to the old communicator
+        # every member (joiners included) allocates its arenas here: symmetric
+        # allocation is collective and must happen in the same order everywhere
+        news = [a for _, ars in self.arenas() for a in ars]
         if old is None:
             return
         olds = [a for _, ars in old for a in ars]
-        news = [a for _, ars in self.arenas() for a in ars]
         for o, n in zip(olds, news):
             if o.master is not None:
                 n.ensure_master()

@@ -203,6 +203,13 @@ class PeerComm(_CommBase):
         """Collective: every rank must call with the same size, in the same order."""
         gran = 2 << 20
         nbytes = _align(max(nbytes, 1), gran)
+        # collective-call hygiene: a mismatch here would otherwise surface as an
+        # obscure driver error when a peer maps a block of another size
+        want = self.xchg.all_gather_bytes(int(nbytes).to_bytes(8, 'little'))
+        if any(w != want[0] for w in want):
+            raise K.KungFuCudaError('symmetric alloc mismatch: ranks asked for %s bytes; allocations are collective '
+                                    'and must be issued in the same order on every rank' %
+                                    [int.from_bytes(w, 'little') for w in want])
         if self.mode == 'vmm':
             size, handles, ptrs = self._alloc_vmm(nbytes)
         else:
