@@ -60,7 +60,12 @@ std::string format_ipv4(uint32_t ip)
 
 std::string PeerID::str() const { return format_ipv4(ipv4) + ":" + std::to_string(port); }
 std::string PeerID::host_str() const { return format_ipv4(ipv4); }
-std::string PeerID::sock_file() const { return "/tmp/kungfu-b200-" + std::to_string(port) + ".sock"; }
+std::string PeerID::sock_file() const
+{
+    // the address is part of the name so that several "hosts" emulated on
+    // loopback aliases (127.0.0.x) of one machine do not collide
+    return "/tmp/kungfu-b200-" + format_ipv4(ipv4) + "-" + std::to_string(port) + ".sock";
+}
 
 bool parse_peer_id(const std::string &s, PeerID *out)
 {

@@ -39,7 +39,7 @@ static void ignore_sigpipe()
     std::call_once(once, [] { signal(SIGPIPE, SIG_IGN); });
 }
 
-int tcp_listen(uint16_t port, std::string *err)
+int tcp_listen(uint16_t port, std::string *err, uint32_t bind_ipv4)
 {
     ignore_sigpipe();
     int fd = socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
@@ -52,7 +52,7 @@ int tcp_listen(uint16_t port, std::string *err)
     sockaddr_in a;
     memset(&a, 0, sizeof(a));
     a.sin_family      = AF_INET;
-    a.sin_addr.s_addr = htonl(INADDR_ANY);
+    a.sin_addr.s_addr = htonl(bind_ipv4 ? bind_ipv4 : INADDR_ANY);
     a.sin_port        = htons(port);
     if (bind(fd, (sockaddr *)&a, sizeof(a)) != 0 || listen(fd, 512) != 0) {
         if (err) *err = "bind/listen :" + std::to_string(port) + ": " + strerror(errno);
@@ -450,7 +450,8 @@ struct WireHello {
 
 bool Server::start(std::string *err)
 {
-    tcp_fd_ = tcp_listen(self_.port, err);
+    // loopback aliases (multi-host emulation on one machine) bind their own address
+    tcp_fd_ = tcp_listen(self_.port, err, (self_.ipv4 >> 24) == 127 ? self_.ipv4 : 0);
     if (tcp_fd_ < 0) return false;
     if (use_unix_) {
         unix_fd_ = unix_listen(self_.sock_file(), err);

@@ -50,7 +50,8 @@ struct TransportConfig {
 };
 
 // ---- low level socket helpers ---------------------------------------------------
-int tcp_listen(uint16_t port, std::string *err);
+// bind_ipv4 == 0 listens on every interface
+int tcp_listen(uint16_t port, std::string *err, uint32_t bind_ipv4 = 0);
 int unix_listen(const std::string &path, std::string *err);
 int tcp_connect(uint32_t ipv4, uint16_t port);
 int unix_connect(const std::string &path);

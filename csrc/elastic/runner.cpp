@@ -5,6 +5,7 @@
 #include <ifaddrs.h>
 #include <net/if.h>
 #include <signal.h>
+#include <sys/prctl.h>
 #include <sys/stat.h>
 #include <sys/wait.h>
 #include <unistd.h>
@@ -410,6 +411,9 @@ class ProcTable
         }
         if (pid == 0) {
             setpgid(0, 0);
+            // never outlive the runner: an orphaned worker would keep its port and GPU
+            prctl(PR_SET_PDEATHSIG, SIGKILL);
+            if (getppid() == 1) _exit(1);  // runner died between fork and prctl
             dup2(po[1], 1);
             dup2(pe[1], 2);
             execvpe(spec.prog.c_str(), argv.data(), envp.data());
