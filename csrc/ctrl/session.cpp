@@ -123,6 +123,9 @@ bool Session::run_graphs(const Workspace &w, const std::vector<const Graph *> &g
                 if (!send_to(q, w.name, w.recv, n)) return false;
         }
     }
+    // a node that never received anything (e.g. the only worker of its host in
+    // a local reduce) still owes the caller a result in recv
+    if (recv_count == 0) w.forward();
     return true;
 }
 
