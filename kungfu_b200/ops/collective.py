@@ -132,3 +132,57 @@ def edge_reduce(dst_ptr, src_ptr, count, dtype, op='sum', blocks=16, threads=512
 
 def edge_copy(dst_ptr, src_ptr, nbytes, blocks=16, threads=512, stream=None):
     K.call('kfb_edge_copy', dst_ptr, src_ptr, nbytes, blocks, threads, K.stream_ptr(stream))
+
+
+_HOST_CODE = None
+_pinned = {}
+
+
+def hier_all_reduce(comm, buf, count, dtype, op='sum', scale=1.0, byte_offset=0, stream=None):
+    """Hierarchical all-reduce for jobs that span hosts: NVLink kernels inside
+    the host, the control plane between host masters, a multicast/push
+    broadcast back (reference: KungfuScheduledHierarchicalNcclAllReduce =
+    ncclReduce -> CrossAllReduce over TCP -> ncclBroadcast,
+    /root/reference/srcs/cpp/src/tensorflow/ops/gpu/collective.cpp:131-153,
+    /root/reference/srcs/cpp/src/nccl/controller.cpp:8-40). In place on `buf`."""
+    import ctypes as C
+
+    from .. import _host as H
+    from .. import python as kfpy
+    code = dtype if isinstance(dtype, int) else K.dtype_code(dtype)
+    opc = op if isinstance(op, int) else K.OPS[op]
+    es = _ESIZE[code]
+    nbytes = count * es
+    tdt = {K.F32: torch.float32, K.BF16: torch.bfloat16, K.F16: torch.float16, K.I32: torch.int32,
+           K.F64: torch.float64, K.I64: torch.int64, K.U8: torch.uint8}[code]
+    hdt = {K.F32: H.F32, K.BF16: H.BF16, K.F16: H.F16, K.I32: H.I32, K.F64: H.F64, K.I64: H.I64, K.U8: H.U8}[code]
+    if comm.np > 1:
+        algo = choose_algo(comm, nbytes, buf, opc, code)
+        if algo == K.ALGO_ONESHOT:
+            algo = K.ALGO_TWOSHOT
+        all_reduce(comm, buf, count, code, opc, scale=1.0, algo=algo, byte_offset=byte_offset, stream=stream)
+    if comm.is_local_root:
+        dev_view = buf.local[byte_offset:byte_offset + nbytes].view(tdt)
+        host = _pinned.get((tdt, count))
+        if host is None:
+            host = torch.empty(count, dtype=tdt).pin_memory()
+            _pinned[(tdt, count)] = host
+        s = stream or torch.cuda.current_stream()
+        with torch.cuda.stream(s):
+            host.copy_(dev_view, non_blocking=True)
+        s.synchronize()
+        _n = getattr(hier_all_reduce, '_seq', 0) + 1
+        hier_all_reduce._seq = _n
+        rc = H.lib().kf_cross_all_reduce(kfpy.peer()._h, host.data_ptr(), host.data_ptr(), count, hdt, opc,
+                                         b'kungfu::hier')
+        if rc != 0:
+            raise K.KungFuCudaError('cross-host all-reduce failed: %s' % H.lib().kf_last_error().decode())
+        if scale != 1.0 and tdt.is_floating_point:
+            host.mul_(scale)
+        with torch.cuda.stream(s):
+            dev_view.copy_(host, non_blocking=True)
+    elif scale != 1.0:
+        pass  # the host master's scaled result arrives with the broadcast below
+    if comm.np > 1:
+        broadcast(comm, buf, (nbytes + 15) // 16 * 16, root=0, byte_offset=byte_offset, stream=stream)
+    return buf

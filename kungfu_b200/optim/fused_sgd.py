@@ -115,7 +115,14 @@ class FusedSGD(torch.optim.Optimizer):
                 ss_l = self._ss_local_parts[k:k + 1] if self.monitor_norms else None
                 ss_g = self._ss_global_parts[k:k + 1] if self.monitor_norms else None
                 a.fuse_grads(sumsq_out=ss_l)
-                if sync and comm.np > 1:
+                step_scale = grad_scale
+                if sync and comm.cross:
+                    # hosts are joined by the control plane: hierarchical all-reduce of
+                    # the bucket first, then the purely local fused update
+                    from ..ops import collective as coll
+                    coll.hier_all_reduce(comm, a.grads_buf, a.count, a.code, 'sum', scale=grad_scale)
+                    step_scale = 1.0
+                if sync and comm.np > 1 and not comm.cross:
                     ga, _k1 = a.grads_buf.ptr_array()
                     pa, _k2 = a.params_buf.ptr_array()
                     cs = comm.cstruct
@@ -125,7 +132,7 @@ class FusedSGD(torch.optim.Optimizer):
                     pa, _k2 = K.ptr_array([a.params_buf.ptrs[me]])
                     cs = self._local_struct()
                 K.call('kfb_ssgd_fused_step', cs, ga, a.code, pa, a.code,
-                       a.master.data_ptr(), a.mom.data_ptr(), a.count, float(grad_scale),
+                       a.master.data_ptr(), a.mom.data_ptr(), a.count, float(step_scale),
                        C.byref(h), ss_g.data_ptr() if ss_g is not None else None,
                        blocks, threads, K.stream_ptr())
                 k += 1
@@ -146,7 +153,8 @@ class FusedSGD(torch.optim.Optimizer):
     @torch.no_grad()
     def sync_step(self, average=True):
         """All-reduce gradients over peer memory and apply the update, fused."""
-        scale = 1.0 / self.comm.np if average else 1.0
+        n = self.comm.global_np if self.comm.cross else self.comm.np
+        scale = 1.0 / n if average else 1.0
         self._run(sync=True, grad_scale=scale)
 
     # -- state ------------------------------------------------------------------------------

@@ -60,6 +60,9 @@ class _CommBase(object):
     rank = 0
     np = 1
     emulated = False
+    cross = False        # True: more hosts exist; collectives need a cross-host leg
+    global_np = None     # job-wide worker count when cross
+    is_local_root = True
 
     def __init__(self, device):
         self.device = torch.device(device)
@@ -152,9 +155,10 @@ class PeerComm(_CommBase):
         self._seq = 0
         self.multicast_ok = False
         if os.environ.get('KUNGFU_DISABLE_NVLS', '0') != '1' and self.mode == 'vmm':
+            # (always exchanged, even by a lone worker of a host: the exchange is job-collective)
             ok = K.lib().kfb_multicast_supported(self.device.index or 0)
             oks = xchg.all_gather_bytes(bytes([1 if ok else 0]))
-            self.multicast_ok = all(b == b'\x01' for b in oks)
+            self.multicast_ok = self.np > 1 and all(b == b'\x01' for b in oks)
         self._pad_buf = self.alloc(K.PAD_BYTES)
         self._init_struct(self.rank, self.np, self._pad_buf.ptrs, 1)
 
@@ -267,9 +271,76 @@ def default_comm():
         dev = torch.device('cuda', torch.cuda.current_device())
         if kfpy.current_cluster_size() <= 1:
             _default = LocalComm(dev)
+        elif kfpy.host_count() > 1:
+            # several hosts: peer memory only spans this host's GPUs; the
+            # cross-host leg goes through the control plane (hierarchical
+            # all-reduce, /root/reference/srcs/cpp/src/nccl/controller.cpp:8-40)
+            lx = LocalExchange(kfpy.peer())
+            _default = PeerComm(lx, dev)  # also for a lone worker: allocation stays job-collective
+            _default.cross = True
+            _default.global_np = kfpy.current_cluster_size()
+            _default.is_local_root = lx.rank == 0
         else:
             _default = PeerComm(kfpy.control_exchange(), dev)
     return _default
+
+
+class LocalExchange(object):
+    """The control-plane exchange restricted to the workers of this host.
+    Calls are still issued by every worker of the job in lockstep (symmetric
+    allocation is collective), so job-wide primitives can be reused and sliced."""
+
+    def __init__(self, peer):
+        from .. import _host as H
+        self._peer = peer
+        self._g = peer.exchange()
+        n = peer.size()
+        buf = C.create_string_buffer(64)
+        hosts = []
+        for r in range(n):
+            H.lib().kf_peer_addr(peer._h, r, buf, 64)
+            hosts.append(buf.value.decode().split(':')[0])
+        mine = hosts[peer.rank()]
+        self.members = [r for r in range(n) if hosts[r] == mine]  # global ranks on this host
+        self.rank = self.members.index(peer.rank())
+        self.size = len(self.members)
+
+    def barrier(self):
+        # host-local: reduce to the host master, then broadcast back (hosts may
+        # take different code paths, e.g. only multi-GPU hosts bind multicast)
+        from .. import _host as H
+        a, b = C.c_uint8(1), C.c_uint8(0)
+        H._check(H.lib().kf_local_reduce(self._peer._h, C.byref(a), C.byref(b), 1, H.U8, 0, b'kungfu::lx-barrier'), 'local barrier')
+        H._check(H.lib().kf_local_broadcast(self._peer._h, C.byref(b), C.byref(b), 1, H.U8, b'kungfu::lx-barrier'), 'local barrier')
+
+    def all_gather_bytes(self, b):
+        # job-wide gather, sliced: only used at points every worker reaches
+        everyone = self._g.all_gather_bytes(b)
+        return [everyone[r] for r in self.members]
+
+    def exchange_fds(self, fd, tag):
+        from .. import _host as H
+        out = [None] * self.size
+        for k in range(1, self.size):
+            dst = self.members[(self.rank + k) % self.size]
+            H._check(H.lib().kf_send_fd(self._peer._h, dst, tag.encode(), fd), 'send_fd')
+        for k in range(1, self.size):
+            i = (self.rank - k) % self.size
+            got = C.c_int(-1)
+            H._check(H.lib().kf_recv_fd(self._peer._h, self.members[i], tag.encode(), C.byref(got)), 'recv_fd')
+            out[i] = got.value
+        return out
+
+    def broadcast_fd(self, fd, tag, root=0):
+        from .. import _host as H
+        if self.rank == root:
+            for i in range(self.size):
+                if i != root:
+                    H._check(H.lib().kf_send_fd(self._peer._h, self.members[i], tag.encode(), fd), 'send_fd')
+            return fd
+        got = C.c_int(-1)
+        H._check(H.lib().kf_recv_fd(self._peer._h, self.members[root], tag.encode(), C.byref(got)), 'recv_fd')
+        return got.value
 
 
 def set_default_comm(comm):

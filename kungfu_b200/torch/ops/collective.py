@@ -90,6 +90,15 @@ def _cuda_all_reduce(x, y, op):
     from ...ops import collective as coll
     comm = _comm()
     opc = K.OPS[op]
+    if comm.cross:
+        # job spans hosts: NVLink inside the host, control plane between host masters
+        xc = x.contiguous()
+        nbytes = xc.numel() * xc.element_size()
+        src = _stage(comm, 'in', (nbytes + 15) // 16 * 16)
+        src.local[:nbytes].copy_(xc.view(-1).view(torch.uint8))
+        coll.hier_all_reduce(comm, src, xc.numel(), K.dtype_code(x.dtype), opc)
+        y.copy_(src.local[:nbytes].view(x.dtype).view(xc.shape))
+        return
     if comm.np == 1:
         if y.data_ptr() != x.data_ptr():
             y.copy_(x)
@@ -114,6 +123,13 @@ def _cuda_all_reduce(x, y, op):
 def _cuda_broadcast(x):
     from ...ops import collective as coll
     comm = _comm()
+    if comm.cross:
+        # rare, latency-insensitive op: stage through the host control plane
+        h = x.detach().contiguous().cpu().view(-1)
+        _check(H.lib().kf_broadcast(kfpy.peer()._h, h.data_ptr(), h.data_ptr(), h.numel(), _host_dtype(h),
+                                    b'kungfu::xhost-bcast'), 'broadcast')
+        x.copy_(h.view(x.shape))
+        return
     if comm.np == 1:
         return
     xc = x.contiguous()
@@ -128,6 +144,13 @@ def _cuda_broadcast(x):
 def _cuda_all_gather(x, y):
     from ...ops import collective as coll
     comm = _comm()
+    if comm.cross:
+        h = x.detach().contiguous().cpu()
+        out = torch.empty([kfpy.current_cluster_size()] + list(h.shape), dtype=h.dtype)
+        _check(H.lib().kf_all_gather(kfpy.peer()._h, h.data_ptr(), out.data_ptr(), h.numel(), _host_dtype(h),
+                                     b'kungfu::xhost-allgather'), 'all_gather')
+        y.copy_(out)
+        return
     if comm.np == 1:
         y.copy_(x.unsqueeze(0))
         return

@@ -100,7 +100,12 @@ class GradSync(object):
             ss_g = self._ss_global[k:k + 1] if self.monitor_norms else None
             if a.fuse_grads(sumsq_out=ss_l) == 0:
                 continue
-            if comm.np > 1:
+            if comm.cross:
+                gscale = 1.0 / comm.global_np if average else 1.0
+                coll.hier_all_reduce(comm, a.grads_buf, a.count, a.code, 'sum', scale=gscale)
+                if self.monitor_norms:
+                    ss_g.copy_(a.flat_grads.float().pow(2).sum().reshape(1))
+            elif comm.np > 1:
                 coll.all_reduce(comm, a.grads_buf, a.count, a.code, 'sum', scale=scale, sumsq_out=ss_g)
             elif self.monitor_norms:
                 ss_g.copy_(ss_l)

@@ -61,3 +61,24 @@ def test_gpu_elastic_resize(tmp_path):
         off += k
     first = next(iter(pids[0]))
     assert all(first in pids[st] for st in range(steps))
+
+
+def test_hierarchical_two_hosts_on_loopback():
+    """2 'hosts' (loopback aliases) x 2 GPUs: local NVLink kernels + cross-host control plane."""
+    import subprocess
+    import sys
+    if _ngpu() < 4:
+        pytest.skip('needs 4 GPUs')
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
+    base = 23000 + (os.getpid() * 17) % 9000
+    hosts = '127.0.0.1:2,127.0.0.2:2'
+    procs = []
+    for i, ip in enumerate(('127.0.0.1', '127.0.0.2')):
+        env = dict(os.environ, PYTHONPATH=ROOT, KUNGFU_TEST_GPU_OFFSET=str(2 * i))
+        cmd = [exe, '-q', '-np', '4', '-H', hosts, '-self', ip, '-allow-nvlink', '-timeout', '200s', '-port-range',
+               '%d-%d' % (base, base + 16), '-port', str(base + 20), sys.executable,
+               os.path.join(ROOT, 'tests', 'workers', 'gpu_hier_worker.py')]
+        procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
+    outs = [p.communicate(timeout=260)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), '\n'.join(o[-3000:] for o in outs)
+    assert sum(o.count('OK hier') for o in outs) == 4
