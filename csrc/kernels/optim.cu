@@ -22,6 +22,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "multimem.cuh"
 
 namespace kfb {
 
@@ -311,6 +312,107 @@ __global__ void __launch_bounds__(512)
                 t += *reinterpret_cast<volatile float *>(scratch + b);
             a.sumsq_out[a.rank < 0 ? rank : 0] = t;
             *reinterpret_cast<unsigned int *>(scratch + KFB_MAX_BLOCKS) = 0u;
+        }
+    }
+}
+
+// NVLS variant of the fused S-SGD step: the NVSwitch sums the gradient shard
+// (multimem.ld_reduce, fp32 accumulation) and multicasts the updated
+// parameters (multimem.st), so each GPU moves ~1x the bucket instead of
+// 2(n-1)/n x. a.stage[0] / a.stage[1] carry the multicast addresses of the
+// gradient and parameter buffers.
+template <typename T> struct Mc8;
+template <> struct Mc8<float> {
+    __device__ static void ld_reduce(const void *mc, long long i, float *v)
+    {
+        const uint4 *p = reinterpret_cast<const uint4 *>(mc) + 2 * i;
+        Pack<float>::unpack(Multimem<float>::ld_reduce(p), v);
+        Pack<float>::unpack(Multimem<float>::ld_reduce(p + 1), v + 4);
+    }
+    __device__ static void st(void *mc, long long i, const float *v)
+    {
+        uint4 *p = reinterpret_cast<uint4 *>(mc) + 2 * i;
+        Multimem<float>::st(p, Pack<float>::pack(v));
+        Multimem<float>::st(p + 1, Pack<float>::pack(v + 4));
+    }
+};
+template <> struct Mc8<__nv_bfloat16> {
+    __device__ static void ld_reduce(const void *mc, long long i, float *v)
+    {
+        Pack<__nv_bfloat16>::unpack(Multimem<__nv_bfloat16>::ld_reduce(reinterpret_cast<const uint4 *>(mc) + i), v);
+    }
+    __device__ static void st(void *mc, long long i, const float *v)
+    {
+        Multimem<__nv_bfloat16>::st(reinterpret_cast<uint4 *>(mc) + i, Pack<__nv_bfloat16>::pack(v));
+    }
+};
+template <> struct Mc8<__half> {
+    __device__ static void ld_reduce(const void *mc, long long i, float *v)
+    {
+        Pack<__half>::unpack(Multimem<__half>::ld_reduce(reinterpret_cast<const uint4 *>(mc) + i), v);
+    }
+    __device__ static void st(void *mc, long long i, const float *v)
+    {
+        Multimem<__half>::st(reinterpret_cast<uint4 *>(mc) + i, Pack<__half>::pack(v));
+    }
+};
+
+template <typename G, typename P, bool NORM>
+__global__ void __launch_bounds__(512)
+    k_ssgd_fused_nvls(const __grid_constant__ StepArgs a)
+{
+    const int rank = a.rank, np = a.np;
+    __shared__ float red[32];
+    peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    const long long per    = (a.npk + np - 1) / np;
+    const long long lo     = (long long)rank * per;
+    const long long hi     = min(lo + per, a.npk);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const void *mc_g       = a.stage[0];
+    void *mc_p             = a.stage[1];
+    float ss               = 0.f;
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+        float g[8], p[8], m[8];
+        Mc8<G>::ld_reduce(mc_g, i, g);
+        Pk8<float>::load(a.master, i, p);
+        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(a.mom, i, m);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            g[k] *= a.grad_scale;
+            if (NORM) ss = fmaf(g[k], g[k], ss);
+        }
+        sgd_update8(p, m, g, a.h);
+        Pk8<float>::store(a.master, i, p);
+        if (a.h.momentum != 0.f) Pk8<float>::store(a.mom, i, m);
+        Mc8<P>::st(mc_p, i, p);
+    }
+    if (NORM) {
+        const float part = block_sum(ss, red);
+        __shared__ float s_part;
+        if (threadIdx.x == 0) s_part = part;
+        __syncthreads();
+        if (threadIdx.x < np)
+            st_relaxed_sys_f32(pad_scalar(a.pads.pad[threadIdx.x], blockIdx.x, rank), s_part);
+    }
+    peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    if (NORM) {
+        __shared__ bool is_last;
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int r = 0; r < np; ++r)
+                t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            a.scratch[blockIdx.x] = t;
+            __threadfence();
+            unsigned int *ticket = reinterpret_cast<unsigned int *>(a.scratch + KFB_MAX_BLOCKS);
+            is_last              = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+        }
+        __syncthreads();
+        if (is_last && threadIdx.x == 0) {
+            __threadfence();
+            float t = 0.f;
+            for (unsigned b = 0; b < gridDim.x; ++b) t += *reinterpret_cast<volatile float *>(a.scratch + b);
+            a.sumsq_out[0] = t;
+            *reinterpret_cast<unsigned int *>(a.scratch + KFB_MAX_BLOCKS) = 0u;
         }
     }
 }
@@ -844,6 +946,37 @@ extern "C" int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
             KFB_SSGD(0);
         }));
 #undef KFB_SSGD
+    return KFB_OK;
+}
+
+extern "C" int kfb_ssgd_fused_step_nvls(const kfb_comm *comm, void *mc_grads, int grad_dtype, void *mc_params,
+                                        int param_dtype, float *master, float *mom, int64_t count,
+                                        float grad_scale, const kfb_sgd_hyper *h, float *sumsq_out, int blocks,
+                                        int threads, void *stream)
+{
+    int rc = check_launch(comm, blocks, threads);
+    if (rc) return rc;
+    if (comm->rank < 0 || comm->np < 2 || !mc_grads || !mc_params) {
+        set_last_error("NVLS fused step needs real ranks (np >= 2) and multicast addresses");
+        return KFB_ERR_ARG;
+    }
+    StepArgs a;
+    rc = fill_step(a, comm, count);
+    if (rc) return rc;
+    a.stage[0]   = mc_grads;
+    a.stage[1]   = mc_params;
+    a.master     = master;
+    a.mom        = mom;
+    a.grad_scale = grad_scale;
+    a.h          = to_h(h);
+    a.sumsq_out  = sumsq_out;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P, {
+            if (sumsq_out) k_ssgd_fused_nvls<G, P, true><<<blocks, threads, 0, s>>>(a);
+            else k_ssgd_fused_nvls<G, P, false><<<blocks, threads, 0, s>>>(a);
+        }));
+    KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
 

@@ -188,6 +188,16 @@ int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
                         float *sumsq_out, int blocks, int threads,
                         void *stream);
 
+/* NVLS variant: the switch sums the gradient shard (multimem.ld_reduce) and
+ * multicasts the updated parameters (multimem.st). mc_grads / mc_params are
+ * the multicast aliases of the flat gradient / parameter buffers. np >= 2. */
+int kfb_ssgd_fused_step_nvls(const kfb_comm *comm, void *mc_grads,
+                             int grad_dtype, void *mc_params, int param_dtype,
+                             float *master, float *mom, int64_t count,
+                             float grad_scale, const kfb_sgd_hyper *h,
+                             float *sumsq_out, int blocks, int threads,
+                             void *stream);
+
 /* Local flat SGD on an already-reduced gradient buffer (any-optimizer path's
  * fast sibling; also the np==1 path). */
 int kfb_sgd_flat(const void *grad, int grad_dtype, void *param,

@@ -35,6 +35,9 @@ class FusedSGD(torch.optim.Optimizer):
         self.sumsq_global = None  # ||averaged grad||^2 of the last sync step (device float)
         self.sumsq_local = None  # ||local grad||^2 of the last step (device float)
         self.monitor_norms = False
+        import os
+        self.use_nvls = os.environ.get('KUNGFU_FUSED_NVLS', '1') != '0'
+        self.nvls_min_bytes = int(os.environ.get('KUNGFU_FUSED_NVLS_MIN_BYTES', str(256 << 10)))
 
     # -- arenas -------------------------------------------------------------------------
     @property
@@ -122,6 +125,16 @@ class FusedSGD(torch.optim.Optimizer):
                     from ..ops import collective as coll
                     coll.hier_all_reduce(comm, a.grads_buf, a.count, a.code, 'sum', scale=grad_scale)
                     step_scale = 1.0
+                use_nvls = (sync and comm.np > 1 and not comm.cross and a.grads_buf.mc_ptr and a.params_buf.mc_ptr
+                            and self.use_nvls and a.nbytes >= self.nvls_min_bytes)
+                if use_nvls:
+                    # the switch reduces the gradient shard and multicasts the new parameters
+                    K.call('kfb_ssgd_fused_step_nvls', comm.cstruct, a.grads_buf.mc_ptr, a.code,
+                           a.params_buf.mc_ptr, a.code, a.master.data_ptr(), a.mom.data_ptr(), a.count,
+                           float(step_scale), C.byref(h), ss_g.data_ptr() if ss_g is not None else None,
+                           min(blocks, 32), threads, K.stream_ptr())
+                    k += 1
+                    continue
                 if sync and comm.np > 1 and not comm.cross:
                     ga, _k1 = a.grads_buf.ptr_array()
                     pa, _k2 = a.params_buf.ptr_array()

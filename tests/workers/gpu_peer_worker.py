@@ -104,26 +104,31 @@ def check_fused_optimizers():
         g = torch.Generator().manual_seed(77 + 13 * r + step)
         return torch.randn(32, 64, generator=g).to(dev), torch.randint(0, 16, (32, ), generator=g).to(dev)
 
-    # S-SGD fused == single process on the concatenated batch
-    m = make()
-    opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.1, momentum=0.9), m.named_parameters())
-    ref = make()
-    ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
-    for step in range(4):
-        x, y = batch(rank, step)
-        opt.zero_grad(set_to_none=True)
-        torch.nn.functional.cross_entropy(m(x), y).backward()
-        opt.step()
-        ropt.zero_grad()
-        xs, ys = zip(*[batch(r, step) for r in range(np_)])
-        torch.nn.functional.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
-        ropt.step()
-    torch.cuda.synchronize()
-    for p, q in zip(m.parameters(), ref.parameters()):
-        assert torch.allclose(p, q, rtol=1e-4, atol=1e-5), (p - q).abs().max()
-    opt.consolidate()
+    # S-SGD fused == single process on the concatenated batch (P2P kernel, then the NVLS kernel)
+    def fused_ssgd_matches_oracle(nvls_min):
+        m = make()
+        opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.1, momentum=0.9), m.named_parameters())
+        opt.nvls_min_bytes = nvls_min
+        ref = make()
+        ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+        for step in range(4):
+            x, y = batch(rank, step)
+            opt.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+            ropt.zero_grad()
+            xs, ys = zip(*[batch(r, step) for r in range(np_)])
+            torch.nn.functional.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
+            ropt.step()
+        torch.cuda.synchronize()
+        for p, q in zip(m.parameters(), ref.parameters()):
+            assert torch.allclose(p, q, rtol=1e-4, atol=1e-5), (nvls_min, (p - q).abs().max())
+        opt.consolidate()
+
+    fused_ssgd_matches_oracle(1 << 40)  # peer load/store kernel
+    fused_ssgd_matches_oracle(0)        # NVLS kernel (when multicast is available)
     if rank == 0:
-        print('fused S-SGD ok', flush=True)
+        print('fused S-SGD ok (p2p + nvls)', flush=True)
 
     # generic optimizer (Adam) through GradSync, plain and overlapped
     for overlap in (False, True):
