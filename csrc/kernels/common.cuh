@@ -262,6 +262,10 @@ __device__ __forceinline__ float block_sum(float v, float *smem32)
 // resize the pads and epochs are re-created from zero (new membership = new
 // epoch space), which is what the reference's connection token did
 // (/root/reference/srcs/go/rchannel/connection/connection.go:77-87).
+#ifndef KFB_BARRIER_TIMEOUT_NS
+#define KFB_BARRIER_TIMEOUT_NS 120000000000ull  // 120 s: far above any legitimate skew between ranks
+#endif
+
 struct PeerPads {
     uint32_t *pad[KFB_MAX_RANKS];  // pad[r] = rank r's pad (peer mapped)
 };
@@ -287,7 +291,24 @@ peer_barrier(const PeerPads &pads, uint32_t *local_epoch, int rank, int np,
         __threadfence_system();
         st_release_sys(pad_flag(pads.pad[threadIdx.x], block, rank), e);
         const uint32_t *mine = pad_flag(pads.pad[rank], block, threadIdx.x);
-        while ((int32_t)(ld_acquire_sys(mine) - e) < 0) { __nanosleep(20); }
+        // A peer that died (or a collective issued by only some ranks) must not
+        // wedge the GPU forever: after KFB_BARRIER_TIMEOUT_NS the kernel traps,
+        // which surfaces as a CUDA error in the host process instead of a hang.
+        unsigned long long t0 = 0;
+        unsigned spins        = 0;
+        while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+            __nanosleep(20);
+            if ((++spins & 0x3fffu) == 0) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > KFB_BARRIER_TIMEOUT_NS) {
+                    printf("kungfu_b200: rank %d gave up waiting for rank %d at a peer barrier (block %d, epoch %u)\n",
+                           rank, (int)threadIdx.x, block, e);
+                    __trap();
+                }
+            }
+        }
     }
     __syncthreads();
     if (threadIdx.x == 0) local_epoch[block] += 1;

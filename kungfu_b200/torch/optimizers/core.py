@@ -65,6 +65,15 @@ class GradSync(object):
         self._arenas = [Arena(comm, groups[d], d, need_grads=True, repoint=False)
                         for d in sorted(groups, key=str)]
         self._comm_id = id(comm)
+        # The bucket layout fixes the order in which gradients are reduced. The
+        # reference negotiated that order at run time (rank 0's arrival order was
+        # broadcast and adopted); here it is static, and every rank proves it holds
+        # the same layout before the first collective.
+        import hashlib
+        layout = '|'.join('%s:%s:%s' % (n, tuple(p.shape), p.dtype) for n, p in self.cuda_named)
+        digest = torch.tensor(list(hashlib.sha1(layout.encode()).digest()), dtype=torch.uint8)
+        if kfpy.current_cluster_size() > 1 and not tops.consensus(digest, name='kungfu::grad-layout'):
+            raise RuntimeError('workers registered different parameter lists (names / shapes / order differ)')
         dev = comm.device
         k = max(1, len(self._arenas))
         self._ss_local = torch.zeros(k, dtype=torch.float32, device=dev)
