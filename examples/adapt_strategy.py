@@ -7,6 +7,11 @@ Reference: /root/reference/experimental/adapt_strategy/adapt_strategy.py:26-28,1
 (monitor=True S-SGD, calc_stats/log_stats each step, check_interference after
 step 4, on consensus set_tree([1]*np) = star rooted at rank 1). On GPUs the same
 loop can drive kungfu_b200.parallel.planner.VariantChooser.check_interference."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from a source checkout
+
 import torch
 
 import kungfu_b200.python as kfpy

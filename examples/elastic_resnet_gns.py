@@ -7,6 +7,11 @@ GPUs when the gradient-noise-scale monitor says larger batches still pay off.
 Surviving workers are never restarted: after each resize the device layer
 re-maps peer memory for the new membership, joiners receive the step counter
 and the model from rank 0."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from a source checkout
+
 import argparse
 import time
 

@@ -4,6 +4,11 @@
 
 Reference: /root/reference/examples/mnist_elastic_policy/{main.py,elastic_policy.py,run.sh}
 (resizes at steps {10:2, 20:3, 30:4, 40:1})."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from a source checkout
+
 import torch
 import torch.nn.functional as F
 

@@ -9,6 +9,11 @@ User-side conventions of the reference's examples
 the cluster size, shard the data by (rank, size), broadcast the initial model,
 checkpoint on rank 0 only. Data: real MNIST idx files under --data-dir if present,
 otherwise a synthetic MNIST-shaped set (no network here)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # run from a source checkout
+
 import argparse
 
 import torch

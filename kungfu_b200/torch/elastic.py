@@ -37,15 +37,18 @@ class ElasticState(object):
         self.model, self.optimizer = model, optimizer
         self.step = 0
         self.trained_samples = 0
+        self.last_resize_step = 0
         self.max_step = max_step
         self.profiler = ResizeProfiler()
         self.stopped = False
         self.sync()
 
     def sync(self):
-        v = torch.tensor([self.step, self.trained_samples], dtype=torch.int64)
+        # everything a policy may base a collective decision on must be equal on
+        # survivors and joiners: step, samples AND the step of the last resize
+        v = torch.tensor([self.step, self.trained_samples, self.last_resize_step], dtype=torch.int64)
         v = tops.all_reduce_fn(v, 'max', name='kungfu::elastic-progress')
-        self.step, self.trained_samples = int(v[0]), int(v[1])
+        self.step, self.trained_samples, self.last_resize_step = int(v[0]), int(v[1]), int(v[2])
         if self.optimizer is not None and hasattr(self.optimizer, 'rebuild'):
             # move the flat arenas (parameters, gradients) into the new
             # membership's symmetric memory before anything is broadcast into them
@@ -68,6 +71,7 @@ class ElasticState(object):
             # fused optimizers shard their fp32 state over the ranks: make it whole
             # on every (old) member while all of them are still here
             self.optimizer.consolidate()
+        self.last_resize_step = self.step
         changed, detached = kfpy.resize_cluster(new_size)
         if detached:
             self.stopped = True

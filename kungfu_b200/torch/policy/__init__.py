@@ -102,7 +102,9 @@ class NoiseScaleElasticPolicy(BasePolicy):
 
     def after_step(self, state):
         np_ = kfpy.current_cluster_size()
-        if state.step % self.check_every or state.step - self._last_resize < self.cooldown or np_ >= self.max_size:
+        # decisions use only state that ElasticState keeps identical on every worker
+        # (a joiner's fresh policy object must not disagree with the survivors')
+        if state.step % self.check_every or state.step - state.last_resize_step < self.cooldown or np_ >= self.max_size:
             return
         ns = getattr(self.opt, 'noise_scale', None)
         # single worker: no cross-worker norm yet, grow once to start measuring
