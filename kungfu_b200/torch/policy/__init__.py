@@ -108,7 +108,9 @@ class NoiseScaleElasticPolicy(BasePolicy):
             return
         ns = getattr(self.opt, 'noise_scale', None)
         # single worker: no cross-worker norm yet, grow once to start measuring
-        grow = np_ == 1 or (ns is not None and float(ns) > self.bs * np_)
+        # B_noise = S/G. A non-positive estimate means the gradient signal is still
+        # below the noise floor at this batch size: larger batches help as well.
+        grow = np_ == 1 or (ns is not None and (float(ns) <= 0 or float(ns) > self.bs * np_))
         # every rank must take the same decision
         from ..ops import collective as tops
         import torch
