@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument('--image-size', type=int, default=224)
     ap.add_argument('--no-graph', action='store_true', help='eager launches instead of a captured CUDA graph')
     ap.add_argument('--fused-bn', type=int, default=int(os.environ.get('KUNGFU_FUSED_BN', '1')))
+    ap.add_argument('--s2d-stem', type=int, default=int(os.environ.get('KUNGFU_S2D_STEM', '1')),
+                    help='evaluate the 7x7/2 stem as a 4x4 conv over a space-to-depth input (same maths)')
     ap.add_argument('--momentum', type=float, default=0.0)
     ap.add_argument('--skip-e2e', action='store_true')
     return ap.parse_args()
@@ -133,7 +135,7 @@ def main():
     torch.backends.cudnn.benchmark = True
 
     torch.manual_seed(1234)
-    model = getattr(models, args.model)(fused_bn=bool(args.fused_bn))
+    model = getattr(models, args.model)(fused_bn=bool(args.fused_bn), s2d_stem=bool(args.s2d_stem))
     model = models.to_b200_layout(model.to(dev), torch.bfloat16)
     model.train()
     opt = FusedSGD(model.parameters(), lr=0.01 * np_, momentum=args.momentum)
@@ -258,7 +260,7 @@ def main():
             'vs_baseline': value / BASELINE_IMG_S, 'dtype': 'bf16', 'data': 'synthetic', 'impl': 'ours',
             'config': {'model': args.model, 'global_batch': B * np_, 'per_gpu_batch': B, 'seq_len': None,
                        'image_size': S, 'parallelism': 'dp%d' % np_, 'optimizer': 'SynchronousSGDOptimizer(FusedSGD)',
-                       'cuda_graph': not args.no_graph, 'fused_bn': bool(args.fused_bn),
+                       'cuda_graph': not args.no_graph, 'fused_bn': bool(args.fused_bn), 's2d_stem': bool(args.s2d_stem),
                        'l2': 'working set per step (activations, bs%d) exceeds the 126 MB L2' % B,
                        'baseline': 'KungFu S-SGD ResNet-50 global batch 4096 on 16xV100 = 5507 img/s'},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': gpu_launches, 'loss': float(loss_dev),

@@ -116,6 +116,15 @@ int kf_monitored_all_reduce(kf_peer *p, const void *send, void *recv, int64_t co
     return done(p, s->monitored_all_reduce(ws(send, recv, count, dtype, op, name)));
 }
 
+int kf_all_reduce_with(kf_peer *p, const int32_t *tree, int tree_len, const void *send, void *recv, int64_t count,
+                       int dtype, int op, const char *name)
+{
+    KF_CHECK_DTYPE(dtype);
+    std::vector<int32_t> forest;
+    if (tree && tree_len > 0) forest.assign(tree, tree + tree_len);
+    return done(p, p->peer->session()->all_reduce_with(forest, ws(send, recv, count, dtype, op, name)));
+}
+
 int kf_cross_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
 {
     KF_CHECK_DTYPE(dtype);

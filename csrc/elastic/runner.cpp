@@ -4,12 +4,14 @@
 #include <fcntl.h>
 #include <ifaddrs.h>
 #include <net/if.h>
+#include <netdb.h>
 #include <signal.h>
 #include <sys/prctl.h>
 #include <sys/stat.h>
 #include <sys/wait.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
 #include <condition_variable>
 #include <cstring>
@@ -172,6 +174,42 @@ std::string run_usage()
            "  -t0 TS -logfile F -logdir D -q -delay DUR\n";
 }
 
+// "-H node1:4,node2:4" may name hosts: each name is resolved to its IPv4 and
+// kept as the public address (/root/reference/srcs/go/kungfu/runner/discovery.go:157-215).
+static bool resolve_host_names(const std::string &list, std::string *out, std::string *err)
+{
+    out->clear();
+    size_t pos = 0;
+    while (pos <= list.size()) {
+        size_t comma = list.find(',', pos);
+        if (comma == std::string::npos) comma = list.size();
+        std::string spec = list.substr(pos, comma - pos);
+        pos              = comma + 1;
+        if (spec.empty()) continue;
+        const size_t colon     = spec.find(':');
+        const std::string host = spec.substr(0, colon);
+        uint32_t ip;
+        if (!parse_ipv4(host, &ip)) {
+            addrinfo hints, *res = nullptr;
+            memset(&hints, 0, sizeof(hints));
+            hints.ai_family = AF_INET;
+            if (getaddrinfo(host.c_str(), nullptr, &hints, &res) != 0 || !res) {
+                *err = "cannot resolve host '" + host + "' in -H";
+                return false;
+            }
+            ip = ntohl(((sockaddr_in *)res->ai_addr)->sin_addr.s_addr);
+            freeaddrinfo(res);
+            std::string rest = colon == std::string::npos ? ":1" : spec.substr(colon);
+            // ip:slots:public (public defaults to the name the user gave)
+            if (std::count(rest.begin(), rest.end(), ':') < 2) rest += ":" + host;
+            spec = format_ipv4(ip) + rest;
+        }
+        if (!out->empty()) *out += ",";
+        *out += spec;
+    }
+    return true;
+}
+
 static bool parse_bool(const std::string &v) { return v == "1" || v == "true" || v == "True" || v == "TRUE" || v.empty(); }
 
 bool parse_run_flags(int argc, char **argv, RunFlags *f, std::string *err)
@@ -246,9 +284,13 @@ bool parse_run_flags(int argc, char **argv, RunFlags *f, std::string *err)
         std::string text;
         if (!open_url(f->hostfile, &text, err)) return false;
         if (!parse_hostfile(text, &f->hosts, err)) return false;
-    } else if (!parse_host_list(f->host_list, &f->hosts)) {
-        *err = "bad -H " + f->host_list;
-        return false;
+    } else {
+        std::string resolved;
+        if (!resolve_host_names(f->host_list, &resolved, err)) return false;
+        if (!parse_host_list(resolved, &f->hosts)) {
+            *err = "bad -H " + f->host_list;
+            return false;
+        }
     }
     return true;
 }

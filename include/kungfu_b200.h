@@ -283,6 +283,11 @@ int kfb_mc_add_device(kfb_mc_object *mc);
 int kfb_mc_bind(kfb_mc_object *mc, kfb_symm_block *mem, void **mc_ptr_out);
 int kfb_mc_free(kfb_mc_object *mc);
 size_t kfb_symm_granularity(int device, int multicast);
+/* 1 if the device can take part in multicast objects (NVLS), else 0 */
+int kfb_multicast_supported(int device);
+/* close a descriptor obtained from kfb_symm_export_fd / kfb_mc_create or
+ * received from a peer, once it has been imported */
+int kfb_close_fd(int fd);
 
 /* ---- model kernels (channels-last bf16 training blocks) ------------------- */
 

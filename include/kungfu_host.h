@@ -36,6 +36,10 @@ int kf_barrier(kf_peer *p);
 int kf_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
 int kf_monitored_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op,
                             const int32_t *tree, int tree_len, const char *name);
+/* one all-reduce along the given tree (father array; empty = active strategy) without installing it
+ * (Session.AllReduceWith, /root/reference/srcs/go/kungfu/session/allreduce.go:15-27) */
+int kf_all_reduce_with(kf_peer *p, const int32_t *tree, int tree_len, const void *send, void *recv, int64_t count,
+                       int dtype, int op, const char *name);
 int kf_cross_all_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
 int kf_reduce(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
 int kf_broadcast(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);

@@ -92,10 +92,11 @@ class _Downsample(nn.Sequential):
 
 
 class ResNet(nn.Module):
-    def __init__(self, block, layers, num_classes=1000, fused_bn=False, zero_init_residual=False):
+    def __init__(self, block, layers, num_classes=1000, fused_bn=False, zero_init_residual=False, s2d_stem=False):
         super().__init__()
         self.inplanes = 64
         self.fused_bn = fused_bn
+        self.s2d_stem = s2d_stem
         self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
         self.bn1 = BNAct(64, relu=True, fused=fused_bn)
         from ..ops.pool import MaxPool3x3s2
@@ -126,8 +127,23 @@ class ResNet(nn.Module):
             layers.append(block(self.inplanes, planes, fused=self.fused_bn))
         return nn.Sequential(*layers)
 
+    def _stem(self, x):
+        """conv1 (7x7, stride 2, 3 input channels). With ``s2d_stem`` the same
+        convolution is evaluated as a 4x4 stride-1 convolution over a 2x2
+        space-to-depth view of the padded input (12 channels): identical maths
+        and the same [64,3,7,7] parameter, but a shape tensor cores like far
+        better than C_in = 3."""
+        if not self.s2d_stem or x.shape[2] % 2 or x.shape[3] % 2:
+            return self.conv1(x)
+        w = self.conv1.weight
+        N, C, H, W = x.shape
+        Hh, Wh = (H + 6) // 2, (W + 6) // 2
+        xs = F.pad(x, (3, 3, 3, 3)).view(N, C, Hh, 2, Wh, 2).permute(0, 3, 5, 1, 2, 4).reshape(N, 4 * C, Hh, Wh)
+        ws = F.pad(w, (0, 1, 0, 1)).view(w.shape[0], C, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4).reshape(w.shape[0], 4 * C, 4, 4)
+        return F.conv2d(xs.contiguous(memory_format=torch.channels_last), ws.contiguous(memory_format=torch.channels_last))
+
     def forward(self, x):
-        x = self.maxpool(self.bn1(self.conv1(x)))
+        x = self.maxpool(self.bn1(self._stem(x)))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         if self.fused_bn:
             from ..ops.pool import global_avg_pool
