@@ -24,6 +24,10 @@
 namespace kfb {
 
 constexpr int BN_THREADS   = 256;
+// CTAs per SM the backward kernels are compiled for (4 => at most 64 registers)
+#ifndef KFB_BN_BWD_OCC
+#define KFB_BN_BWD_OCC 4
+#endif
 constexpr int BN_MAX_BLOCKS = 592;  // 4 CTAs per SM
 
 template <typename T> struct Ld8 {
@@ -224,7 +228,7 @@ __global__ void __launch_bounds__(BN_THREADS)
 // ---- backward --------------------------------------------------------------------------
 // partial[b][0][c] = sum dz, partial[b][1][c] = sum dz * xhat
 template <typename T, bool RELU>
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, KFB_BN_BWD_OCC)
     k_bn_bwd_stats(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint8_t *__restrict__ mask,
                    const float *__restrict__ mean, const float *__restrict__ invstd, long long rows, int C,
                    float *__restrict__ partial)
@@ -294,7 +298,8 @@ __global__ void __launch_bounds__(FIN_TX *FIN_TY)
 }
 
 template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(BN_THREADS)
+// (the residual variant needs ~75 registers: capping it at 64 spills and measures slower)
+__global__ void __launch_bounds__(BN_THREADS, RES ? 3 : KFB_BN_BWD_OCC)
     k_bn_bwd_apply(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint8_t *__restrict__ mask,
                    const float *__restrict__ weight, const float *__restrict__ mean,
                    const float *__restrict__ invstd, const float *__restrict__ sums, uint4 *__restrict__ dx,

@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cstdio>
+
 #include "../../include/kungfu_b200.h"
 
 namespace kfb {
