@@ -35,6 +35,7 @@ ap.add_argument('--image-size', type=int, default=224)
 ap.add_argument('--steps', type=int, default=20)
 ap.add_argument('--warmup', type=int, default=5)
 ap.add_argument('--fused-bn', type=int, default=1)
+ap.add_argument('--fused-linear', type=int, default=0, help='BERT: tcgen05 linear layers with fused bias/GELU')
 ap.add_argument('--graph', action='store_true', help='capture the step in a CUDA graph (not for pair averaging)')
 ap.add_argument('--momentum', type=float, default=0.9)
 args = ap.parse_args()
@@ -48,7 +49,7 @@ is_bert = args.model.startswith('bert')
 B = args.batch_size
 
 if is_bert:
-    model = getattr(models, args.model)().to(dev).to(torch.bfloat16)
+    model = getattr(models, args.model)(fused_linear=bool(args.fused_linear)).to(dev).to(torch.bfloat16)
     ids = torch.randint(0, 30522, (B, args.seq_len), device=dev)
     labels = ids.clone()
     labels[torch.rand(B, args.seq_len, device=dev) > 0.15] = -100

@@ -1,0 +1,521 @@
+// Y = act(X . W^T + bias) on the 5th-generation tensor cores (sm_100a).
+//
+// X [M,K] and W [N,K] are bf16 with K contiguous (torch.nn.Linear's layout), so
+// both operands are "K-major" and no transpose is ever materialised.
+//
+//   warp 0      TMA producer: cp.async.bulk.tensor (128B swizzle) of a 128x64 X
+//               tile and a 256x64 W tile per stage, 4 stages of 48 KiB
+//   warp 1      MMA issuer: one thread issues tcgen05.mma (128x256x16, bf16 ->
+//               fp32) with the accumulator in tensor memory; tcgen05.commit
+//               hands smem stages back to the producer and accumulators to the
+//               epilogue through mbarriers
+//   warp 2      allocates / frees the 512 TMEM columns (two 128x256 accumulators)
+//   warps 4-11  epilogue: tcgen05.ld the accumulator, + bias, activation, bf16
+//               pack, 16-byte stores; runs while the tensor cores are already
+//               on the next tile (double-buffered accumulators)
+//
+// The kernel is persistent (one CTA per SM, static tile schedule). The fused
+// epilogue removes the separate bias / GELU passes over the [M,N] activation;
+// with `z` given the pre-activation is stored too (what the backward needs).
+//
+// The reference has no counterpart: its models come from TensorFlow/Keras and
+// its own native code is communication only. This kernel serves the BERT
+// benchmark model of this repo (kungfu_b200/models/bert.py).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <mutex>
+
+#include "kungfu_b200.h"
+
+namespace kfb
+{
+void set_last_error(const char *fmt, ...);  // collectives.cu
+
+constexpr int LT_BM     = 128;
+constexpr int LT_BN     = 256;
+constexpr int LT_BK     = 64;  // 64 bf16 = 128 bytes = one swizzle row
+constexpr int LT_UMMA_K = 16;
+constexpr int LT_STAGES = 4;
+constexpr int LT_A_BYTES     = LT_BM * LT_BK * 2;
+constexpr int LT_B_BYTES     = LT_BN * LT_BK * 2;
+constexpr int LT_STAGE_BYTES = LT_A_BYTES + LT_B_BYTES;
+constexpr int LT_EPI_WARPS   = 8;
+constexpr int LT_FIRST_EPI_WARP = 4;
+constexpr int LT_THREADS     = (LT_FIRST_EPI_WARP + LT_EPI_WARPS) * 32;
+constexpr int LT_TMEM_COLS   = 2 * LT_BN;
+constexpr int LT_NUM_BARS    = 2 * LT_STAGES + 4;
+constexpr int LT_SMEM_BYTES  = 1024 + LT_STAGES * LT_STAGE_BYTES + LT_NUM_BARS * 8 + 16;
+
+// ---- PTX wrappers ----------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok;
+}
+
+// Bounded wait: a pipeline bug must end in a trap, not in a wedged GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000LL) {
+            printf("[kungfu_b200] linear_tc: mbarrier wait timed out (block %d thread %d)\n", blockIdx.x,
+                   threadIdx.x);
+            __trap();
+        }
+    }
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            dst),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// tcgen05.commit: the mbarrier gets one arrival once every MMA issued so far by
+// this thread has finished (implies fence::before_thread_sync).
+__device__ __forceinline__ void tc_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// D[tmem] (+)= A[smem] . B[smem]^T, 128 x N x 16, bf16 inputs, fp32 accumulate.
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets row (lane base + t).
+__device__ __forceinline__ void tc_ld_32x32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+          "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+          "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor for a K-major bf16 tile whose rows are 128
+// bytes (64 elements) under the 128-byte swizzle TMA wrote: 8-row groups are
+// 1024 bytes apart (stride byte offset), the leading byte offset is unused for
+// swizzled K-major tiles (set to 1), descriptor version 1, layout type 2.
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFF);
+    d |= static_cast<uint64_t>(1) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+
+// Instruction descriptor: D fp32, A/B bf16, both K-major, M=128, N=LT_BN.
+constexpr uint32_t LT_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(LT_BN >> 3) << 17) |
+                              (static_cast<uint32_t>(LT_BM >> 4) << 24);
+
+__device__ __forceinline__ float gelu_erf(float z)
+{
+    // 0.5 z (1 + erf(z / sqrt 2)); erf by Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7,
+    // far below the bf16 output's resolution)
+    const float x  = fabsf(z) * 0.70710678f;
+    const float t  = __frcp_rn(fmaf(0.3275911f, x, 1.0f));
+    float p        = fmaf(1.061405429f, t, -1.453152027f);
+    p              = fmaf(p, t, 1.421413741f);
+    p              = fmaf(p, t, -0.284496736f);
+    p              = fmaf(p, t, 0.254829592f);
+    const float e  = 1.0f - p * t * __expf(-x * x);
+    return 0.5f * z * (1.0f + copysignf(e, z));
+}
+
+template <int ACT> __device__ __forceinline__ float apply_act(float z)
+{
+    if (ACT == KFB_ACT_GELU) return gelu_erf(z);
+    if (ACT == KFB_ACT_RELU) return fmaxf(z, 0.0f);
+    return z;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
+{
+    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// ---- the kernel ------------------------------------------------------------------
+
+template <int ACT, bool SAVE_Z>
+__global__ void __launch_bounds__(LT_THREADS, 1)
+    k_linear_act(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                 const void *__restrict__ bias, int bias_bf16, __nv_bfloat16 *__restrict__ y,
+                 __nv_bfloat16 *__restrict__ z, int M, int N, int K)
+{
+    extern __shared__ uint8_t lt_smem_raw[];
+    // the 128-byte swizzle pattern is a function of address bits [4,10): tiles need 1024-byte alignment
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(lt_smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t *bars      = reinterpret_cast<uint64_t *>(smem + LT_STAGES * LT_STAGE_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + LT_NUM_BARS);
+
+    const uint32_t smem_base  = smem_u32(smem);
+    const uint32_t bar_base   = smem_u32(bars);
+    auto full_bar             = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar            = [&](int s) { return bar_base + 8u * (LT_STAGES + s); };
+    auto tmem_full_bar        = [&](int a) { return bar_base + 8u * (2 * LT_STAGES + a); };
+    auto tmem_empty_bar       = [&](int a) { return bar_base + 8u * (2 * LT_STAGES + 2 + a); };
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int num_m     = (M + LT_BM - 1) / LT_BM;
+    const int num_n     = (N + LT_BN - 1) / LT_BN;
+    const int num_tiles = num_m * num_n;
+    const int num_kb    = (K + LT_BK - 1) / LT_BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tm_x)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tm_w)) : "memory");
+    } else if (warp == 1 && lane == 0) {
+        for (int s = 0; s < LT_STAGES; ++s) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tmem_full_bar(a), 1);
+            mbar_init(tmem_empty_bar(a), LT_EPI_WARPS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    } else if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"(LT_TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % num_m) * LT_BM;
+            const int n0 = (tile / num_m) * LT_BN;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(empty_bar(stage), phase ^ 1);
+                const uint32_t a_smem = smem_base + stage * LT_STAGE_BYTES;
+                mbar_arrive_expect_tx(full_bar(stage), LT_STAGE_BYTES);
+                tma_load_2d(a_smem, &tm_x, full_bar(stage), kb * LT_BK, m0);
+                tma_load_2d(a_smem + LT_A_BYTES, &tm_w, full_bar(stage), kb * LT_BK, n0);
+                if (++stage == LT_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer (a single thread) =====
+        int stage = 0, accum = 0;
+        uint32_t phase = 0, accum_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            mbar_wait(tmem_empty_bar(accum), accum_phase ^ 1);  // the epilogue has drained this accumulator
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + accum * LT_BN;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(full_bar(stage), phase);  // TMA has landed this stage
+                tc_fence_after();
+                const uint32_t a_smem = smem_base + stage * LT_STAGE_BYTES;
+                const uint64_t a_desc = make_kmajor_sw128_desc(a_smem);
+                const uint64_t b_desc = make_kmajor_sw128_desc(a_smem + LT_A_BYTES);
+#pragma unroll
+                for (int k = 0; k < LT_BK / LT_UMMA_K; ++k) {
+                    // advancing 16 elements (32 bytes) along K inside the swizzle row: +2 in the >>4 address field
+                    tc_mma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, LT_IDESC, (kb | k) != 0);
+                }
+                tc_commit(empty_bar(stage));  // stage reusable once these MMAs have read it
+                if (++stage == LT_STAGES) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+            tc_commit(tmem_full_bar(accum));  // accumulator complete
+            if (++accum == 2) {
+                accum = 0;
+                accum_phase ^= 1;
+            }
+        }
+    } else if (warp >= LT_FIRST_EPI_WARP) {
+        // ===== epilogue: TMEM -> registers -> bias/activation -> global =====
+        const int quarter = warp & 3;                        // the TMEM lanes this warp may read: 32*(warp%4)..+31
+        const int half    = (warp - LT_FIRST_EPI_WARP) >> 2;  // which 128 of the 256 accumulator columns
+        int accum = 0;
+        uint32_t accum_phase = 0;
+        const float *bias_f          = reinterpret_cast<const float *>(bias);
+        const __nv_bfloat16 *bias_h  = reinterpret_cast<const __nv_bfloat16 *>(bias);
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0  = (tile % num_m) * LT_BM;
+            const int n0  = (tile / num_m) * LT_BN;
+            const int row = m0 + quarter * 32 + lane;
+            mbar_wait(tmem_full_bar(accum), accum_phase);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < LT_BN / 2 / 32; ++c) {
+                const int col0 = half * (LT_BN / 2) + c * 32;
+                const int n    = n0 + col0;
+                if (n >= N) break;  // warp-uniform
+                uint32_t v[32];
+                tc_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + accum * LT_BN + col0, v);
+                float b_lane = 0.0f;
+                if (bias != nullptr && n + lane < N)
+                    b_lane = bias_bf16 ? __bfloat162float(bias_h[n + lane]) : bias_f[n + lane];
+                tc_ld_wait();
+                float f[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + __shfl_sync(0xffffffffu, b_lane, j);
+                if (row < M) {
+                    const size_t off = static_cast<size_t>(row) * N + n;
+                    if (n + 32 <= N) {
+                        if (SAVE_Z) {
+                            uint4 *zp = reinterpret_cast<uint4 *>(z + off);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q)
+                                zp[q] = make_uint4(pack_bf16(f[8 * q], f[8 * q + 1]), pack_bf16(f[8 * q + 2], f[8 * q + 3]),
+                                                   pack_bf16(f[8 * q + 4], f[8 * q + 5]),
+                                                   pack_bf16(f[8 * q + 6], f[8 * q + 7]));
+                        }
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) f[j] = apply_act<ACT>(f[j]);
+                        uint4 *yp = reinterpret_cast<uint4 *>(y + off);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            yp[q] = make_uint4(pack_bf16(f[8 * q], f[8 * q + 1]), pack_bf16(f[8 * q + 2], f[8 * q + 3]),
+                                               pack_bf16(f[8 * q + 4], f[8 * q + 5]),
+                                               pack_bf16(f[8 * q + 6], f[8 * q + 7]));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            if (n + j < N) {
+                                if (SAVE_Z) z[off + j] = __float2bfloat16(f[j]);
+                                y[off + j] = __float2bfloat16(apply_act<ACT>(f[j]));
+                            }
+                        }
+                    }
+                }
+            }
+            // hand the accumulator back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty_bar(accum));
+            if (++accum == 2) {
+                accum = 0;
+                accum_phase ^= 1;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(LT_TMEM_COLS)
+                     : "memory");
+    }
+}
+
+// dz = dy * act'(z), one pass (the backward of the fused epilogue)
+template <int ACT>
+__global__ void __launch_bounds__(256) k_act_bwd(const uint4 *__restrict__ dy, const uint4 *__restrict__ z,
+                                                  uint4 *__restrict__ dz, size_t n8)
+{
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n8;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        uint4 a = dy[i], b = z[i], o;
+        const __nv_bfloat162 *ap = reinterpret_cast<const __nv_bfloat162 *>(&a);
+        const __nv_bfloat162 *bp = reinterpret_cast<const __nv_bfloat162 *>(&b);
+        __nv_bfloat162 *op       = reinterpret_cast<__nv_bfloat162 *>(&o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float2 g = __bfloat1622float2(ap[j]), v = __bfloat1622float2(bp[j]), r;
+            if (ACT == KFB_ACT_GELU) {
+                // d/dz [z Phi(z)] = Phi(z) + z phi(z)
+                const float px = 0.5f * (1.0f + erff(v.x * 0.70710678f)), py = 0.5f * (1.0f + erff(v.y * 0.70710678f));
+                r.x = g.x * (px + v.x * 0.39894228f * __expf(-0.5f * v.x * v.x));
+                r.y = g.y * (py + v.y * 0.39894228f * __expf(-0.5f * v.y * v.y));
+            } else {
+                r.x = v.x > 0.0f ? g.x : 0.0f;
+                r.y = v.y > 0.0f ? g.y : 0.0f;
+            }
+            op[j] = __floats2bfloat162_rn(r.x, r.y);
+        }
+        dz[i] = o;
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// [rows, K] bf16, K contiguous; box = 64 (K) x box_rows, 128-byte swizzle, zero fill out of bounds
+static bool make_kmajor_map(CUtensorMap *map, const void *base, int rows, int K, int box_rows)
+{
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    cuuint64_t dims[2]    = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(K) * 2};
+    cuuint32_t box[2]     = {static_cast<cuuint32_t>(LT_BK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2]    = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int ACT, bool SAVE_Z>
+static int launch_linear(const CUtensorMap &tx, const CUtensorMap &tw, const void *bias, int bias_bf16, void *y, void *z,
+                         int M, int N, int K, int grid, cudaStream_t stream)
+{
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(once, [] {
+        attr_err = cudaFuncSetAttribute(k_linear_act<ACT, SAVE_Z>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        LT_SMEM_BYTES);
+    });
+    if (attr_err != cudaSuccess) return static_cast<int>(attr_err);
+    k_linear_act<ACT, SAVE_Z><<<grid, LT_THREADS, LT_SMEM_BYTES, stream>>>(
+        tx, tw, bias, bias_bf16, static_cast<__nv_bfloat16 *>(y), static_cast<__nv_bfloat16 *>(z), M, N, K);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) set_last_error("linear_act launch: %s", cudaGetErrorString(e));
+    return static_cast<int>(e);
+}
+}  // namespace kfb
+
+extern "C" int kfb_linear_act(const void *x, const void *w, const void *bias, int bias_dtype, void *y, void *z, int M,
+                              int N, int K, int act, void *stream_)
+{
+    using namespace kfb;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    // TMA needs 16-byte global strides; the epilogue's vector stores need 16-byte rows
+    if ((K % 8) != 0 || (N % 8) != 0) {
+        set_last_error("linear_act: K and N must be multiples of 8 (got K=%d N=%d)", K, N);
+        return static_cast<int>(cudaErrorInvalidValue);
+    }
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(y) |
+         reinterpret_cast<uintptr_t>(z)) & 15) {
+        set_last_error("linear_act: x, w, y, z must be 16-byte aligned");
+        return static_cast<int>(cudaErrorMisalignedAddress);
+    }
+    if (bias && bias_dtype != KFB_F32 && bias_dtype != KFB_BF16) {
+        set_last_error("linear_act: bias must be f32 or bf16");
+        return static_cast<int>(cudaErrorInvalidValue);
+    }
+    CUtensorMap tx, tw;
+    if (!make_kmajor_map(&tx, x, M, K, LT_BM) || !make_kmajor_map(&tw, w, N, K, LT_BN)) {
+        set_last_error("linear_act: cuTensorMapEncodeTiled failed (M=%d N=%d K=%d)", M, N, K);
+        return static_cast<int>(cudaErrorNotSupported);
+    }
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int tiles = ((M + LT_BM - 1) / LT_BM) * ((N + LT_BN - 1) / LT_BN);
+    const int grid  = tiles < sms ? tiles : sms;
+    const int bb    = bias_dtype == KFB_BF16;
+    const bool sz   = z != nullptr;
+    switch (act) {
+    case KFB_ACT_NONE: return launch_linear<KFB_ACT_NONE, false>(tx, tw, bias, bb, y, nullptr, M, N, K, grid, stream);
+    case KFB_ACT_GELU:
+        return sz ? launch_linear<KFB_ACT_GELU, true>(tx, tw, bias, bb, y, z, M, N, K, grid, stream)
+                  : launch_linear<KFB_ACT_GELU, false>(tx, tw, bias, bb, y, z, M, N, K, grid, stream);
+    case KFB_ACT_RELU:
+        return sz ? launch_linear<KFB_ACT_RELU, true>(tx, tw, bias, bb, y, z, M, N, K, grid, stream)
+                  : launch_linear<KFB_ACT_RELU, false>(tx, tw, bias, bb, y, z, M, N, K, grid, stream);
+    }
+    return static_cast<int>(cudaErrorInvalidValue);
+}
+
+extern "C" int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, int act, void *stream_)
+{
+    using namespace kfb;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (n == 0) return 0;
+    if (n % 8) return static_cast<int>(cudaErrorInvalidValue);
+    const size_t n8 = n / 8;
+    size_t want     = (n8 + 255) / 256;
+    const int grid  = static_cast<int>(want < 148 * 8 ? want : 148 * 8);
+    if (act == KFB_ACT_GELU)
+        k_act_bwd<KFB_ACT_GELU><<<grid, 256, 0, stream>>>(static_cast<const uint4 *>(dy), static_cast<const uint4 *>(z),
+                                                          static_cast<uint4 *>(dz), n8);
+    else if (act == KFB_ACT_RELU)
+        k_act_bwd<KFB_ACT_RELU><<<grid, 256, 0, stream>>>(static_cast<const uint4 *>(dy), static_cast<const uint4 *>(z),
+                                                          static_cast<uint4 *>(dz), n8);
+    else
+        return static_cast<int>(cudaErrorInvalidValue);
+    return static_cast<int>(cudaGetLastError());
+}

@@ -326,6 +326,23 @@ int kfb_gap_fwd(const void *x, void *y, int N, int HW, int C, int dtype,
 int kfb_gap_bwd(const void *dy, void *dx, int N, int HW, int C, int dtype,
                 void *stream);
 
+/* ---- tcgen05 linear layer (csrc/kernels/linear_tc.cu) ------------------------
+ * y[M,N] = act(x[M,K] . w[N,K]^T + bias[N]); x, w, y (and z) bf16 row-major,
+ * fp32 accumulation in tensor memory, operands staged by TMA. bias may be NULL,
+ * KFB_F32 or KFB_BF16. With z != NULL the pre-activation is stored as well
+ * (what kfb_act_bwd needs). K and N must be multiples of 8, pointers 16-byte
+ * aligned. No counterpart in the reference (its models are TensorFlow's). */
+enum kfb_act {
+    KFB_ACT_NONE = 0,
+    KFB_ACT_GELU = 1, /* erf form */
+    KFB_ACT_RELU = 2,
+};
+int kfb_linear_act(const void *x, const void *w, const void *bias, int bias_dtype,
+                   void *y, void *z, int M, int N, int K, int act, void *stream);
+/* dz = dy * act'(z), n bf16 elements (n % 8 == 0) */
+int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, int act,
+                void *stream);
+
 #ifdef __cplusplus
 }
 #endif

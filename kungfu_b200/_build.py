@@ -32,6 +32,7 @@ CUDA_SOURCES = [
     'csrc/kernels/optim.cu',
     'csrc/kernels/bn_act.cu',
     'csrc/kernels/pool.cu',
+    'csrc/kernels/linear_tc.cu',
     'csrc/device/symm.cu',
 ]
 HOST_LIB_DIRS = ['csrc/core', 'csrc/ctrl', 'csrc/elastic', 'csrc/capi']

@@ -15,20 +15,24 @@ import torch.nn.functional as F
 
 class BertConfig(object):
     def __init__(self, vocab_size=30522, hidden=768, layers=12, heads=12, intermediate=3072, max_pos=512,
-                 type_vocab=2, dropout=0.1, eps=1e-12):
+                 type_vocab=2, dropout=0.1, eps=1e-12, fused_linear=False):
         self.vocab_size, self.hidden, self.layers, self.heads = vocab_size, hidden, layers, heads
         self.intermediate, self.max_pos, self.type_vocab, self.dropout, self.eps = intermediate, max_pos, type_vocab, dropout, eps
+        # fused_linear: the FFN / projection layers run the tcgen05 kernel with the
+        # bias (+GELU) epilogue (kungfu_b200.ops.linear); same parameters either way
+        self.fused_linear = fused_linear
 
 
 class _Layer(nn.Module):
     def __init__(self, c):
         super().__init__()
+        from ..ops.linear import LinearAct
         self.heads = c.heads
-        self.qkv = nn.Linear(c.hidden, 3 * c.hidden)
-        self.proj = nn.Linear(c.hidden, c.hidden)
+        self.qkv = LinearAct(c.hidden, 3 * c.hidden, fused=c.fused_linear)
+        self.proj = LinearAct(c.hidden, c.hidden, fused=c.fused_linear)
         self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
-        self.fc1 = nn.Linear(c.hidden, c.intermediate)
-        self.fc2 = nn.Linear(c.intermediate, c.hidden)
+        self.fc1 = LinearAct(c.hidden, c.intermediate, act='gelu', fused=c.fused_linear)
+        self.fc2 = LinearAct(c.intermediate, c.hidden, fused=c.fused_linear)
         self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
         self.drop = c.dropout
 
@@ -38,7 +42,7 @@ class _Layer(nn.Module):
         a = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=self.drop if self.training else 0.0)
         a = a.transpose(1, 2).reshape(B, S, H)
         x = self.ln1(x + F.dropout(self.proj(a), self.drop, self.training))
-        h = self.fc2(F.gelu(self.fc1(x)))
+        h = self.fc2(self.fc1(x))  # fc1 applies the GELU (fused epilogue or F.gelu)
         return self.ln2(x + F.dropout(h, self.drop, self.training))
 
 
@@ -53,7 +57,8 @@ class BertForPreTraining(nn.Module):
         self.ln = nn.LayerNorm(c.hidden, eps=c.eps)
         self.layers = nn.ModuleList([_Layer(c) for _ in range(c.layers)])
         self.pooler = nn.Linear(c.hidden, c.hidden)
-        self.mlm_dense = nn.Linear(c.hidden, c.hidden)
+        from ..ops.linear import LinearAct
+        self.mlm_dense = LinearAct(c.hidden, c.hidden, act='gelu', fused=c.fused_linear)
         self.mlm_ln = nn.LayerNorm(c.hidden, eps=c.eps)
         self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_size))
         self.nsp = nn.Linear(c.hidden, 2)
@@ -73,7 +78,7 @@ class BertForPreTraining(nn.Module):
         x = F.dropout(self.ln(x), self.config.dropout, self.training)
         for layer in self.layers:
             x = layer(x)
-        h = self.mlm_ln(F.gelu(self.mlm_dense(x)))
+        h = self.mlm_ln(self.mlm_dense(x))
         logits = F.linear(h, self.tok.weight, self.mlm_bias.to(h.dtype))  # tied decoder
         pooled = torch.tanh(self.pooler(x[:, 0]))
         nsp_logits = self.nsp(pooled)
@@ -86,6 +91,12 @@ class BertForPreTraining(nn.Module):
 
 
 def bert_base(**kw):
+    return BertForPreTraining(BertConfig(**kw))
+
+
+def bert_tiny(**kw):
+    """2-layer toy configuration for tests."""
+    kw = dict(dict(vocab_size=1000, hidden=128, layers=2, heads=2, intermediate=512, max_pos=128), **kw)
     return BertForPreTraining(BertConfig(**kw))
 
 
