@@ -11,11 +11,14 @@ import torch
 import torch.nn.functional as F
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from kungfu_b200.ops.linear import linear_act  # noqa: E402
+from kungfu_b200.ops.linear import linear_act, set_tiling  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument('--iters', type=int, default=30)
+ap.add_argument('--tiling', default='auto', choices=['auto', 'single', 'pair'])
 args = ap.parse_args()
+set_tiling(args.tiling)
+print('# tiling: %s' % args.tiling)
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
 
@@ -43,7 +46,7 @@ except Exception:
     pass
 peak = peaks.get('bf16_tflops', 1675.8)
 print('# M N K act | ours ms (TFLOP/s, %% of measured cuBLAS peak %.0f) | library ms (TFLOP/s) | speedup' % peak)
-shapes = [(4096, 3072, 768, 'gelu'), (4096, 768, 3072, None), (4096, 2304, 768, None), (4096, 768, 768, None),
+shapes = [(128, 256, 64, None), (128 * 148, 256, 64, None), (128 * 148, 256, 768, None), (4096, 3072, 768, 'gelu'), (4096, 768, 3072, None), (4096, 2304, 768, None), (4096, 768, 768, None),
           (16384, 3072, 768, 'gelu'), (16384, 768, 3072, None), (8192, 4096, 1024, 'gelu'), (8192, 8192, 8192, None)]
 for M, N, K, act in shapes:
     x = torch.randn(M, K, device='cuda').to(torch.bfloat16)

@@ -3,16 +3,25 @@
 // X [M,K] and W [N,K] are bf16 with K contiguous (torch.nn.Linear's layout), so
 // both operands are "K-major" and no transpose is ever materialised.
 //
-//   warp 0      TMA producer: cp.async.bulk.tensor (128B swizzle) of a 128x64 X
-//               tile and a 256x64 W tile per stage, 4 stages of 48 KiB
-//   warp 1      MMA issuer: one thread issues tcgen05.mma (128x256x16, bf16 ->
-//               fp32) with the accumulator in tensor memory; tcgen05.commit
-//               hands smem stages back to the producer and accumulators to the
-//               epilogue through mbarriers
+//   warp 0      TMA producer: cp.async.bulk.tensor (128B swizzle) of X and W
+//               tiles, 64 K-elements (one swizzle row) per stage
+//   warp 1      MMA issuer: one thread issues tcgen05.mma (bf16 -> fp32) with
+//               the accumulator in tensor memory; tcgen05.commit hands smem
+//               stages back to the producer and accumulators to the epilogue
+//               through mbarriers
 //   warp 2      allocates / frees the 512 TMEM columns (two 128x256 accumulators)
 //   warps 4-11  epilogue: tcgen05.ld the accumulator, + bias, activation, bf16
 //               pack, 16-byte stores; runs while the tensor cores are already
 //               on the next tile (double-buffered accumulators)
+//
+// Two tilings of the same kernel:
+//   PAIR = false  one CTA per 128x256 tile (cta_group::1), 4 stages of 48 KiB
+//   PAIR = true   a cluster of two CTAs (one TPC) per 256x256 tile: each CTA
+//                 stages its own 128 rows of X and HALF of the W tile, the leader
+//                 issues tcgen05.mma.cta_group::2 (M = 256) which reads both
+//                 CTAs' shared memory and writes both CTAs' tensor memory. A
+//                 stage is 32 KiB per CTA, so 6 stages fit and L2->SM traffic
+//                 per flop drops by a third.
 //
 // The kernel is persistent (one CTA per SM, static tile schedule). The fused
 // epilogue removes the separate bias / GELU passes over the [M,N] activation;
@@ -27,6 +36,7 @@
 #include <stdint.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "kungfu_b200.h"
@@ -35,26 +45,56 @@ namespace kfb
 {
 void set_last_error(const char *fmt, ...);  // collectives.cu
 
-constexpr int LT_BM     = 128;
+constexpr int LT_BM     = 128;  // rows per CTA
 constexpr int LT_BN     = 256;
 constexpr int LT_BK     = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int LT_UMMA_K = 16;
-constexpr int LT_STAGES = 4;
-constexpr int LT_A_BYTES     = LT_BM * LT_BK * 2;
-constexpr int LT_B_BYTES     = LT_BN * LT_BK * 2;
-constexpr int LT_STAGE_BYTES = LT_A_BYTES + LT_B_BYTES;
-constexpr int LT_EPI_WARPS   = 8;
+constexpr int LT_A_BYTES        = LT_BM * LT_BK * 2;
+constexpr int LT_EPI_WARPS      = 8;
 constexpr int LT_FIRST_EPI_WARP = 4;
-constexpr int LT_THREADS     = (LT_FIRST_EPI_WARP + LT_EPI_WARPS) * 32;
-constexpr int LT_TMEM_COLS   = 2 * LT_BN;
-constexpr int LT_NUM_BARS    = 2 * LT_STAGES + 4;
-constexpr int LT_SMEM_BYTES  = 1024 + LT_STAGES * LT_STAGE_BYTES + LT_NUM_BARS * 8 + 16;
+constexpr int LT_THREADS        = (LT_FIRST_EPI_WARP + LT_EPI_WARPS) * 32;
+constexpr int LT_TMEM_COLS      = 2 * LT_BN;
+
+template <bool PAIR> struct LtCfg {
+    static constexpr int STAGES      = PAIR ? 6 : 4;
+    static constexpr int B_ROWS      = PAIR ? LT_BN / 2 : LT_BN;  // W rows this CTA stages
+    static constexpr int B_BYTES     = B_ROWS * LT_BK * 2;
+    static constexpr int STAGE_BYTES = LT_A_BYTES + B_BYTES;
+    static constexpr int NUM_BARS    = 2 * STAGES + 4;
+    static constexpr int SMEM_BYTES  = 1024 + STAGES * STAGE_BYTES + NUM_BARS * 8 + 16;
+    // bytes that land per stage on the barrier the MMA thread waits on
+    static constexpr uint32_t TX_BYTES = (PAIR ? 2u : 1u) * STAGE_BYTES;
+    // instruction descriptor: D fp32 (bit 4), A/B bf16 (bits 7, 10), both K-major, N>>3 at 17, M>>4 at 24
+    static constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(LT_BN >> 3) << 17) |
+                                      (static_cast<uint32_t>((PAIR ? 2 * LT_BM : LT_BM) >> 4) << 24);
+};
 
 // ---- PTX wrappers ----------------------------------------------------------------
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+
+// shared::cluster address of the same shared-memory location in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
@@ -70,6 +110,12 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// arrive on a barrier that may live in the other CTA of the cluster (shared::cluster address)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar)
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 
 __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
@@ -108,26 +154,59 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
         : "memory");
 }
 
+// CTA-pair form: the data lands in this CTA's shared memory, the byte count is
+// signalled on `cluster_bar`, which may be the leader CTA's barrier.
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, uint32_t cluster_bar, int c0,
+                                                 int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+        "%4}], [%2];" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(cluster_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // tcgen05.commit: the mbarrier gets one arrival once every MMA issued so far by
-// this thread has finished (implies fence::before_thread_sync).
-__device__ __forceinline__ void tc_commit(uint32_t bar)
+// this thread has finished (implies fence::before_thread_sync). The pair form
+// arrives on the barrier at the same offset in both CTAs of the pair.
+template <bool PAIR> __device__ __forceinline__ void tc_commit(uint32_t bar)
 {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    if (PAIR) {
+        const uint16_t mask = 3;
+        asm volatile(
+            "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                bar),
+            "h"(mask)
+            : "memory");
+    } else {
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                     : "memory");
+    }
 }
 
-// D[tmem] (+)= A[smem] . B[smem]^T, 128 x N x 16, bf16 inputs, fp32 accumulate.
+// D[tmem] (+)= A[smem] . B[smem]^T, (128 | 256) x 256 x 16, bf16 inputs, fp32 accumulate.
+template <bool PAIR>
 __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                             uint32_t accumulate)
 {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
+    if (PAIR) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+            "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+            "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
 }
 
 // 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets row (lane base + t).
@@ -162,22 +241,21 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr)
     return d;
 }
 
-// Instruction descriptor: D fp32, A/B bf16, both K-major, M=128, N=LT_BN.
-constexpr uint32_t LT_IDESC = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(LT_BN >> 3) << 17) |
-                              (static_cast<uint32_t>(LT_BM >> 4) << 24);
-
 __device__ __forceinline__ float gelu_erf(float z)
 {
-    // 0.5 z (1 + erf(z / sqrt 2)); erf by Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7,
-    // far below the bf16 output's resolution)
-    const float x  = fabsf(z) * 0.70710678f;
-    const float t  = __frcp_rn(fmaf(0.3275911f, x, 1.0f));
-    float p        = fmaf(1.061405429f, t, -1.453152027f);
-    p              = fmaf(p, t, 1.421413741f);
-    p              = fmaf(p, t, -0.284496736f);
-    p              = fmaf(p, t, 0.254829592f);
-    const float e  = 1.0f - p * t * __expf(-x * x);
-    return 0.5f * z * (1.0f + copysignf(e, z));
+    // 0.5 z (1 + erf(z / sqrt 2)); erf by Abramowitz-Stegun 7.1.25 (|error| < 2.5e-5,
+    // two orders below the bf16 output's resolution): 2 MUFU + ~12 FP32 ops per
+    // element, no slow-path branches, so the epilogue stays under the MMA time.
+    const float x = fabsf(z) * 0.70710678f;
+    float t;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.47047f, x, 1.0f)));
+    float p = fmaf(0.7478556f, t, -0.0958798f);
+    p       = fmaf(p, t, 0.3480242f) * t;
+    float ex;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"(x * x * -1.44269504f));
+    const float e  = fmaf(-p, ex, 1.0f);
+    const float hz = 0.5f * z;
+    return fmaf(hz, copysignf(e, z), hz);
 }
 
 template <int ACT> __device__ __forceinline__ float apply_act(float z)
@@ -195,102 +273,128 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 
 // ---- the kernel ------------------------------------------------------------------
 
-template <int ACT, bool SAVE_Z>
+template <int ACT, bool SAVE_Z, bool PAIR>
 __global__ void __launch_bounds__(LT_THREADS, 1)
     k_linear_act(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                  const void *__restrict__ bias, int bias_bf16, __nv_bfloat16 *__restrict__ y,
                  __nv_bfloat16 *__restrict__ z, int M, int N, int K)
 {
+    using Cfg = LtCfg<PAIR>;
     extern __shared__ uint8_t lt_smem_raw[];
     // the 128-byte swizzle pattern is a function of address bits [4,10): tiles need 1024-byte alignment
+    // (the dynamic shared window starts at the same offset in both CTAs of a pair, so offsets match)
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(lt_smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t *bars      = reinterpret_cast<uint64_t *>(smem + LT_STAGES * LT_STAGE_BYTES);
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + LT_NUM_BARS);
+    uint64_t *bars      = reinterpret_cast<uint64_t *>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + Cfg::NUM_BARS);
 
-    const uint32_t smem_base  = smem_u32(smem);
-    const uint32_t bar_base   = smem_u32(bars);
-    auto full_bar             = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar            = [&](int s) { return bar_base + 8u * (LT_STAGES + s); };
-    auto tmem_full_bar        = [&](int a) { return bar_base + 8u * (2 * LT_STAGES + a); };
-    auto tmem_empty_bar       = [&](int a) { return bar_base + 8u * (2 * LT_STAGES + 2 + a); };
+    const uint32_t smem_base = smem_u32(smem);
+    const uint32_t bar_base  = smem_u32(bars);
+    auto full_bar            = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar           = [&](int s) { return bar_base + 8u * (Cfg::STAGES + s); };
+    auto tmem_full_bar       = [&](int a) { return bar_base + 8u * (2 * Cfg::STAGES + a); };
+    auto tmem_empty_bar      = [&](int a) { return bar_base + 8u * (2 * Cfg::STAGES + 2 + a); };
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;  // 0 = leader (issues the MMAs)
 
-    const int num_m     = (M + LT_BM - 1) / LT_BM;
-    const int num_n     = (N + LT_BN - 1) / LT_BN;
-    const int num_tiles = num_m * num_n;
-    const int num_kb    = (K + LT_BK - 1) / LT_BK;
+    const int tile_rows   = PAIR ? 2 * LT_BM : LT_BM;
+    const int num_m       = (M + tile_rows - 1) / tile_rows;
+    const int num_n       = (N + LT_BN - 1) / LT_BN;
+    const int num_tiles   = num_m * num_n;
+    const int num_kb      = (K + LT_BK - 1) / LT_BK;
+    const int worker      = PAIR ? blockIdx.x >> 1 : blockIdx.x;
+    const int num_workers = PAIR ? gridDim.x >> 1 : gridDim.x;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tm_x)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tm_w)) : "memory");
     } else if (warp == 1 && lane == 0) {
-        for (int s = 0; s < LT_STAGES; ++s) {
-            mbar_init(full_bar(s), 1);
-            mbar_init(empty_bar(s), 1);
+        for (int s = 0; s < Cfg::STAGES; ++s) {
+            mbar_init(full_bar(s), 1);   // the (leader's) producer's arrive.expect_tx
+            mbar_init(empty_bar(s), 1);  // one tcgen05.commit arrival
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tmem_full_bar(a), 1);
-            mbar_init(tmem_empty_bar(a), LT_EPI_WARPS);
+            mbar_init(tmem_empty_bar(a), LT_EPI_WARPS * (PAIR ? 2 : 1));  // both CTAs' epilogue warps
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     } else if (warp == 2) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"(LT_TMEM_COLS)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"(LT_TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                             smem_u32(tmem_slot)),
+                         "r"(LT_TMEM_COLS)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (PAIR)
+        cluster_sync_all();  // the peer's barriers must be initialised before anything signals them
+    else
+        __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0 && lane == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (every CTA stages its own operands) =====
         int stage = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int m0 = (tile % num_m) * LT_BM;
-            const int n0 = (tile / num_m) * LT_BN;
+        for (int tile = worker; tile < num_tiles; tile += num_workers) {
+            const int m0 = (tile % num_m) * tile_rows + static_cast<int>(cta_rank) * LT_BM;
+            const int n0 = (tile / num_m) * LT_BN + static_cast<int>(cta_rank) * Cfg::B_ROWS * (PAIR ? 1 : 0);
             for (int kb = 0; kb < num_kb; ++kb) {
-                mbar_wait(empty_bar(stage), phase ^ 1);
-                const uint32_t a_smem = smem_base + stage * LT_STAGE_BYTES;
-                mbar_arrive_expect_tx(full_bar(stage), LT_STAGE_BYTES);
-                tma_load_2d(a_smem, &tm_x, full_bar(stage), kb * LT_BK, m0);
-                tma_load_2d(a_smem + LT_A_BYTES, &tm_w, full_bar(stage), kb * LT_BK, n0);
-                if (++stage == LT_STAGES) {
+                mbar_wait(empty_bar(stage), phase ^ 1);  // this CTA's slot has been consumed
+                const uint32_t a_smem = smem_base + stage * Cfg::STAGE_BYTES;
+                if (PAIR) {
+                    // both CTAs' bytes are counted on the leader's barrier: that is the one the MMA thread waits on
+                    const uint32_t sig = map_to_cta(full_bar(stage), 0);
+                    if (cta_rank == 0) mbar_arrive_expect_tx(full_bar(stage), Cfg::TX_BYTES);
+                    tma_load_2d_pair(a_smem, &tm_x, sig, kb * LT_BK, m0);
+                    tma_load_2d_pair(a_smem + LT_A_BYTES, &tm_w, sig, kb * LT_BK, n0);
+                } else {
+                    mbar_arrive_expect_tx(full_bar(stage), Cfg::TX_BYTES);
+                    tma_load_2d(a_smem, &tm_x, full_bar(stage), kb * LT_BK, m0);
+                    tma_load_2d(a_smem + LT_A_BYTES, &tm_w, full_bar(stage), kb * LT_BK, n0);
+                }
+                if (++stage == Cfg::STAGES) {
                     stage = 0;
                     phase ^= 1;
                 }
             }
         }
-    } else if (warp == 1 && lane == 0) {
-        // ===== MMA issuer (a single thread) =====
+    } else if (warp == 1 && lane == 0 && cta_rank == 0) {
+        // ===== MMA issuer (a single thread; of the leader CTA for a pair) =====
         int stage = 0, accum = 0;
         uint32_t phase = 0, accum_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            mbar_wait(tmem_empty_bar(accum), accum_phase ^ 1);  // the epilogue has drained this accumulator
+        for (int tile = worker; tile < num_tiles; tile += num_workers) {
+            mbar_wait(tmem_empty_bar(accum), accum_phase ^ 1);  // the epilogue(s) drained this accumulator
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + accum * LT_BN;
             for (int kb = 0; kb < num_kb; ++kb) {
-                mbar_wait(full_bar(stage), phase);  // TMA has landed this stage
+                mbar_wait(full_bar(stage), phase);  // TMA has landed this stage (in both CTAs)
                 tc_fence_after();
-                const uint32_t a_smem = smem_base + stage * LT_STAGE_BYTES;
+                const uint32_t a_smem = smem_base + stage * Cfg::STAGE_BYTES;
                 const uint64_t a_desc = make_kmajor_sw128_desc(a_smem);
                 const uint64_t b_desc = make_kmajor_sw128_desc(a_smem + LT_A_BYTES);
 #pragma unroll
                 for (int k = 0; k < LT_BK / LT_UMMA_K; ++k) {
                     // advancing 16 elements (32 bytes) along K inside the swizzle row: +2 in the >>4 address field
-                    tc_mma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, LT_IDESC, (kb | k) != 0);
+                    tc_mma_bf16<PAIR>(d_tmem, a_desc + 2 * k, b_desc + 2 * k, Cfg::IDESC, (kb | k) != 0);
                 }
-                tc_commit(empty_bar(stage));  // stage reusable once these MMAs have read it
-                if (++stage == LT_STAGES) {
+                tc_commit<PAIR>(empty_bar(stage));  // stage reusable once these MMAs have read it
+                if (++stage == Cfg::STAGES) {
                     stage = 0;
                     phase ^= 1;
                 }
             }
-            tc_commit(tmem_full_bar(accum));  // accumulator complete
+            tc_commit<PAIR>(tmem_full_bar(accum));  // accumulator complete
             if (++accum == 2) {
                 accum = 0;
                 accum_phase ^= 1;
@@ -302,24 +406,31 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         const int half    = (warp - LT_FIRST_EPI_WARP) >> 2;  // which 128 of the 256 accumulator columns
         int accum = 0;
         uint32_t accum_phase = 0;
-        const float *bias_f          = reinterpret_cast<const float *>(bias);
-        const __nv_bfloat16 *bias_h  = reinterpret_cast<const __nv_bfloat16 *>(bias);
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int m0  = (tile % num_m) * LT_BM;
+        const float *bias_f         = reinterpret_cast<const float *>(bias);
+        const __nv_bfloat16 *bias_h = reinterpret_cast<const __nv_bfloat16 *>(bias);
+        for (int tile = worker; tile < num_tiles; tile += num_workers) {
+            const int m0  = (tile % num_m) * tile_rows + static_cast<int>(cta_rank) * LT_BM;
             const int n0  = (tile / num_m) * LT_BN;
             const int row = m0 + quarter * 32 + lane;
+            // this warp's 128 bias values (lane j holds column c*32+j of chunk c), fetched while
+            // the tensor cores are still working on the tile
+            float b_pref[LT_BN / 2 / 32];
+#pragma unroll
+            for (int c = 0; c < LT_BN / 2 / 32; ++c) {
+                const int nb = n0 + half * (LT_BN / 2) + c * 32 + lane;
+                b_pref[c]    = 0.0f;
+                if (bias != nullptr && nb < N) b_pref[c] = bias_bf16 ? __bfloat162float(bias_h[nb]) : bias_f[nb];
+            }
             mbar_wait(tmem_full_bar(accum), accum_phase);
             tc_fence_after();
-#pragma unroll 1
+#pragma unroll
             for (int c = 0; c < LT_BN / 2 / 32; ++c) {
                 const int col0 = half * (LT_BN / 2) + c * 32;
                 const int n    = n0 + col0;
                 if (n >= N) break;  // warp-uniform
                 uint32_t v[32];
                 tc_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + accum * LT_BN + col0, v);
-                float b_lane = 0.0f;
-                if (bias != nullptr && n + lane < N)
-                    b_lane = bias_bf16 ? __bfloat162float(bias_h[n + lane]) : bias_f[n + lane];
+                const float b_lane = b_pref[c];
                 tc_ld_wait();
                 float f[32];
 #pragma unroll
@@ -354,10 +465,15 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
                     }
                 }
             }
-            // hand the accumulator back to the MMA warp
+            // hand the accumulator back to the MMA thread (which lives in the leader CTA)
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tmem_empty_bar(accum));
+            if (lane == 0) {
+                if (PAIR)
+                    mbar_arrive_cluster(map_to_cta(tmem_empty_bar(accum), 0));
+                else
+                    mbar_arrive(tmem_empty_bar(accum));
+            }
             if (++accum == 2) {
                 accum = 0;
                 accum_phase ^= 1;
@@ -365,12 +481,20 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         }
     }
 
+    __syncwarp();  // the single-thread roles rejoin their warps before the aligned barrier
     tc_fence_before();
-    __syncthreads();
+    if (PAIR)
+        cluster_sync_all();  // neither CTA may leave while the other can still touch its smem / TMEM / barriers
+    else
+        __syncthreads();
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(LT_TMEM_COLS)
-                     : "memory");
+        if (PAIR)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(LT_TMEM_COLS)
+                         : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(LT_TMEM_COLS)
+                         : "memory");
     }
 }
 
@@ -437,24 +561,83 @@ static bool make_kmajor_map(CUtensorMap *map, const void *base, int rows, int K,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int ACT, bool SAVE_Z>
-static int launch_linear(const CUtensorMap &tx, const CUtensorMap &tw, const void *bias, int bias_bf16, void *y, void *z,
-                         int M, int N, int K, int grid, cudaStream_t stream)
+// -1: choose per shape, 0: one CTA per tile, 1: CTA pairs (kfb_linear_act_set_mode / KUNGFU_LINEAR_TC_PAIR)
+static int g_pair_mode = -2;
+
+static int pair_mode()
 {
+    if (g_pair_mode == -2) {
+        const char *e = getenv("KUNGFU_LINEAR_TC_PAIR");
+        g_pair_mode   = e ? atoi(e) : -1;
+    }
+    return g_pair_mode;
+}
+
+template <int ACT, bool SAVE_Z, bool PAIR>
+static int launch_linear(const void *x, const void *w, const void *bias, int bias_bf16, void *y, void *z, int M, int N,
+                         int K, int sms, cudaStream_t stream)
+{
+    using Cfg = LtCfg<PAIR>;
     static std::once_flag once;
     static cudaError_t attr_err = cudaSuccess;
     std::call_once(once, [] {
-        attr_err = cudaFuncSetAttribute(k_linear_act<ACT, SAVE_Z>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        LT_SMEM_BYTES);
+        attr_err = cudaFuncSetAttribute(k_linear_act<ACT, SAVE_Z, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        Cfg::SMEM_BYTES);
     });
-    if (attr_err != cudaSuccess) return static_cast<int>(attr_err);
-    k_linear_act<ACT, SAVE_Z><<<grid, LT_THREADS, LT_SMEM_BYTES, stream>>>(
-        tx, tw, bias, bias_bf16, static_cast<__nv_bfloat16 *>(y), static_cast<__nv_bfloat16 *>(z), M, N, K);
-    const cudaError_t e = cudaGetLastError();
+    if (attr_err != cudaSuccess) {
+        set_last_error("linear_act: cannot opt in to %d bytes of shared memory: %s", Cfg::SMEM_BYTES,
+                       cudaGetErrorString(attr_err));
+        return static_cast<int>(attr_err);
+    }
+    CUtensorMap tx, tw;
+    if (!make_kmajor_map(&tx, x, M, K, LT_BM) || !make_kmajor_map(&tw, w, N, K, Cfg::B_ROWS)) {
+        set_last_error("linear_act: cuTensorMapEncodeTiled failed (M=%d N=%d K=%d)", M, N, K);
+        return static_cast<int>(cudaErrorNotSupported);
+    }
+    const int tile_rows = PAIR ? 2 * LT_BM : LT_BM;
+    const int tiles     = ((M + tile_rows - 1) / tile_rows) * ((N + LT_BN - 1) / LT_BN);
+    const int workers   = PAIR ? sms / 2 : sms;
+    const int grid      = (tiles < workers ? tiles : workers) * (PAIR ? 2 : 1);
+
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim            = dim3(grid);
+    cfg.blockDim           = dim3(LT_THREADS);
+    cfg.dynamicSmemBytes   = Cfg::SMEM_BYTES;
+    cfg.stream             = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id               = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = PAIR ? 2 : 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs                = attr;
+    cfg.numAttrs             = 1;
+    const cudaError_t e =
+        cudaLaunchKernelEx(&cfg, k_linear_act<ACT, SAVE_Z, PAIR>, tx, tw, bias, bias_bf16,
+                           static_cast<__nv_bfloat16 *>(y), static_cast<__nv_bfloat16 *>(z), M, N, K);
     if (e != cudaSuccess) set_last_error("linear_act launch: %s", cudaGetErrorString(e));
     return static_cast<int>(e);
 }
+
+template <bool PAIR>
+static int dispatch_linear(const void *x, const void *w, const void *bias, int bb, void *y, void *z, int M, int N, int K,
+                           int act, int sms, cudaStream_t s)
+{
+    const bool sz = z != nullptr;
+    switch (act) {
+    case KFB_ACT_NONE: return launch_linear<KFB_ACT_NONE, false, PAIR>(x, w, bias, bb, y, nullptr, M, N, K, sms, s);
+    case KFB_ACT_GELU:
+        return sz ? launch_linear<KFB_ACT_GELU, true, PAIR>(x, w, bias, bb, y, z, M, N, K, sms, s)
+                  : launch_linear<KFB_ACT_GELU, false, PAIR>(x, w, bias, bb, y, z, M, N, K, sms, s);
+    case KFB_ACT_RELU:
+        return sz ? launch_linear<KFB_ACT_RELU, true, PAIR>(x, w, bias, bb, y, z, M, N, K, sms, s)
+                  : launch_linear<KFB_ACT_RELU, false, PAIR>(x, w, bias, bb, y, z, M, N, K, sms, s);
+    }
+    set_last_error("linear_act: unknown activation %d", act);
+    return static_cast<int>(cudaErrorInvalidValue);
+}
 }  // namespace kfb
+
+extern "C" void kfb_linear_act_set_mode(int mode) { kfb::g_pair_mode = mode < -1 || mode > 1 ? -1 : mode; }
 
 extern "C" int kfb_linear_act(const void *x, const void *w, const void *bias, int bias_dtype, void *y, void *z, int M,
                               int N, int K, int act, void *stream_)
@@ -476,28 +659,17 @@ extern "C" int kfb_linear_act(const void *x, const void *w, const void *bias, in
         set_last_error("linear_act: bias must be f32 or bf16");
         return static_cast<int>(cudaErrorInvalidValue);
     }
-    CUtensorMap tx, tw;
-    if (!make_kmajor_map(&tx, x, M, K, LT_BM) || !make_kmajor_map(&tw, w, N, K, LT_BN)) {
-        set_last_error("linear_act: cuTensorMapEncodeTiled failed (M=%d N=%d K=%d)", M, N, K);
-        return static_cast<int>(cudaErrorNotSupported);
-    }
-    int dev = 0, sms = 0;
+    static int sms_of[64];
+    int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const int tiles = ((M + LT_BM - 1) / LT_BM) * ((N + LT_BN - 1) / LT_BN);
-    const int grid  = tiles < sms ? tiles : sms;
-    const int bb    = bias_dtype == KFB_BF16;
-    const bool sz   = z != nullptr;
-    switch (act) {
-    case KFB_ACT_NONE: return launch_linear<KFB_ACT_NONE, false>(tx, tw, bias, bb, y, nullptr, M, N, K, grid, stream);
-    case KFB_ACT_GELU:
-        return sz ? launch_linear<KFB_ACT_GELU, true>(tx, tw, bias, bb, y, z, M, N, K, grid, stream)
-                  : launch_linear<KFB_ACT_GELU, false>(tx, tw, bias, bb, y, z, M, N, K, grid, stream);
-    case KFB_ACT_RELU:
-        return sz ? launch_linear<KFB_ACT_RELU, true>(tx, tw, bias, bb, y, z, M, N, K, grid, stream)
-                  : launch_linear<KFB_ACT_RELU, false>(tx, tw, bias, bb, y, z, M, N, K, grid, stream);
-    }
-    return static_cast<int>(cudaErrorInvalidValue);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (sms_of[dev] == 0) cudaDeviceGetAttribute(&sms_of[dev], cudaDevAttrMultiProcessorCount, dev);
+    const int sms = sms_of[dev] > 0 ? sms_of[dev] : 148;
+    const int bb  = bias_dtype == KFB_BF16;
+    int mode      = pair_mode();
+    if (mode < 0) mode = M > LT_BM ? 1 : 0;  // a pair needs two row blocks to be worth its second SM
+    return mode ? dispatch_linear<true>(x, w, bias, bb, y, z, M, N, K, act, sms, stream)
+                : dispatch_linear<false>(x, w, bias, bb, y, z, M, N, K, act, sms, stream);
 }
 
 extern "C" int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, int act, void *stream_)
@@ -505,7 +677,10 @@ extern "C" int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, in
     using namespace kfb;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     if (n == 0) return 0;
-    if (n % 8) return static_cast<int>(cudaErrorInvalidValue);
+    if (n % 8) {
+        set_last_error("act_bwd: element count must be a multiple of 8");
+        return static_cast<int>(cudaErrorInvalidValue);
+    }
     const size_t n8 = n / 8;
     size_t want     = (n8 + 255) / 256;
     const int grid  = static_cast<int>(want < 148 * 8 ? want : 148 * 8);
@@ -515,7 +690,9 @@ extern "C" int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, in
     else if (act == KFB_ACT_RELU)
         k_act_bwd<KFB_ACT_RELU><<<grid, 256, 0, stream>>>(static_cast<const uint4 *>(dy), static_cast<const uint4 *>(z),
                                                           static_cast<uint4 *>(dz), n8);
-    else
+    else {
+        set_last_error("act_bwd: unknown activation %d", act);
         return static_cast<int>(cudaErrorInvalidValue);
+    }
     return static_cast<int>(cudaGetLastError());
 }

@@ -21,6 +21,12 @@ ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
 _ACT = {None: ACT_NONE, 'none': ACT_NONE, 'gelu': ACT_GELU, 'relu': ACT_RELU}
 
 
+def set_tiling(mode):
+    """'auto' (default: CTA pairs whenever M > 128), 'single' (one CTA per 128x256
+    tile, cta_group::1) or 'pair' (two CTAs per 256x256 tile, cta_group::2)."""
+    K.lib().kfb_linear_act_set_mode({'auto': -1, 'single': 0, 'pair': 1}[mode])
+
+
 def supported(x, weight, bias=None):
     """bf16 CUDA operands, K and N multiples of 8, dense row-major."""
     if not (x.is_cuda and weight.is_cuda and x.dtype == torch.bfloat16 and weight.dtype == torch.bfloat16):

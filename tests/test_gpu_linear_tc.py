@@ -7,6 +7,15 @@ import torch.nn.functional as F
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(params=['single', 'pair'], autouse=True)
+def tiling(request):
+    """Every test runs on both tilings of the kernel (cta_group::1 and cta_group::2)."""
+    from kungfu_b200.ops.linear import set_tiling
+    set_tiling(request.param)
+    yield request.param
+    set_tiling('auto')
+
+
 def _ref(x, w, b, act):
     z = x.float() @ w.float().t()
     if b is not None:
