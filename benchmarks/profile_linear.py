@@ -8,7 +8,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from kungfu_b200.ops.linear import linear_act  # noqa: E402
 
-shapes = [(4096, 768, 768, None), (16384, 3072, 768, 'gelu')]
+shapes = [(4096, 3072, 768, 'gelu'), (8192, 8192, 8192, None)]
 ts = []
 for M, N, K, act in shapes:
     x = torch.randn(M, K, device='cuda').to(torch.bfloat16)

@@ -10,7 +10,7 @@
 //               stages back to the producer and accumulators to the epilogue
 //               through mbarriers
 //   warp 2      allocates / frees the 512 TMEM columns (two 128x256 accumulators)
-//   warps 4-11  epilogue: tcgen05.ld the accumulator, + bias, activation, bf16
+//   warps 4-19  epilogue: tcgen05.ld the accumulator, + bias, activation, bf16
 //               pack, 16-byte stores; runs while the tensor cores are already
 //               on the next tile (double-buffered accumulators)
 //
@@ -50,8 +50,9 @@ constexpr int LT_BN     = 256;
 constexpr int LT_BK     = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int LT_UMMA_K = 16;
 constexpr int LT_A_BYTES        = LT_BM * LT_BK * 2;
-constexpr int LT_EPI_WARPS      = 8;
+constexpr int LT_EPI_WARPS      = 16;  // 4 TMEM lane quarters x 4 column parts
 constexpr int LT_FIRST_EPI_WARP = 4;
+constexpr int LT_EPI_COLS       = LT_BN / (LT_EPI_WARPS / 4);  // accumulator columns per epilogue warp
 constexpr int LT_THREADS        = (LT_FIRST_EPI_WARP + LT_EPI_WARPS) * 32;
 constexpr int LT_TMEM_COLS      = 2 * LT_BN;
 
@@ -115,7 +116,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 // arrive on a barrier that may live in the other CTA of the cluster (shared::cluster address)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar)
 {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+    // default (.release.cta) semantics: the consumer only needs this warp's TMEM reads to be done, which
+    // tcgen05.wait::ld + fence::before_thread_sync order; a cluster-scope release would drain the global stores
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 
 __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
@@ -271,6 +274,23 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
     return *reinterpret_cast<uint32_t *>(&h);
 }
 
+// Tile order: groups of LT_GROUP_M row-blocks sweep all column-blocks before the
+// next group starts, so the ~148 tiles in flight cover a near-square patch of
+// the output and re-read a small set of X / W panels out of L2 (instead of one
+// wave streaming all of X from HBM).
+constexpr int LT_GROUP_M = 8;
+
+__device__ __forceinline__ void tile_to_blocks(int tile, int num_m, int num_n, int &m_blk, int &n_blk)
+{
+    const int per_group = LT_GROUP_M * num_n;
+    const int group     = tile / per_group;
+    const int first_m   = group * LT_GROUP_M;
+    const int rows      = min(num_m - first_m, LT_GROUP_M);
+    const int in_group  = tile - group * per_group;
+    m_blk               = first_m + in_group % rows;
+    n_blk               = in_group / rows;
+}
+
 // ---- the kernel ------------------------------------------------------------------
 
 template <int ACT, bool SAVE_Z, bool PAIR>
@@ -347,8 +367,10 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
         int stage = 0;
         uint32_t phase = 0;
         for (int tile = worker; tile < num_tiles; tile += num_workers) {
-            const int m0 = (tile % num_m) * tile_rows + static_cast<int>(cta_rank) * LT_BM;
-            const int n0 = (tile / num_m) * LT_BN + static_cast<int>(cta_rank) * Cfg::B_ROWS * (PAIR ? 1 : 0);
+            int m_blk, n_blk;
+            tile_to_blocks(tile, num_m, num_n, m_blk, n_blk);
+            const int m0 = m_blk * tile_rows + static_cast<int>(cta_rank) * LT_BM;
+            const int n0 = n_blk * LT_BN + (PAIR ? static_cast<int>(cta_rank) * Cfg::B_ROWS : 0);
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(empty_bar(stage), phase ^ 1);  // this CTA's slot has been consumed
                 const uint32_t a_smem = smem_base + stage * Cfg::STAGE_BYTES;
@@ -403,34 +425,35 @@ __global__ void __launch_bounds__(LT_THREADS, 1)
     } else if (warp >= LT_FIRST_EPI_WARP) {
         // ===== epilogue: TMEM -> registers -> bias/activation -> global =====
         const int quarter = warp & 3;                        // the TMEM lanes this warp may read: 32*(warp%4)..+31
-        const int half    = (warp - LT_FIRST_EPI_WARP) >> 2;  // which 128 of the 256 accumulator columns
+        const int part    = (warp - LT_FIRST_EPI_WARP) >> 2;  // which LT_EPI_COLS of the 256 accumulator columns
         int accum = 0;
         uint32_t accum_phase = 0;
         const float *bias_f         = reinterpret_cast<const float *>(bias);
         const __nv_bfloat16 *bias_h = reinterpret_cast<const __nv_bfloat16 *>(bias);
         for (int tile = worker; tile < num_tiles; tile += num_workers) {
-            const int m0  = (tile % num_m) * tile_rows + static_cast<int>(cta_rank) * LT_BM;
-            const int n0  = (tile / num_m) * LT_BN;
+            int m_blk, n_blk;
+            tile_to_blocks(tile, num_m, num_n, m_blk, n_blk);
+            const int m0  = m_blk * tile_rows + static_cast<int>(cta_rank) * LT_BM;
+            const int n0  = n_blk * LT_BN;
             const int row = m0 + quarter * 32 + lane;
-            // this warp's 128 bias values (lane j holds column c*32+j of chunk c), fetched while
-            // the tensor cores are still working on the tile
-            float b_pref[LT_BN / 2 / 32];
-#pragma unroll
-            for (int c = 0; c < LT_BN / 2 / 32; ++c) {
-                const int nb = n0 + half * (LT_BN / 2) + c * 32 + lane;
-                b_pref[c]    = 0.0f;
-                if (bias != nullptr && nb < N) b_pref[c] = bias_bf16 ? __bfloat162float(bias_h[nb]) : bias_f[nb];
-            }
+            // bias for this warp's columns (lane j holds column j of the 32-column chunk), fetched one
+            // chunk ahead - the first one while the tensor cores are still working on the tile
+            auto load_bias = [&](int nb) -> float {
+                if (bias == nullptr || nb >= N) return 0.0f;
+                return bias_bf16 ? __bfloat162float(bias_h[nb]) : bias_f[nb];
+            };
+            float b_next = load_bias(n0 + part * LT_EPI_COLS + lane);
             mbar_wait(tmem_full_bar(accum), accum_phase);
             tc_fence_after();
-#pragma unroll
-            for (int c = 0; c < LT_BN / 2 / 32; ++c) {
-                const int col0 = half * (LT_BN / 2) + c * 32;
+#pragma unroll 1  // one copy of the epilogue body: the unrolled form overflows the instruction cache
+            for (int c = 0; c < LT_EPI_COLS / 32; ++c) {
+                const int col0 = part * LT_EPI_COLS + c * 32;
                 const int n    = n0 + col0;
                 if (n >= N) break;  // warp-uniform
                 uint32_t v[32];
                 tc_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + accum * LT_BN + col0, v);
-                const float b_lane = b_pref[c];
+                const float b_lane = b_next;
+                if (c + 1 < LT_EPI_COLS / 32) b_next = load_bias(n + 32 + lane);
                 tc_ld_wait();
                 float f[32];
 #pragma unroll

@@ -28,11 +28,13 @@ class _Layer(nn.Module):
         super().__init__()
         from ..ops.linear import LinearAct
         self.heads = c.heads
-        self.qkv = LinearAct(c.hidden, 3 * c.hidden, fused=c.fused_linear)
-        self.proj = LinearAct(c.hidden, c.hidden, fused=c.fused_linear)
+        # plain projections stay library GEMMs; the layer whose epilogue has work to fuse
+        # (bias + GELU over the [tokens, intermediate] activation) runs the tcgen05 kernel
+        self.qkv = nn.Linear(c.hidden, 3 * c.hidden)
+        self.proj = nn.Linear(c.hidden, c.hidden)
         self.ln1 = nn.LayerNorm(c.hidden, eps=c.eps)
         self.fc1 = LinearAct(c.hidden, c.intermediate, act='gelu', fused=c.fused_linear)
-        self.fc2 = LinearAct(c.intermediate, c.hidden, fused=c.fused_linear)
+        self.fc2 = nn.Linear(c.intermediate, c.hidden)
         self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
         self.drop = c.dropout
 
