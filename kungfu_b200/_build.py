@@ -41,6 +41,8 @@ HOST_BINARIES = {
     'kungfu-config-server': 'csrc/launch/config_server_main.cpp',
     'kungfu-rrun': 'csrc/launch/remote_tools.cpp',
     'kungfu-distribute': 'csrc/launch/remote_tools.cpp',
+    'kungfu-bench-allreduce': 'csrc/tools/bench_tools.cpp',
+    'kungfu-bench-p2p': 'csrc/tools/bench_tools.cpp',
 }
 
 

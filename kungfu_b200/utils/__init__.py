@@ -32,3 +32,89 @@ def step_based_schedule(config, step, default=1, strict=True):
     if strict:
         raise ValueError('step %d is beyond the schedule %r' % (step, config))
     return default
+
+
+def list_nvidia_gpu_names():
+    """Names of the visible NVIDIA GPUs, [] when there is no driver
+    (/root/reference/srcs/go/utils/nvidia.go: `nvidia-smi -L` parser)."""
+    import subprocess
+    try:
+        out = subprocess.run(['nvidia-smi', '-L'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True,
+                             timeout=20).stdout
+    except Exception:
+        return []
+    names = []
+    for line in out.splitlines():
+        # "GPU 0: NVIDIA B200 (UUID: GPU-...)"
+        if line.startswith('GPU ') and ':' in line:
+            names.append(line.split(':', 1)[1].split('(UUID')[0].strip())
+    return names
+
+
+def measure(f, *args, **kw):
+    """(result, seconds) of one call (/root/reference/srcs/go/utils/utils.go Measure)."""
+    import time
+    t0 = time.perf_counter()
+    r = f(*args, **kw)
+    return r, time.perf_counter() - t0
+
+
+def show_rate(nbytes, seconds):
+    """Human-readable data rate (/root/reference/srcs/go/utils/utils.go ShowRate)."""
+    rate = nbytes / max(seconds, 1e-12)
+    for unit in ('B/s', 'KiB/s', 'MiB/s', 'GiB/s', 'TiB/s'):
+        if rate < 1024 or unit == 'TiB/s':
+            return '%.2f %s' % (rate, unit)
+        rate /= 1024
+
+
+def show_size(nbytes):
+    for unit in ('B', 'KiB', 'MiB', 'GiB', 'TiB'):
+        if nbytes < 1024 or unit == 'TiB':
+            return '%.1f %s' % (nbytes, unit) if unit != 'B' else '%d B' % nbytes
+        nbytes /= 1024.0
+
+
+def poll(cond, timeout=10.0, interval=0.05):
+    """Wait until cond() is truthy; returns its value or None on timeout
+    (/root/reference/srcs/go/utils/utils.go Poll)."""
+    import time
+    end = time.monotonic() + timeout
+    while True:
+        v = cond()
+        if v:
+            return v
+        if time.monotonic() >= end:
+            return None
+        time.sleep(interval)
+
+
+class StallDetector(object):
+    """Context manager that prints "<name> stalled for N s" every `period`
+    seconds while the body has not finished (the runtime has the same watchdog
+    around its blocking calls; /root/reference/srcs/go/utils/stalldetector.go:15-46)."""
+
+    def __init__(self, name, period=3.0, out=None):
+        import sys
+        self.name, self.period, self.out = name, period, out or sys.stderr
+        self.reports = 0
+
+    def __enter__(self):
+        import threading
+        import time
+        self._done = threading.Event()
+        t0 = time.monotonic()
+
+        def watch():
+            while not self._done.wait(self.period):
+                self.reports += 1
+                print('%s stalled for %.0f s' % (self.name, time.monotonic() - t0), file=self.out, flush=True)
+
+        self._th = threading.Thread(target=watch, daemon=True)
+        self._th.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._done.set()
+        self._th.join()
+        return False

@@ -184,3 +184,21 @@ def test_single_process_mode_and_ema():
     vals = [round(ema.update(x), 4) for x in (2, 3, 4, 5, 6)]
     # the reference's unit test values (tests/python/unit, alpha 0.9)
     assert vals == [2.0, 2.1, 2.29, 2.561, 2.9049]
+
+
+def test_python_utils_helpers():
+    import io
+    import time
+    from kungfu_b200 import utils
+    assert utils.show_rate(3 * 1024 ** 3, 1.0) == '3.00 GiB/s'
+    assert utils.show_size(1536) == '1.5 KiB' and utils.show_size(12) == '12 B'
+    r, dt = utils.measure(lambda x: x + 1, 41)
+    assert r == 42 and dt >= 0
+    t0 = time.monotonic()
+    assert utils.poll(lambda: time.monotonic() - t0 > 0.1, timeout=2) is True
+    assert utils.poll(lambda: False, timeout=0.1) is None
+    assert isinstance(utils.list_nvidia_gpu_names(), list)
+    buf = io.StringIO()
+    with utils.StallDetector('slow op', period=0.05, out=buf) as sd:
+        time.sleep(0.2)
+    assert sd.reports >= 2 and 'slow op stalled for' in buf.getvalue()

@@ -27,3 +27,28 @@ def test_fake_agent(fake_agent, np_, strategy):
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=90)
     assert res.returncode == 0, res.stdout[-3000:]
     assert res.stdout.count('OK fake-agent') == np_
+
+
+def test_cpp_utils_header(tmp_path):
+    """include/kungfu/utils.hpp: Channel, Latch, ExponentialMovingAverage, HandleTable, trace / check macros."""
+    out = str(tmp_path / 'utils-test')
+    subprocess.check_call(['g++', '-O1', '-std=c++17', '-pthread', '-I', os.path.join(ROOT, 'include'),
+                           os.path.join(ROOT, 'tests', 'cpp', 'utils_test.cpp'), '-o', out])
+    res = subprocess.run([out], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert res.returncode == 0 and 'OK utils' in res.stdout, res.stdout
+
+
+@pytest.mark.parametrize('tool,args,np_', [
+    ('kungfu-bench-allreduce', ['-model', '6x5000', '-mode', 'par', '-epochs', '1', '-warmup', '1'], 3),
+    ('kungfu-bench-allreduce', ['-model', 'resnet50', '-mode', 'seq', '-fuse', '-epochs', '1', '-warmup', '0'], 2),
+    ('kungfu-bench-p2p', ['-model', '4x10000', '-epochs', '1', '-warmup', '1'], 3),
+])
+def test_native_bench_tools(tool, args, np_):
+    """Host data-plane micro-benchmarks (reference: tests/go/cmd/kungfu-bench-allreduce, kungfu-bench-p2p)."""
+    bindir = os.path.join(ROOT, 'kungfu_b200', 'bin')
+    base = 21000 + (os.getpid() * 59 + len(args) * 101) % 15000
+    res = subprocess.run([os.path.join(bindir, 'kungfu-run'), '-q', '-np', str(np_), '-timeout', '60s', '-port-range',
+                          '%d-%d' % (base, base + 32), '-port', str(base + 40), os.path.join(bindir, tool)] + args,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert 'OK ' + tool in res.stdout and 'rate' in res.stdout
