@@ -687,7 +687,11 @@ int watch_run(const RunFlags &f, const PeerID &parent, const Cluster &init_clust
     GpuPool gpus(std::max(slots, 1));
     std::map<PeerID, int> gpu_of;
     Cluster current;  // nothing runs yet
-    {
+    if (f.init_version < 0) {
+        // started empty; the first stage arrives over the control channel (kungfu-notify-start,
+        // a cluster manager). /root/reference/srcs/go/cmd/kungfu-run/app/kungfu-run.go:99-101
+        KF_INFO("runner %s: waiting to be initialized", parent.str().c_str());
+    } else {
         Stage s0;
         s0.version = f.init_version;
         s0.cluster = init_cluster;

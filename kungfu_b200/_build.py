@@ -43,6 +43,9 @@ HOST_BINARIES = {
     'kungfu-distribute': 'csrc/launch/remote_tools.cpp',
     'kungfu-bench-allreduce': 'csrc/tools/bench_tools.cpp',
     'kungfu-bench-p2p': 'csrc/tools/bench_tools.cpp',
+    'kungfu-test-util': 'csrc/tools/ops_tools.cpp',
+    'kungfu-notify-start': 'csrc/tools/ops_tools.cpp',
+    'kungfu-config-client': 'csrc/tools/ops_tools.cpp',
 }
 
 

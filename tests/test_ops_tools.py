@@ -1,0 +1,124 @@
+"""Operator tools: kungfu-test-util (-kill / -propose), kungfu-notify-start, kungfu-config-client
+(reference: tests/go/cmd/kungfu-test-util, kungfu-notify-start, kungfu-config-client-example)."""
+import json
+import os
+import subprocess
+import sys
+import time
+import urllib.error
+import urllib.request
+
+from conftest import ROOT
+
+BIN = os.path.join(ROOT, 'kungfu_b200', 'bin')
+
+
+def _base(salt):
+    return 21000 + (os.getpid() * 61 + salt * 977) % 15000
+
+
+def _get(url):
+    try:
+        with urllib.request.urlopen(url, timeout=5) as r:
+            return r.status, r.read().decode()
+    except urllib.error.HTTPError as e:
+        return e.code, ''
+
+
+def test_config_client_and_propose(tmp_path):
+    port = _base(1)
+    url = 'http://127.0.0.1:%d/config' % port
+    srv = subprocess.Popen([os.path.join(BIN, 'kungfu-config-server'), '-port', str(port)],
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    try:
+        for _ in range(50):
+            try:
+                _get(url)
+                break
+            except Exception:
+                time.sleep(0.1)
+        assert _get(url)[0] == 404
+        example = subprocess.run([os.path.join(BIN, 'kungfu-config-client'), '-example', '-H', '127.0.0.1:3'],
+                                 stdout=subprocess.PIPE, text=True, check=True).stdout
+        cluster = json.loads(example)
+        assert len(cluster['Workers']) == 3 and len(cluster['Runners']) == 1
+        f = tmp_path / 'c.json'
+        f.write_text(example)
+        out = subprocess.run([os.path.join(BIN, 'kungfu-test-util'), '-propose', str(f), '-server', url],
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert out.returncode == 0, out.stdout
+        status, body = _get(url)
+        assert status == 200 and json.loads(body)['Workers'] == cluster['Workers']
+        # the periodic client PUTs clusters of random size within the host list's capacity
+        out = subprocess.run([os.path.join(BIN, 'kungfu-config-client'), '-server', url, '-H', '127.0.0.1:3',
+                              '-period', '50ms', '-ttl', '200ms'], stdout=subprocess.PIPE, text=True, timeout=30)
+        assert out.returncode == 0 and out.stdout.count('-> 200') >= 2
+        assert 1 <= len(json.loads(_get(url)[1])['Workers']) <= 3
+        out = subprocess.run([os.path.join(BIN, 'kungfu-config-client'), '-server', url, '-clear'],
+                             stdout=subprocess.PIPE, text=True, timeout=30)
+        assert out.returncode == 0
+        assert _get(url)[0] == 404
+    finally:
+        srv.kill()
+        srv.wait()
+
+
+WORKER = """
+import sys, time
+sys.path.insert(0, %r)
+import kungfu_b200.torch as kf
+print('up', kf.current_rank(), kf.current_cluster_size(), flush=True)
+kf.run_barrier()
+time.sleep(%f)
+print('done', kf.current_rank(), flush=True)
+"""
+
+
+def test_notify_start_initialises_an_empty_runner(tmp_path):
+    base = _base(2)
+    script = tmp_path / 'w.py'
+    script.write_text(WORKER % (ROOT, 0.2))
+    cfg = tmp_path / 'cluster.json'
+    cfg.write_text(json.dumps({'Runners': ['127.0.0.1:%d' % (base + 40)],
+                               'Workers': ['127.0.0.1:%d' % base, '127.0.0.1:%d' % (base + 1)]}))
+    run = subprocess.Popen([os.path.join(BIN, 'kungfu-run'), '-q', '-w', '-init-version', '-1', '-H', '127.0.0.1:2',
+                            '-port', str(base + 40), '-port-range', '%d-%d' % (base, base + 16), '-timeout', '60s',
+                            sys.executable, str(script)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        out = subprocess.run([os.path.join(BIN, 'kungfu-notify-start'), '-config-server', str(cfg)],
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+        assert out.returncode == 0, out.stdout
+        log, _ = run.communicate(timeout=90)
+    finally:
+        if run.poll() is None:
+            run.kill()
+    assert run.returncode == 0, log[-2000:]
+    assert 'waiting to be initialized' in log
+    assert log.count('up ') == 2 and log.count('done ') == 2
+
+
+def test_kill_asks_one_worker_to_exit(tmp_path):
+    base = _base(3)
+    script = tmp_path / 'w.py'
+    # rank 1 would sleep for a minute; the exit request ends it early (exit code 0, so the job succeeds)
+    script.write_text(WORKER.replace('time.sleep(%f)', 'time.sleep(%f if kf.current_rank() == 0 else 60)') % (ROOT, 3.0))
+    run = subprocess.Popen([os.path.join(BIN, 'kungfu-run'), '-q', '-np', '2', '-port', str(base + 40), '-port-range',
+                            '%d-%d' % (base, base + 16), '-timeout', '50s', sys.executable, str(script)],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        time.sleep(1.0)
+        t0 = time.time()
+        ok = False
+        while time.time() - t0 < 30 and not ok:
+            out = subprocess.run([os.path.join(BIN, 'kungfu-test-util'), '-kill', '127.0.0.1:%d' % (base + 1)],
+                                 stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=30)
+            ok = out.returncode == 0
+            if not ok:
+                time.sleep(0.5)
+        assert ok, out.stdout
+        log, _ = run.communicate(timeout=45)
+    finally:
+        if run.poll() is None:
+            run.kill()
+    assert run.returncode == 0, log[-2000:]
+    assert 'done 0' in log and 'done 1' not in log
