@@ -122,3 +122,14 @@ def test_kill_asks_one_worker_to_exit(tmp_path):
             run.kill()
     assert run.returncode == 0, log[-2000:]
     assert 'done 0' in log and 'done 1' not in log
+
+
+def test_cluster_manager_example():
+    """examples/cluster_manager.py: config server + two empty runners on loopback aliases + notify-start + PUT resizes."""
+    base = _base(4)
+    res = subprocess.run([sys.executable, os.path.join(ROOT, 'examples', 'cluster_manager.py'), '--max-step', '50',
+                          '--period', '3', '--sizes', '2,4,3', '--port-base', str(base)],
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240)
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert 'runners exited with [0, 0]' in res.stdout
+    assert res.stdout.count('finished 50 steps with np=3') == 3
