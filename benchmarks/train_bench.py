@@ -36,6 +36,9 @@ ap.add_argument('--steps', type=int, default=20)
 ap.add_argument('--warmup', type=int, default=5)
 ap.add_argument('--fused-bn', type=int, default=1)
 ap.add_argument('--fused-linear', type=int, default=0, help='BERT: tcgen05 linear layers with fused bias/GELU')
+ap.add_argument('--mlm-positions', type=int, default=0,
+                help='BERT: masked positions per sequence fed as masked_lm_positions (original BERT uses 20 at seq 128); '
+                     '0 = MLM head on every position with -100 labels')
 ap.add_argument('--graph', action='store_true', help='capture the step in a CUDA graph (not for pair averaging)')
 ap.add_argument('--momentum', type=float, default=0.9)
 args = ap.parse_args()
@@ -56,8 +59,13 @@ if is_bert:
     nsp = torch.randint(0, 2, (B, ), device=dev)
     unit = 'seq/s'
 
+    mlm_pos = None
+    if args.mlm_positions > 0:
+        mlm_pos = torch.stack([torch.randperm(args.seq_len, device=dev)[:args.mlm_positions].sort().values for _ in range(B)])
+        labels = torch.gather(ids, 1, mlm_pos)
+
     def loss_fn():
-        return model(ids, mlm_labels=labels, nsp_labels=nsp)
+        return model(ids, mlm_labels=labels, nsp_labels=nsp, mlm_positions=mlm_pos)
 else:
     kw = {'fused_bn': bool(args.fused_bn)} if not args.model.startswith('vgg') else {}
     model = models.to_b200_layout(getattr(models, args.model)(**kw).to(dev), torch.bfloat16)

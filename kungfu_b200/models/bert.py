@@ -73,14 +73,21 @@ class BertForPreTraining(nn.Module):
         if isinstance(m, nn.Linear) and m.bias is not None:
             nn.init.zeros_(m.bias)
 
-    def forward(self, ids, token_type=None, mlm_labels=None, nsp_labels=None):
+    def forward(self, ids, token_type=None, mlm_labels=None, nsp_labels=None, mlm_positions=None):
+        """``mlm_positions`` [B, P] (the original BERT input format: masked_lm_positions with
+        mlm_labels [B, P] = masked_lm_ids) restricts the MLM head - a 30522-way projection - to the
+        masked tokens; without it the head runs on every position and mlm_labels is [B, S] with -100
+        at unmasked tokens. Same loss either way."""
         B, S = ids.shape
         pos = torch.arange(S, device=ids.device).unsqueeze(0)
         x = self.tok(ids) + self.pos(pos) + self.typ(token_type if token_type is not None else torch.zeros_like(ids))
         x = F.dropout(self.ln(x), self.config.dropout, self.training)
         for layer in self.layers:
             x = layer(x)
-        h = self.mlm_ln(self.mlm_dense(x))
+        x_mlm = x
+        if mlm_positions is not None:
+            x_mlm = torch.gather(x, 1, mlm_positions.unsqueeze(-1).expand(-1, -1, x.shape[-1]))
+        h = self.mlm_ln(self.mlm_dense(x_mlm))
         logits = F.linear(h, self.tok.weight, self.mlm_bias.to(h.dtype))  # tied decoder
         pooled = torch.tanh(self.pooler(x[:, 0]))
         nsp_logits = self.nsp(pooled)

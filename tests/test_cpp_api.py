@@ -52,3 +52,20 @@ def test_native_bench_tools(tool, args, np_):
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
     assert res.returncode == 0, res.stdout[-3000:]
     assert 'OK ' + tool in res.stdout and 'rate' in res.stdout
+
+
+def test_fake_adaptive_trainer(tmp_path):
+    """C++ elastic trainer: kungfu::Peer::ResizeCluster along a schedule under kungfu-run -w."""
+    out = str(tmp_path / 'fake-adaptive-trainer')
+    lib = os.path.join(ROOT, 'kungfu_b200', 'lib')
+    subprocess.check_call(['g++', '-O1', '-std=c++17', '-pthread', '-I', os.path.join(ROOT, 'include'),
+                           os.path.join(ROOT, 'tests', 'cpp', 'fake_adaptive_trainer.cpp'), '-o', out,
+                           '-L', lib, '-lkungfu_host', '-Wl,-rpath,' + lib])
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
+    base = 21000 + (os.getpid() * 71) % 15000
+    res = subprocess.run([exe, '-q', '-w', '-np', '1', '-H', '127.0.0.1:4', '-timeout', '90s', '-port-range',
+                          '%d-%d' % (base, base + 32), '-port', str(base + 40), out, '3:1,3:3,3:4,3:2', '50000'],
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert 'resized 1 -> 3' in res.stdout and 'resized 3 -> 4' in res.stdout and 'resized 4 -> 2' in res.stdout
+    assert res.stdout.count('OK fake-adaptive-trainer') == 2 and res.stdout.count('detached at step') == 2

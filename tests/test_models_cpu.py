@@ -38,3 +38,21 @@ def test_bert_and_simple_models_forward():
     assert logits.shape == (2, 8, 100) and nsp.shape == (2, 2)
     assert models.SLP()(torch.randn(3, 1, 28, 28)).shape == (3, 10)
     assert models.MnistCNN()(torch.randn(3, 1, 28, 28)).shape == (3, 10)
+
+
+def test_bert_masked_positions_give_the_same_loss():
+    """mlm_positions (masked_lm_positions format) == full-sequence head with -100 labels."""
+    import torch
+    from kungfu_b200 import models
+    torch.manual_seed(0)
+    m = models.bert_tiny(dropout=0.0)
+    m.eval()
+    ids = torch.randint(0, 1000, (3, 16))
+    pos = torch.stack([torch.randperm(16)[:4].sort().values for _ in range(3)])
+    lab_p = torch.gather(ids, 1, pos)
+    lab_full = torch.full_like(ids, -100)
+    lab_full.scatter_(1, pos, lab_p)
+    nsp = torch.tensor([0, 1, 0])
+    a = m(ids, mlm_labels=lab_full, nsp_labels=nsp)
+    b = m(ids, mlm_labels=lab_p, nsp_labels=nsp, mlm_positions=pos)
+    assert abs(float(a) - float(b)) < 1e-5
