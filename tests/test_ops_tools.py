@@ -100,23 +100,29 @@ def test_notify_start_initialises_an_empty_runner(tmp_path):
 def test_kill_asks_one_worker_to_exit(tmp_path):
     base = _base(3)
     script = tmp_path / 'w.py'
-    # rank 1 would sleep for a minute; the exit request ends it early (exit code 0, so the job succeeds)
-    script.write_text(WORKER.replace('time.sleep(%f)', 'time.sleep(%f if kf.current_rank() == 0 else 60)') % (ROOT, 3.0))
+    # after the barrier both workers drop a marker; rank 1 would then sleep for a minute, the exit
+    # request ends it early (exit code 0, so the job succeeds)
+    script.write_text("""
+import sys, time
+sys.path.insert(0, %r)
+import kungfu_b200.torch as kf
+kf.run_barrier()
+open(%r + '/ready-%%d' %% kf.current_rank(), 'w').close()
+time.sleep(4 if kf.current_rank() == 0 else 60)
+print('done', kf.current_rank(), flush=True)
+""" % (ROOT, str(tmp_path)))
     run = subprocess.Popen([os.path.join(BIN, 'kungfu-run'), '-q', '-np', '2', '-port', str(base + 40), '-port-range',
-                            '%d-%d' % (base, base + 16), '-timeout', '50s', sys.executable, str(script)],
+                            '%d-%d' % (base, base + 16), '-timeout', '100s', sys.executable, str(script)],
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     try:
-        time.sleep(1.0)
         t0 = time.time()
-        ok = False
-        while time.time() - t0 < 30 and not ok:
-            out = subprocess.run([os.path.join(BIN, 'kungfu-test-util'), '-kill', '127.0.0.1:%d' % (base + 1)],
-                                 stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=30)
-            ok = out.returncode == 0
-            if not ok:
-                time.sleep(0.5)
-        assert ok, out.stdout
-        log, _ = run.communicate(timeout=45)
+        while time.time() - t0 < 60 and not all(os.path.exists(str(tmp_path / ('ready-%d' % r))) for r in (0, 1)):
+            time.sleep(0.2)
+        assert os.path.exists(str(tmp_path / 'ready-1')), 'workers never came up'
+        out = subprocess.run([os.path.join(BIN, 'kungfu-test-util'), '-kill', '127.0.0.1:%d' % (base + 1)],
+                             stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=30)
+        assert out.returncode == 0, out.stdout
+        log, _ = run.communicate(timeout=60)
     finally:
         if run.poll() is None:
             run.kill()
