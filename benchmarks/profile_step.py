@@ -19,15 +19,27 @@ ap.add_argument('--model', default='resnet50')
 ap.add_argument('--rows', type=int, default=40)
 args = ap.parse_args()
 torch.backends.cudnn.benchmark = True
-model = models.to_b200_layout(getattr(models, args.model)(fused_bn=bool(args.fused_bn)).cuda())
-opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(model.parameters(), lr=0.01), model.named_parameters())
-x = torch.randn(args.batch_size, 3, 224, 224, device='cuda').bfloat16().contiguous(memory_format=torch.channels_last)
-y = torch.randint(0, 1000, (args.batch_size, ), device='cuda')
+is_bert = args.model.startswith('bert')
+if is_bert:
+    B, S, P = (args.batch_size if args.batch_size != 256 else 32), 128, 20
+    model = getattr(models, args.model)().cuda().to(torch.bfloat16)
+    ids = torch.randint(0, 30522, (B, S), device='cuda')
+    pos = torch.stack([torch.randperm(S, device='cuda')[:P].sort().values for _ in range(B)])
+    labels = torch.gather(ids, 1, pos)
+    nsp = torch.randint(0, 2, (B, ), device='cuda')
+else:
+    model = models.to_b200_layout(getattr(models, args.model)(fused_bn=bool(args.fused_bn)).cuda())
+    x = torch.randn(args.batch_size, 3, 224, 224, device='cuda').bfloat16().contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (args.batch_size, ), device='cuda')
+opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(model.parameters(), lr=0.01, momentum=0.9), model.named_parameters())
 
 
 def step():
     opt.zero_grad(set_to_none=True)
-    loss = F.cross_entropy(model(x).float(), y)
+    if is_bert:
+        loss = model(ids, mlm_labels=labels, nsp_labels=nsp, mlm_positions=pos)
+    else:
+        loss = F.cross_entropy(model(x).float(), y)
     loss.backward()
     opt.step()
 
@@ -39,4 +51,8 @@ with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) a
     for _ in range(3):
         step()
     torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by='cuda_time_total', row_limit=args.rows, max_name_column_width=90))
+rows = sorted(prof.key_averages(), key=lambda e: -e.self_device_time_total)
+total = sum(e.self_device_time_total for e in rows)
+print('# total device time per step: %.3f ms' % (total / 3e3))
+for e in rows[:args.rows]:
+    print('%8.3f ms/step %5d x  %s' % (e.self_device_time_total / 3e3, e.count // 3, e.key[:110]))

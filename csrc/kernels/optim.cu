@@ -20,6 +20,7 @@
 #include <cstring>
 #include <mutex>
 #include <type_traits>
+#include <vector>
 
 #include "common.cuh"
 #include "multimem.cuh"
@@ -751,15 +752,31 @@ extern "C" int kfb_fuse(void *const *srcs, const int64_t *counts,
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     // scratch layout: KFB_FUSE_MAX * FUSE_BX partial slots per launch.
     constexpr int BX = 16;
-    bool first       = true;
+    // Every entry gets one row of BX blocks, so a big tensor is cut into pieces first: 16 blocks
+    // cannot stream a 23 M-element embedding gradient at HBM speed. The piece size is a multiple
+    // of 16 elements, which keeps the 16-byte alignment of both sides.
+    constexpr int64_t PIECE = 1 << 19;
+    const size_t esz        = src_dtype == KFB_F32 ? 4 : 2;
+    struct Piece {
+        void *src;
+        int64_t count, off;
+    };
+    std::vector<Piece> pieces;
+    pieces.reserve(n + 64);
+    for (int i = 0; i < n; ++i)
+        for (int64_t o = 0; o < counts[i]; o += PIECE)
+            pieces.push_back({static_cast<char *>(srcs[i]) + o * esz, std::min(PIECE, counts[i] - o), dst_offs[i] + o});
+    if (pieces.empty() && sumsq_out) KFB_CUDA_OK(cudaMemsetAsync(sumsq_out, 0, sizeof(float), s));
+    n          = static_cast<int>(pieces.size());
+    bool first = true;
     for (int base = 0; base < n; base += KFB_FUSE_MAX) {
         FuseArgs a;
         memset(&a, 0, sizeof(a));
         a.n = std::min(KFB_FUSE_MAX, n - base);
         for (int i = 0; i < a.n; ++i) {
-            a.src[i]   = srcs[base + i];
-            a.count[i] = counts[base + i];
-            a.off[i]   = dst_offs[base + i];
+            a.src[i]   = pieces[base + i].src;
+            a.count[i] = pieces[base + i].count;
+            a.off[i]   = pieces[base + i].off;
         }
         float *partials = sumsq_out ? scratch : nullptr;
         if (sumsq_out && !scratch) {

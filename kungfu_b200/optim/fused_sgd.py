@@ -10,6 +10,7 @@ which is what the reference's benchmarks wrap
 (/root/reference/benchmarks/system/benchmark_kungfu_torch.py:76-83).
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -30,6 +31,7 @@ class FusedSGD(torch.optim.Optimizer):
         self._arenas = None  # list of (group, [Arena])
         self._steps = 0
         self._blocks = blocks
+        self.local_blocks = int(os.environ.get('KUNGFU_LOCAL_STEP_BLOCKS', '128'))
         self._threads = threads
         self._local = None
         self.sumsq_global = None  # ||averaged grad||^2 of the last sync step (device float)
@@ -135,6 +137,7 @@ class FusedSGD(torch.optim.Optimizer):
                            min(blocks, 32), threads, K.stream_ptr())
                     k += 1
                     continue
+                step_blocks = blocks
                 if sync and comm.np > 1 and not comm.cross:
                     ga, _k1 = a.grads_buf.ptr_array()
                     pa, _k2 = a.params_buf.ptr_array()
@@ -144,10 +147,13 @@ class FusedSGD(torch.optim.Optimizer):
                     ga, _k1 = K.ptr_array([a.grads_buf.ptrs[me]])
                     pa, _k2 = K.ptr_array([a.params_buf.ptrs[me]])
                     cs = self._local_struct()
+                    # a purely local update is HBM-bound, not NVLink-bound: it needs every SM it can
+                    # get (the comm default of 32 CTAs reaches ~1.7 TB/s; 128 is the flag-slot limit)
+                    step_blocks = self.local_blocks
                 K.call('kfb_ssgd_fused_step', cs, ga, a.code, pa, a.code,
                        a.master.data_ptr(), a.mom.data_ptr(), a.count, float(step_scale),
                        C.byref(h), ss_g.data_ptr() if ss_g is not None else None,
-                       blocks, threads, K.stream_ptr())
+                       step_blocks, threads, K.stream_ptr())
                 k += 1
         if self.monitor_norms:
             self.sumsq_local = self._ss_local_parts[:k].sum()

@@ -60,7 +60,9 @@ class _PairAveraging(object):
             self._kf_started = True
         target = self._pick()
         me = max(comm.rank, 0)
-        blocks = self._blocks or comm.default_blocks
+        # one peer pull (NVLink) + a full-model local update (HBM): no CTA-indexed barrier in this kernel, so
+        # it takes as many CTAs as the launch check allows instead of the NVLink-sized comm default
+        blocks = self._blocks or max(comm.default_blocks, K.MAX_BLOCKS)
         threads = self._threads or comm.default_threads
         for g, arenas in self.arenas():
             h = self._hyper(g)
