@@ -1,0 +1,344 @@
+// y = LayerNorm(x + dropout(h)) * gamma + beta, forward and backward, bf16.
+//
+// The transformer block's "add & norm" (BERT: after the attention projection
+// and after the FFN) as ONE pass each way instead of dropout + add + layer-norm
+// (3 kernels, 4 reads + 3 writes of the [tokens, hidden] activation) and, on the
+// way back, layer-norm input grad + gamma/beta grad + dropout grad (3-4 kernels):
+//
+//   forward   reads h, x; writes y and s = x + dropout(h) (what backward needs),
+//             mean / rstd per row
+//   backward  reads dy, s; writes dx (= ds), dh (= ds * mask / (1-p)) and
+//             per-block partial sums of dgamma / dbeta, summed by a small second
+//             kernel in a fixed order (deterministic, no atomics)
+//
+// No dropout mask is stored: it is regenerated from a counter-based generator
+// (Philox 4x32-10) keyed by (seed, stream id of the call site) and indexed by
+// (training step, element), so forward and backward of the same step agree and
+// a CUDA graph replays with fresh masks as long as the step counter (a device
+// scalar the caller bumps once per step) advances.
+//
+// One warp per row, hidden size = VPL * 256 (256, 512, 768, 1024): lane l owns
+// 8 consecutive elements of every 256-element slice, so all global accesses are
+// 16-byte and coalesced, the row lives in registers, statistics are two-pass.
+//
+// The reference has no counterpart (its models are TensorFlow's); this serves
+// the BERT benchmark model (kungfu_b200/models/bert.py).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kungfu_b200.h"
+
+namespace kfb
+{
+void set_last_error(const char *fmt, ...);  // collectives.cu
+
+constexpr int LN_THREADS = 256;
+constexpr int LN_WARPS   = LN_THREADS / 32;
+
+// Philox 4x32-10 (Salmon et al., SC'11): 128 random bits per (counter, key)
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k)
+{
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u;
+        k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+
+struct DropoutCfg {
+    float p;                   // drop probability; 0 disables
+    uint64_t seed;
+    const long long *step;     // device scalar: training step (may be NULL = 0)
+    uint32_t stream;           // distinguishes call sites within a step
+};
+
+// keep-mask of the 8 elements of vector `vec` (global index of the 16-byte group): bit j = keep element j
+__device__ __forceinline__ uint32_t keep_mask8(const DropoutCfg &d, unsigned long long step, unsigned long long vec)
+{
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)vec, (uint32_t)(vec >> 32), (uint32_t)step, (uint32_t)(step >> 32)),
+                                  make_uint2((uint32_t)d.seed ^ d.stream, (uint32_t)(d.seed >> 32)));
+    const uint32_t thr = (uint32_t)(d.p * 65536.0f);  // drop when the 16-bit draw is below p * 2^16
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+    uint32_t m = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        m |= ((w[j] & 0xFFFFu) >= thr ? 1u : 0u) << (2 * j);
+        m |= ((w[j] >> 16) >= thr ? 1u : 0u) << (2 * j + 1);
+    }
+    return m;
+}
+
+__device__ __forceinline__ void unpack8(const uint4 &v, float (&f)[8])
+{
+    const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float2 t = __bfloat1622float2(h[j]);
+        f[2 * j]       = t.x;
+        f[2 * j + 1]   = t.y;
+    }
+}
+
+__device__ __forceinline__ uint4 pack8(const float (&f)[8])
+{
+    uint4 v;
+    __nv_bfloat162 *h = reinterpret_cast<__nv_bfloat162 *>(&v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+    return v;
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(LN_THREADS)
+    k_add_dropout_ln_fwd(const uint4 *__restrict__ h, const uint4 *__restrict__ x, const uint4 *__restrict__ gamma,
+                         const uint4 *__restrict__ beta, uint4 *__restrict__ y, uint4 *__restrict__ s_out,
+                         float *__restrict__ mean_out, float *__restrict__ rstd_out, long long M, float eps,
+                         DropoutCfg d)
+{
+    constexpr int H   = VPL * 256;
+    constexpr int VEC = H / 8;  // 16-byte vectors per row
+    const int lane    = threadIdx.x & 31;
+    const long long warp0  = (long long)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+    const long long nwarps = (long long)gridDim.x * LN_WARPS;
+    const unsigned long long step = d.step ? (unsigned long long)*d.step : 0ull;
+    const float keep_scale        = d.p > 0.f ? 1.0f / (1.0f - d.p) : 1.0f;
+
+    float g[VPL][8], b[VPL][8];
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        unpack8(gamma[v * 32 + lane], g[v]);
+        unpack8(beta[v * 32 + lane], b[v]);
+    }
+    for (long long row = warp0; row < M; row += nwarps) {
+        float s[VPL][8];
+        float sum = 0.f;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const long long vi = row * VEC + v * 32 + lane;
+            float hv[8];
+            unpack8(h[vi], hv);
+            if (d.p > 0.f) {
+                const uint32_t keep = keep_mask8(d, step, (unsigned long long)vi);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) hv[j] = (keep >> j) & 1u ? hv[j] * keep_scale : 0.f;
+            }
+            if (x != nullptr) {
+                float xv[8];
+                unpack8(x[vi], xv);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) hv[j] += xv[j];
+            }
+            // statistics are taken over the bf16-rounded sum: exactly what backward will read back
+            const uint4 packed = pack8(hv);
+            if (s_out != nullptr) s_out[vi] = packed;
+            unpack8(packed, s[v]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sum += s[v][j];
+        }
+        const float mean = warp_sum(sum) * (1.0f / H);
+        float sq         = 0.f;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float c = s[v][j] - mean;
+                sq            = fmaf(c, c, sq);
+            }
+        const float rstd = rsqrtf(warp_sum(sq) * (1.0f / H) + eps);
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = fmaf((s[v][j] - mean) * rstd, g[v][j], b[v][j]);
+            y[row * VEC + v * 32 + lane] = pack8(o);
+        }
+        if (lane == 0 && mean_out != nullptr) {
+            mean_out[row] = mean;
+            rstd_out[row] = rstd;
+        }
+    }
+}
+
+// partial: [gridDim.x][2][H] floats (dgamma row then dbeta row per block)
+template <int VPL>
+__global__ void __launch_bounds__(LN_THREADS)
+    k_add_dropout_ln_bwd(const uint4 *__restrict__ dy, const uint4 *__restrict__ s, const float *__restrict__ mean,
+                         const float *__restrict__ rstd, const uint4 *__restrict__ gamma, uint4 *__restrict__ dx,
+                         uint4 *__restrict__ dh, float *__restrict__ partial, long long M, DropoutCfg d)
+{
+    constexpr int H   = VPL * 256;
+    constexpr int VEC = H / 8;
+    const int lane    = threadIdx.x & 31;
+    const int warp    = threadIdx.x >> 5;
+    const long long warp0  = (long long)blockIdx.x * LN_WARPS + warp;
+    const long long nwarps = (long long)gridDim.x * LN_WARPS;
+    const unsigned long long step = d.step ? (unsigned long long)*d.step : 0ull;
+    const float keep_scale        = d.p > 0.f ? 1.0f / (1.0f - d.p) : 1.0f;
+
+    float g[VPL][8], dg[VPL][8], db[VPL][8];
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        unpack8(gamma[v * 32 + lane], g[v]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dg[v][j] = db[v][j] = 0.f;
+    }
+    for (long long row = warp0; row < M; row += nwarps) {
+        const float mu = mean[row], rs = rstd[row];
+        float xh[VPL][8], gy[VPL][8];
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const long long vi = row * VEC + v * 32 + lane;
+            float dyv[8], sv[8];
+            unpack8(dy[vi], dyv);
+            unpack8(s[vi], sv);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                xh[v][j] = (sv[j] - mu) * rs;
+                gy[v][j] = dyv[j] * g[v][j];
+                c1 += gy[v][j];
+                c2 = fmaf(gy[v][j], xh[v][j], c2);
+                dg[v][j] = fmaf(dyv[j], xh[v][j], dg[v][j]);
+                db[v][j] += dyv[j];
+            }
+        }
+        c1 = warp_sum(c1) * (1.0f / H);
+        c2 = warp_sum(c2) * (1.0f / H);
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const long long vi = row * VEC + v * 32 + lane;
+            float ds[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ds[j] = rs * (gy[v][j] - c1 - xh[v][j] * c2);
+            if (dx != nullptr) dx[vi] = pack8(ds);
+            if (dh != nullptr) {
+                if (d.p > 0.f) {
+                    const uint32_t keep = keep_mask8(d, step, (unsigned long long)vi);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) ds[j] = (keep >> j) & 1u ? ds[j] * keep_scale : 0.f;
+                }
+                dh[vi] = pack8(ds);
+            }
+        }
+    }
+    // block-level sum of the per-warp column accumulators, one quantity at a time (24 KiB of smem for H = 768)
+    __shared__ float red[LN_WARPS][H];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        __syncthreads();
+#pragma unroll
+        for (int v = 0; v < VPL; ++v)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) red[warp][(v * 32 + lane) * 8 + j] = q == 0 ? dg[v][j] : db[v][j];
+        __syncthreads();
+        for (int c = threadIdx.x; c < H; c += LN_THREADS) {
+            float t = 0.f;
+#pragma unroll
+            for (int w = 0; w < LN_WARPS; ++w) t += red[w][c];
+            partial[((size_t)blockIdx.x * 2 + q) * H + c] = t;
+        }
+    }
+}
+
+// dgamma[c] = sum_b partial[b][0][c], dbeta[c] = sum_b partial[b][1][c]; fixed order
+__global__ void __launch_bounds__(256)
+    k_ln_bwd_finalize(const float *__restrict__ partial, int blocks, int H, __nv_bfloat16 *__restrict__ dgamma,
+                      __nv_bfloat16 *__restrict__ dbeta)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= 2 * H) return;
+    const int q = c / H, col = c % H;
+    float t = 0.f;
+    for (int b = 0; b < blocks; ++b) t += partial[((size_t)b * 2 + q) * H + col];
+    (q == 0 ? dgamma : dbeta)[col] = __float2bfloat16(t);
+}
+
+static int ln_grid(long long M)
+{
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    static int cached[64];
+    if (dev >= 0 && dev < 64) {
+        if (cached[dev] == 0) cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev);
+        if (cached[dev] > 0) sms = cached[dev];
+    }
+    const long long want = (M + LN_WARPS - 1) / LN_WARPS;
+    const long long cap  = (long long)sms * 4;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+}  // namespace kfb
+
+extern "C" int kfb_ln_partial_floats(long long M, int H)
+{
+    return kfb::ln_grid(M) * 2 * H;
+}
+
+#define KFB_LN_DISPATCH(H, ...)                                                                   \
+    switch (H) {                                                                                  \
+    case 256: { constexpr int VPL = 1; __VA_ARGS__; } break;                                      \
+    case 512: { constexpr int VPL = 2; __VA_ARGS__; } break;                                      \
+    case 768: { constexpr int VPL = 3; __VA_ARGS__; } break;                                      \
+    case 1024: { constexpr int VPL = 4; __VA_ARGS__; } break;                                     \
+    default:                                                                                      \
+        kfb::set_last_error("add_dropout_ln: hidden size %d not in {256, 512, 768, 1024}", H);    \
+        return (int)cudaErrorInvalidValue;                                                        \
+    }
+
+extern "C" int kfb_add_dropout_ln_fwd(const void *h, const void *x, const void *gamma, const void *beta, void *y,
+                                      void *s_out, float *mean, float *rstd, long long M, int H, float eps, float p,
+                                      unsigned long long seed, const long long *step, unsigned int stream_id,
+                                      void *stream)
+{
+    using namespace kfb;
+    if (M <= 0) return 0;
+    if (p < 0.f || p >= 1.f) {
+        set_last_error("add_dropout_ln: dropout probability %f outside [0, 1)", p);
+        return (int)cudaErrorInvalidValue;
+    }
+    const DropoutCfg d{p, seed, step, stream_id};
+    const int grid = ln_grid(M);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KFB_LN_DISPATCH(H, (k_add_dropout_ln_fwd<VPL><<<grid, LN_THREADS, 0, st>>>(
+                           static_cast<const uint4 *>(h), static_cast<const uint4 *>(x),
+                           static_cast<const uint4 *>(gamma), static_cast<const uint4 *>(beta),
+                           static_cast<uint4 *>(y), static_cast<uint4 *>(s_out), mean, rstd, M, eps, d)));
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) set_last_error("add_dropout_ln fwd launch: %s", cudaGetErrorString(e));
+    return (int)e;
+}
+
+extern "C" int kfb_add_dropout_ln_bwd(const void *dy, const void *s, const float *mean, const float *rstd,
+                                      const void *gamma, void *dx, void *dh, void *dgamma, void *dbeta,
+                                      float *partial, long long M, int H, float p, unsigned long long seed,
+                                      const long long *step, unsigned int stream_id, void *stream)
+{
+    using namespace kfb;
+    if (M <= 0) return 0;
+    const DropoutCfg d{p, seed, step, stream_id};
+    const int grid = ln_grid(M);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    KFB_LN_DISPATCH(H, (k_add_dropout_ln_bwd<VPL><<<grid, LN_THREADS, 0, st>>>(
+                           static_cast<const uint4 *>(dy), static_cast<const uint4 *>(s), mean, rstd,
+                           static_cast<const uint4 *>(gamma), static_cast<uint4 *>(dx), static_cast<uint4 *>(dh),
+                           partial, M, d)));
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) {
+        k_ln_bwd_finalize<<<(2 * H + 255) / 256, 256, 0, st>>>(partial, grid, H, static_cast<__nv_bfloat16 *>(dgamma),
+                                                                static_cast<__nv_bfloat16 *>(dbeta));
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) set_last_error("add_dropout_ln bwd launch: %s", cudaGetErrorString(e));
+    return (int)e;
+}

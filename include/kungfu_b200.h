@@ -342,6 +342,31 @@ int kfb_linear_act(const void *x, const void *w, const void *bias, int bias_dtyp
 /* dz = dy * act'(z), n bf16 elements (n % 8 == 0) */
 int kfb_act_bwd(const void *dy, const void *z, void *dz, size_t n, int act,
                 void *stream);
+/* -1: choose per shape, 0: one CTA per tile (cta_group::1), 1: CTA pairs (cta_group::2) */
+void kfb_linear_act_set_mode(int mode);
+
+/* ---- fused "add & norm" (csrc/kernels/ln_fused.cu) ---------------------------
+ * y = LayerNorm(x + dropout(h)) * gamma + beta over rows of H bf16 elements,
+ * H in {256, 512, 768, 1024}; all tensors bf16, mean / rstd fp32 [M]. x may be
+ * NULL (no residual), s_out / mean / rstd may be NULL in inference. The dropout
+ * mask is never stored: forward and backward regenerate it from
+ * (seed, stream_id, *step, element index); `step` is a device scalar the caller
+ * advances once per training step (NULL = 0). Backward writes dx (= ds), dh
+ * (= ds * mask / (1-p); either may be NULL) and dgamma / dbeta through
+ * `partial`, a scratch of kfb_ln_partial_floats(M, H) floats. No counterpart in
+ * the reference (its models are TensorFlow's). */
+int kfb_ln_partial_floats(long long M, int H);
+int kfb_add_dropout_ln_fwd(const void *h, const void *x, const void *gamma,
+                           const void *beta, void *y, void *s_out, float *mean,
+                           float *rstd, long long M, int H, float eps, float p,
+                           unsigned long long seed, const long long *step,
+                           unsigned int stream_id, void *stream);
+int kfb_add_dropout_ln_bwd(const void *dy, const void *s, const float *mean,
+                           const float *rstd, const void *gamma, void *dx,
+                           void *dh, void *dgamma, void *dbeta, float *partial,
+                           long long M, int H, float p, unsigned long long seed,
+                           const long long *step, unsigned int stream_id,
+                           void *stream);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,7 @@ CUDA_SOURCES = [
     'csrc/kernels/bn_act.cu',
     'csrc/kernels/pool.cu',
     'csrc/kernels/linear_tc.cu',
+    'csrc/kernels/ln_fused.cu',
     'csrc/device/symm.cu',
 ]
 HOST_LIB_DIRS = ['csrc/core', 'csrc/ctrl', 'csrc/elastic', 'csrc/capi']

@@ -15,19 +15,28 @@ import torch.nn.functional as F
 
 class BertConfig(object):
     def __init__(self, vocab_size=30522, hidden=768, layers=12, heads=12, intermediate=3072, max_pos=512,
-                 type_vocab=2, dropout=0.1, eps=1e-12, fused_linear=False):
+                 type_vocab=2, dropout=0.1, eps=1e-12, fused_linear=False, fused_ln=False, pad_vocab=1):
         self.vocab_size, self.hidden, self.layers, self.heads = vocab_size, hidden, layers, heads
         self.intermediate, self.max_pos, self.type_vocab, self.dropout, self.eps = intermediate, max_pos, type_vocab, dropout, eps
         # fused_linear: the FFN / projection layers run the tcgen05 kernel with the
         # bias (+GELU) epilogue (kungfu_b200.ops.linear); same parameters either way
         self.fused_linear = fused_linear
+        # fused_ln: "add & norm" (dropout + residual + LayerNorm) as one kernel each way
+        # (kungfu_b200.ops.fused_ln); same parameters either way
+        self.fused_ln = fused_ln
+        # pad_vocab=8: embedding / decoder rows rounded up to a multiple of 8 so the 30522-way
+        # decoder GEMMs take the aligned tensor-core kernels (pad logits are pinned to -1e4)
+        self.pad_vocab = max(1, int(pad_vocab))
+        self.vocab_rows = (vocab_size + self.pad_vocab - 1) // self.pad_vocab * self.pad_vocab
 
 
 class _Layer(nn.Module):
-    def __init__(self, c):
+    def __init__(self, c, index=0):
         super().__init__()
         from ..ops.linear import LinearAct
         self.heads = c.heads
+        self.fused_ln = c.fused_ln
+        self.index = index
         # plain projections stay library GEMMs; the layer whose epilogue has work to fuse
         # (bias + GELU over the [tokens, intermediate] activation) runs the tcgen05 kernel
         self.qkv = nn.Linear(c.hidden, 3 * c.hidden)
@@ -43,6 +52,13 @@ class _Layer(nn.Module):
         q, k, v = self.qkv(x).view(B, S, 3, self.heads, H // self.heads).permute(2, 0, 3, 1, 4)
         a = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=self.drop if self.training else 0.0)
         a = a.transpose(1, 2).reshape(B, S, H)
+        if self.fused_ln:
+            from ..ops.fused_ln import add_dropout_layer_norm as adln
+            x = adln(self.proj(a), x, self.ln1.weight, self.ln1.bias, self.drop, self.training, self.ln1.eps,
+                     stream_id=2 * self.index + 1)
+            h = self.fc2(self.fc1(x))
+            return adln(h, x, self.ln2.weight, self.ln2.bias, self.drop, self.training, self.ln2.eps,
+                        stream_id=2 * self.index + 2)
         x = self.ln1(x + F.dropout(self.proj(a), self.drop, self.training))
         h = self.fc2(self.fc1(x))  # fc1 applies the GELU (fused epilogue or F.gelu)
         return self.ln2(x + F.dropout(h, self.drop, self.training))
@@ -53,18 +69,21 @@ class BertForPreTraining(nn.Module):
         super().__init__()
         c = config or BertConfig()
         self.config = c
-        self.tok = nn.Embedding(c.vocab_size, c.hidden)
+        self.tok = nn.Embedding(c.vocab_rows, c.hidden)
         self.pos = nn.Embedding(c.max_pos, c.hidden)
         self.typ = nn.Embedding(c.type_vocab, c.hidden)
         self.ln = nn.LayerNorm(c.hidden, eps=c.eps)
-        self.layers = nn.ModuleList([_Layer(c) for _ in range(c.layers)])
+        self.layers = nn.ModuleList([_Layer(c, i) for i in range(c.layers)])
         self.pooler = nn.Linear(c.hidden, c.hidden)
         from ..ops.linear import LinearAct
         self.mlm_dense = LinearAct(c.hidden, c.hidden, act='gelu', fused=c.fused_linear)
         self.mlm_ln = nn.LayerNorm(c.hidden, eps=c.eps)
-        self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_size))
+        self.mlm_bias = nn.Parameter(torch.zeros(c.vocab_rows))
         self.nsp = nn.Linear(c.hidden, 2)
         self.apply(self._init)
+        if c.vocab_rows > c.vocab_size:
+            with torch.no_grad():
+                self.mlm_bias[c.vocab_size:] = -1e4  # pad tokens never win the softmax
 
     @staticmethod
     def _init(m):
@@ -82,17 +101,24 @@ class BertForPreTraining(nn.Module):
         pos = torch.arange(S, device=ids.device).unsqueeze(0)
         x = self.tok(ids) + self.pos(pos) + self.typ(token_type if token_type is not None else torch.zeros_like(ids))
         x = F.dropout(self.ln(x), self.config.dropout, self.training)
+        if self.config.fused_ln and self.training and x.is_cuda:
+            from ..ops.fused_ln import DropoutState
+            DropoutState.advance(x.device)  # fresh dropout masks for this step (one tiny device op, graph-capturable)
         for layer in self.layers:
             x = layer(x)
         x_mlm = x
         if mlm_positions is not None:
             x_mlm = torch.gather(x, 1, mlm_positions.unsqueeze(-1).expand(-1, -1, x.shape[-1]))
-        h = self.mlm_ln(self.mlm_dense(x_mlm))
+        if self.config.fused_ln:
+            from ..ops.fused_ln import add_dropout_layer_norm as adln
+            h = adln(self.mlm_dense(x_mlm), None, self.mlm_ln.weight, self.mlm_ln.bias, 0.0, False, self.mlm_ln.eps)
+        else:
+            h = self.mlm_ln(self.mlm_dense(x_mlm))
         logits = F.linear(h, self.tok.weight, self.mlm_bias.to(h.dtype))  # tied decoder
         pooled = torch.tanh(self.pooler(x[:, 0]))
         nsp_logits = self.nsp(pooled)
         if mlm_labels is None:
-            return logits, nsp_logits
+            return logits[..., :self.config.vocab_size], nsp_logits
         loss = F.cross_entropy(logits.float().view(-1, logits.shape[-1]), mlm_labels.view(-1), ignore_index=-100)
         if nsp_labels is not None:
             loss = loss + F.cross_entropy(nsp_logits.float(), nsp_labels)
