@@ -37,7 +37,6 @@ class FusedSGD(torch.optim.Optimizer):
         self.sumsq_global = None  # ||averaged grad||^2 of the last sync step (device float)
         self.sumsq_local = None  # ||local grad||^2 of the last step (device float)
         self.monitor_norms = False
-        import os
         self.use_nvls = os.environ.get('KUNGFU_FUSED_NVLS', '1') != '0'
         self.nvls_min_bytes = int(os.environ.get('KUNGFU_FUSED_NVLS_MIN_BYTES', str(256 << 10)))
 

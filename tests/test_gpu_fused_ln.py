@@ -96,7 +96,7 @@ def test_bert_fused_ln_matches_unfused_in_eval_and_trains():
     assert float((ya.float() - yb.float()).norm() / ya.float().norm()) < 3e-2
     b.train()
     labels = torch.randint(0, 1000, (4, 64), device='cuda')
-    loss = b(ids, mlm_labels=labels)
+    loss = b(ids, mlm_labels=labels, nsp_labels=torch.randint(0, 2, (4, ), device='cuda'))
     loss.backward()
     assert torch.isfinite(loss)
     assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in b.parameters())
