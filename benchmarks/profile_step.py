@@ -19,12 +19,14 @@ ap.add_argument('--model', default='resnet50')
 ap.add_argument('--rows', type=int, default=40)
 ap.add_argument('--fused-ln', type=int, default=0)
 ap.add_argument('--pad-vocab', type=int, default=1)
+ap.add_argument('--fused-grads', type=int, default=0)
+ap.add_argument('--fused-linear', type=int, default=0)
 args = ap.parse_args()
 torch.backends.cudnn.benchmark = True
 is_bert = args.model.startswith('bert')
 if is_bert:
     B, S, P = (args.batch_size if args.batch_size != 256 else 32), 128, 20
-    model = getattr(models, args.model)(fused_ln=bool(args.fused_ln), pad_vocab=args.pad_vocab).cuda().to(torch.bfloat16)
+    model = getattr(models, args.model)(fused_ln=bool(args.fused_ln), pad_vocab=args.pad_vocab, fused_grads=bool(args.fused_grads), fused_linear=bool(args.fused_linear)).cuda().to(torch.bfloat16)
     ids = torch.randint(0, 30522, (B, S), device='cuda')
     pos = torch.stack([torch.randperm(S, device='cuda')[:P].sort().values for _ in range(B)])
     labels = torch.gather(ids, 1, pos)

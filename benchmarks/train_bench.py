@@ -37,6 +37,7 @@ ap.add_argument('--warmup', type=int, default=5)
 ap.add_argument('--fused-bn', type=int, default=1)
 ap.add_argument('--fused-linear', type=int, default=0, help='BERT: tcgen05 linear layers with fused bias/GELU')
 ap.add_argument('--fused-ln', type=int, default=0, help='BERT: fused dropout+residual+LayerNorm kernels')
+ap.add_argument('--fused-grads', type=int, default=0, help='BERT: column-sum bias grads + one-pass qkv grad gather')
 ap.add_argument('--pad-vocab', type=int, default=1, help='BERT: round the vocabulary up to a multiple of this (8 = aligned decoder GEMMs)')
 ap.add_argument('--mlm-positions', type=int, default=0,
                 help='BERT: masked positions per sequence fed as masked_lm_positions (original BERT uses 20 at seq 128); '
@@ -54,7 +55,7 @@ is_bert = args.model.startswith('bert')
 B = args.batch_size
 
 if is_bert:
-    model = getattr(models, args.model)(fused_linear=bool(args.fused_linear), fused_ln=bool(args.fused_ln),
+    model = getattr(models, args.model)(fused_linear=bool(args.fused_linear), fused_ln=bool(args.fused_ln), fused_grads=bool(args.fused_grads),
                                        pad_vocab=args.pad_vocab).to(dev).to(torch.bfloat16)
     ids = torch.randint(0, 30522, (B, args.seq_len), device=dev)
     labels = ids.clone()

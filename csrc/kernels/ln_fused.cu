@@ -252,20 +252,31 @@ __global__ void __launch_bounds__(LN_THREADS)
     }
 }
 
-// dgamma[c] = sum_b partial[b][0][c], dbeta[c] = sum_b partial[b][1][c]; fixed order
-__global__ void __launch_bounds__(256)
+// dgamma[c] = sum_b partial[b][0][c], dbeta[c] = sum_b partial[b][1][c]. 32 x 32 threads per block: 32
+// consecutive columns (coalesced), 32 threads per column each summing every 32nd block, then a fixed-order
+// combine through shared memory (deterministic).
+__global__ void __launch_bounds__(1024)
     k_ln_bwd_finalize(const float *__restrict__ partial, int blocks, int H, __nv_bfloat16 *__restrict__ dgamma,
                       __nv_bfloat16 *__restrict__ dbeta)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= 2 * H) return;
-    const int q = c / H, col = c % H;
-    float t = 0.f;
-    for (int b = 0; b < blocks; ++b) t += partial[((size_t)b * 2 + q) * H + col];
-    (q == 0 ? dgamma : dbeta)[col] = __float2bfloat16(t);
+    __shared__ float red[32][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;  // column in [0, 2H)
+    float t     = 0.f;
+    if (c < 2 * H) {
+        const int q = c / H, col = c % H;
+        for (int b = threadIdx.y; b < blocks; b += 32) t += partial[((size_t)b * 2 + q) * H + col];
+    }
+    red[threadIdx.y][threadIdx.x] = t;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < 2 * H) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) s += red[k][threadIdx.x];
+        (c < H ? dgamma : dbeta)[c % H] = __float2bfloat16(s);
+    }
 }
 
-static int ln_grid(long long M)
+static int sm_count()
 {
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
@@ -274,15 +285,157 @@ static int ln_grid(long long M)
         if (cached[dev] == 0) cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev);
         if (cached[dev] > 0) sms = cached[dev];
     }
+    return sms;
+}
+
+// forward: up to 4 CTAs per SM; backward: its register footprint allows one CTA per SM, so one wave
+static int ln_grid(long long M, int per_sm)
+{
     const long long want = (M + LN_WARPS - 1) / LN_WARPS;
-    const long long cap  = (long long)sms * 4;
+    const long long cap  = (long long)sm_count() * per_sm;
     return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+// ---- column sum: out[N] = sum over rows of a[M, N] (bias gradients) -------------------------
+//
+// grid (N / 64, R): a block owns 64 columns (one bf16 pair per lane) of one row split; its 8 warps
+// stride over the rows, combine through shared memory and write one partial row. The last block
+// of a column group to finish (ticket counter, reset for the next call) adds the R partials in
+// order - deterministic, one launch, no atomics on the data.
+__global__ void __launch_bounds__(256)
+    k_colsum(const __nv_bfloat162 *__restrict__ a, long long M, int N, __nv_bfloat16 *__restrict__ out,
+             float *__restrict__ partial, unsigned int *__restrict__ tickets)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int R        = gridDim.y;
+    const int col2     = blockIdx.x * 32 + lane;  // index of the bf16 pair within a row
+    const long long r0 = (M * blockIdx.y) / R, r1 = (M * (blockIdx.y + 1)) / R;
+    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll 4
+    for (long long r = r0 + warp; r < r1; r += 8) {
+        const float2 v = __bfloat1622float2(a[r * (N / 2) + col2]);
+        acc.x += v.x;
+        acc.y += v.y;
+    }
+    __shared__ float2 red[8][32];
+    __shared__ bool is_last;
+    red[warp][lane] = acc;
+    __syncthreads();
+    if (warp == 0) {
+        float2 t = red[0][lane];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) {
+            t.x += red[w][lane].x;
+            t.y += red[w][lane].y;
+        }
+        reinterpret_cast<float2 *>(partial)[(size_t)blockIdx.y * (N / 2) + col2] = t;
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) is_last = atomicAdd(&tickets[blockIdx.x], 1u) == (unsigned)R - 1;
+        __syncwarp();
+        if (is_last) {
+            __threadfence();
+            float2 s = make_float2(0.f, 0.f);
+            for (int y = 0; y < R; ++y) {
+                const float2 p = __ldcg(reinterpret_cast<const float2 *>(partial) + (size_t)y * (N / 2) + col2);
+                s.x += p.x;
+                s.y += p.y;
+            }
+            reinterpret_cast<__nv_bfloat162 *>(out)[col2] = __floats2bfloat162_rn(s.x, s.y);
+            if (lane == 0) tickets[blockIdx.x] = 0u;
+        }
+    }
+}
+
+// ---- gradient of "split a packed qkv into heads": (dq, dk, dv) [B, h, S, d] -> dqkv [B, S, 3, h, d] ----
+//
+// Autograd does this as a stack (one pass) followed by a permuting copy (another pass); this is one
+// 16-byte-vectorised gather. Sources may be strided in (b, h, s); d is contiguous.
+struct PackQkvArgs {
+    const uint4 *src[3];
+    long long sb[3], sh[3], ss[3];  // strides in elements
+    int B, h, S, d8;                // d8 = d / 8
+};
+
+__global__ void __launch_bounds__(256) k_pack_qkv_grad(const __grid_constant__ PackQkvArgs a, uint4 *__restrict__ out)
+{
+    const long long total = (long long)a.B * a.S * 3 * a.h * a.d8;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        long long t  = i;
+        const int v  = (int)(t % a.d8);
+        t /= a.d8;
+        const int hh = (int)(t % a.h);
+        t /= a.h;
+        const int w = (int)(t % 3);
+        t /= 3;
+        const int s = (int)(t % a.S);
+        const int b = (int)(t / a.S);
+        const long long off = b * a.sb[w] + hh * a.sh[w] + s * a.ss[w];  // elements; multiple of 8 by contract
+        out[i]              = a.src[w][off / 8 + v];
+    }
 }
 }  // namespace kfb
 
 extern "C" int kfb_ln_partial_floats(long long M, int H)
 {
-    return kfb::ln_grid(M) * 2 * H;
+    return kfb::ln_grid(M, 1) * 2 * H;
+}
+
+extern "C" int kfb_colsum_scratch_floats(int N)
+{
+    return 64 * N + N / 64 + 64;  // up to 64 row splits of partials, then the tickets
+}
+
+extern "C" int kfb_colsum(const void *a, long long M, int N, void *out, float *scratch, void *stream)
+{
+    using namespace kfb;
+    if (N <= 0 || (N % 64) != 0 || M <= 0) {
+        set_last_error("colsum: N must be a positive multiple of 64 and M > 0 (got M=%lld N=%d)", M, N);
+        return (int)cudaErrorInvalidValue;
+    }
+    const int groups = N / 64;
+    int R            = (3 * sm_count() + groups - 1) / groups;
+    if (R > 64) R = 64;
+    if (R > M) R = (int)M;
+    if (R < 1) R = 1;
+    unsigned int *tickets = reinterpret_cast<unsigned int *>(scratch + (size_t)64 * N);
+    k_colsum<<<dim3(groups, R), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat162 *>(a), M, N, static_cast<__nv_bfloat16 *>(out), scratch, tickets);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) set_last_error("colsum launch: %s", cudaGetErrorString(e));
+    return (int)e;
+}
+
+extern "C" int kfb_pack_qkv_grad(const void *dq, const void *dk, const void *dv, const long long *strides9, int B,
+                                 int h, int S, int d, void *out, void *stream)
+{
+    using namespace kfb;
+    if (d % 8) {
+        set_last_error("pack_qkv_grad: head dim %d must be a multiple of 8", d);
+        return (int)cudaErrorInvalidValue;
+    }
+    PackQkvArgs a;
+    const void *src[3] = {dq, dk, dv};
+    for (int w = 0; w < 3; ++w) {
+        a.src[w] = static_cast<const uint4 *>(src[w]);
+        a.sb[w]  = strides9[3 * w];
+        a.sh[w]  = strides9[3 * w + 1];
+        a.ss[w]  = strides9[3 * w + 2];
+        if ((a.sb[w] | a.sh[w] | a.ss[w]) % 8 || (reinterpret_cast<uintptr_t>(src[w]) & 15)) {
+            set_last_error("pack_qkv_grad: sources must be 16-byte aligned with strides that are multiples of 8");
+            return (int)cudaErrorInvalidValue;
+        }
+    }
+    a.B = B, a.h = h, a.S = S, a.d8 = d / 8;
+    const long long total = (long long)B * S * 3 * h * a.d8;
+    if (total == 0) return 0;
+    long long want = (total + 255) / 256;
+    const int grid = (int)(want < (long long)sm_count() * 8 ? want : (long long)sm_count() * 8);
+    k_pack_qkv_grad<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a, static_cast<uint4 *>(out));
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) set_last_error("pack_qkv_grad launch: %s", cudaGetErrorString(e));
+    return (int)e;
 }
 
 #define KFB_LN_DISPATCH(H, ...)                                                                   \
@@ -308,7 +461,7 @@ extern "C" int kfb_add_dropout_ln_fwd(const void *h, const void *x, const void *
         return (int)cudaErrorInvalidValue;
     }
     const DropoutCfg d{p, seed, step, stream_id};
-    const int grid = ln_grid(M);
+    const int grid = ln_grid(M, 4);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     KFB_LN_DISPATCH(H, (k_add_dropout_ln_fwd<VPL><<<grid, LN_THREADS, 0, st>>>(
                            static_cast<const uint4 *>(h), static_cast<const uint4 *>(x),
@@ -327,7 +480,7 @@ extern "C" int kfb_add_dropout_ln_bwd(const void *dy, const void *s, const float
     using namespace kfb;
     if (M <= 0) return 0;
     const DropoutCfg d{p, seed, step, stream_id};
-    const int grid = ln_grid(M);
+    const int grid = ln_grid(M, 1);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     KFB_LN_DISPATCH(H, (k_add_dropout_ln_bwd<VPL><<<grid, LN_THREADS, 0, st>>>(
                            static_cast<const uint4 *>(dy), static_cast<const uint4 *>(s), mean, rstd,
@@ -335,8 +488,8 @@ extern "C" int kfb_add_dropout_ln_bwd(const void *dy, const void *s, const float
                            partial, M, d)));
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) {
-        k_ln_bwd_finalize<<<(2 * H + 255) / 256, 256, 0, st>>>(partial, grid, H, static_cast<__nv_bfloat16 *>(dgamma),
-                                                                static_cast<__nv_bfloat16 *>(dbeta));
+        k_ln_bwd_finalize<<<(2 * H + 31) / 32, dim3(32, 32), 0, st>>>(
+            partial, grid, H, static_cast<__nv_bfloat16 *>(dgamma), static_cast<__nv_bfloat16 *>(dbeta));
         e = cudaGetLastError();
     }
     if (e != cudaSuccess) set_last_error("add_dropout_ln bwd launch: %s", cudaGetErrorString(e));

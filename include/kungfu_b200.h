@@ -361,6 +361,18 @@ int kfb_add_dropout_ln_fwd(const void *h, const void *x, const void *gamma,
                            float *rstd, long long M, int H, float eps, float p,
                            unsigned long long seed, const long long *step,
                            unsigned int stream_id, void *stream);
+/* out[N] = column sums of a[M, N] (bf16; a bias gradient), N % 64 == 0. `scratch`
+ * holds kfb_colsum_scratch_floats(N) floats, ZEROED once by the caller (the
+ * kernel leaves its ticket counters at zero again); calls sharing a scratch
+ * must be stream-ordered. Deterministic. */
+int kfb_colsum_scratch_floats(int N);
+int kfb_colsum(const void *a, long long M, int N, void *out, float *scratch,
+               void *stream);
+/* dqkv[B, S, 3, h, d] = gather of dq, dk, dv (each logically [B, h, S, d], d
+ * contiguous; strides9 = {stride_b, stride_h, stride_s} x 3 in elements). */
+int kfb_pack_qkv_grad(const void *dq, const void *dk, const void *dv,
+                      const long long *strides9, int B, int h, int S, int d,
+                      void *out, void *stream);
 int kfb_add_dropout_ln_bwd(const void *dy, const void *s, const float *mean,
                            const float *rstd, const void *gamma, void *dx,
                            void *dh, void *dgamma, void *dbeta, float *partial,

@@ -15,7 +15,8 @@ import torch.nn.functional as F
 
 class BertConfig(object):
     def __init__(self, vocab_size=30522, hidden=768, layers=12, heads=12, intermediate=3072, max_pos=512,
-                 type_vocab=2, dropout=0.1, eps=1e-12, fused_linear=False, fused_ln=False, pad_vocab=1):
+                 type_vocab=2, dropout=0.1, eps=1e-12, fused_linear=False, fused_ln=False, fused_grads=False,
+                 pad_vocab=1):
         self.vocab_size, self.hidden, self.layers, self.heads = vocab_size, hidden, layers, heads
         self.intermediate, self.max_pos, self.type_vocab, self.dropout, self.eps = intermediate, max_pos, type_vocab, dropout, eps
         # fused_linear: the FFN / projection layers run the tcgen05 kernel with the
@@ -24,6 +25,9 @@ class BertConfig(object):
         # fused_ln: "add & norm" (dropout + residual + LayerNorm) as one kernel each way
         # (kungfu_b200.ops.fused_ln); same parameters either way
         self.fused_ln = fused_ln
+        # fused_grads: bias gradients through the column-sum kernel and a one-pass gather for the packed
+        # qkv gradient (kungfu_b200.ops.fused_ln) instead of autograd's generic reduce / stack / copy
+        self.fused_grads = fused_grads
         # pad_vocab=8: embedding / decoder rows rounded up to a multiple of 8 so the 30522-way
         # decoder GEMMs take the aligned tensor-core kernels (pad logits are pinned to -1e4)
         self.pad_vocab = max(1, int(pad_vocab))
@@ -36,6 +40,7 @@ class _Layer(nn.Module):
         from ..ops.linear import LinearAct
         self.heads = c.heads
         self.fused_ln = c.fused_ln
+        self.fused_grads = c.fused_grads
         self.index = index
         # plain projections stay library GEMMs; the layer whose epilogue has work to fuse
         # (bias + GELU over the [tokens, intermediate] activation) runs the tcgen05 kernel
@@ -47,18 +52,36 @@ class _Layer(nn.Module):
         self.ln2 = nn.LayerNorm(c.hidden, eps=c.eps)
         self.drop = c.dropout
 
+    def _lin(self, m, x):
+        """A plain projection: library GEMMs; with fused_grads its bias gradient comes from the
+        single-launch column-sum kernel instead of a generic reduction."""
+        if self.fused_grads:
+            from ..ops.fused_ln import linear_fast_bias_grad
+            return linear_fast_bias_grad(x, m.weight, m.bias)
+        return m(x)
+
     def forward(self, x, mask=None):
         B, S, H = x.shape
-        q, k, v = self.qkv(x).view(B, S, 3, self.heads, H // self.heads).permute(2, 0, 3, 1, 4)
+        if self.fused_grads:
+            from ..ops.fused_ln import split_qkv
+            q, k, v = split_qkv(self._lin(self.qkv, x), self.heads)
+        else:
+            q, k, v = self.qkv(x).view(B, S, 3, self.heads, H // self.heads).permute(2, 0, 3, 1, 4)
         a = F.scaled_dot_product_attention(q, k, v, attn_mask=mask, dropout_p=self.drop if self.training else 0.0)
         a = a.transpose(1, 2).reshape(B, S, H)
+        if self.fused_grads and not self.fc1.fused:
+            ffn = lambda t: self._lin(self.fc2, F.gelu(self._lin(self.fc1, t)))  # noqa: E731
+        else:
+            ffn = lambda t: self._lin(self.fc2, self.fc1(t))  # noqa: E731  (fc1 applies the GELU)
         if self.fused_ln:
             from ..ops.fused_ln import add_dropout_layer_norm as adln
-            x = adln(self.proj(a), x, self.ln1.weight, self.ln1.bias, self.drop, self.training, self.ln1.eps,
+            x = adln(self._lin(self.proj, a), x, self.ln1.weight, self.ln1.bias, self.drop, self.training, self.ln1.eps,
                      stream_id=2 * self.index + 1)
-            h = self.fc2(self.fc1(x))
-            return adln(h, x, self.ln2.weight, self.ln2.bias, self.drop, self.training, self.ln2.eps,
+            return adln(ffn(x), x, self.ln2.weight, self.ln2.bias, self.drop, self.training, self.ln2.eps,
                         stream_id=2 * self.index + 2)
+        if self.fused_grads:
+            x = self.ln1(x + F.dropout(self._lin(self.proj, a), self.drop, self.training))
+            return self.ln2(x + F.dropout(ffn(x), self.drop, self.training))
         x = self.ln1(x + F.dropout(self.proj(a), self.drop, self.training))
         h = self.fc2(self.fc1(x))  # fc1 applies the GELU (fused epilogue or F.gelu)
         return self.ln2(x + F.dropout(h, self.drop, self.training))

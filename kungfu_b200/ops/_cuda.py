@@ -122,6 +122,10 @@ _SIGS = {
     'kfb_linear_act': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     'kfb_linear_act_set_mode': (None, [C.c_int]),
     'kfb_ln_partial_floats': (C.c_int, [C.c_longlong, C.c_int]),
+    'kfb_colsum_scratch_floats': (C.c_int, [C.c_int]),
+    'kfb_colsum': (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'kfb_pack_qkv_grad': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_void_p, C.c_void_p]),
     'kfb_add_dropout_ln_fwd': (C.c_int, [C.c_void_p] * 8 + [C.c_longlong, C.c_int, C.c_float, C.c_float, C.c_ulonglong,
                                          C.c_void_p, C.c_uint, C.c_void_p]),
     'kfb_add_dropout_ln_bwd': (C.c_int, [C.c_void_p] * 10 + [C.c_longlong, C.c_int, C.c_float, C.c_ulonglong,

@@ -108,3 +108,95 @@ def add_dropout_layer_norm(h, x, gamma, beta, p=0.0, training=True, eps=1e-5, st
     if x is not None:
         s = x + s
     return F.layer_norm(s, (h.shape[-1], ), gamma, beta, eps)
+
+
+# ---- gradient-side helpers for transformer blocks ----------------------------------------------
+
+_colsum_scratch = {}
+
+
+def col_sum(a2):
+    """Column sums of a 2-D bf16 CUDA tensor (a bias gradient) with the deterministic single-launch
+    kernel (kfb_colsum); anything else goes to torch.sum."""
+    M, N = a2.shape
+    if not (a2.is_cuda and a2.dtype == torch.bfloat16 and N % 64 == 0 and M > 0 and a2.is_contiguous()):
+        return a2.sum(0)
+    key = (a2.device.index, N)
+    scratch = _colsum_scratch.get(key)
+    if scratch is None:
+        scratch = torch.zeros(K.lib().kfb_colsum_scratch_floats(N), dtype=torch.float32, device=a2.device)
+        _colsum_scratch[key] = scratch
+    out = torch.empty(N, dtype=a2.dtype, device=a2.device)
+    K.call('kfb_colsum', a2.data_ptr(), M, N, out.data_ptr(), scratch.data_ptr(), K.stream_ptr())
+    return out
+
+
+class _LinearFastBiasGrad(torch.autograd.Function):
+    """F.linear whose backward takes the bias gradient from col_sum instead of a generic reduction
+    (all three GEMMs stay library GEMMs)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return F.linear(x, weight, bias)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        dy2 = dy2 if dy2.is_contiguous() else dy2.contiguous()
+        x2 = x.reshape(-1, x.shape[-1])
+        dx = (dy2 @ weight).view(x.shape) if ctx.needs_input_grad[0] else None
+        dw = dy2.t() @ x2 if ctx.needs_input_grad[1] else None
+        db = col_sum(dy2) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db
+
+
+def linear_fast_bias_grad(x, weight, bias):
+    if x.is_cuda and x.dtype == torch.bfloat16 and bias is not None:
+        return _LinearFastBiasGrad.apply(x, weight, bias)
+    return F.linear(x, weight, bias)
+
+
+class _SplitQKV(torch.autograd.Function):
+    """[B, S, 3*H] -> q, k, v views of shape [B, heads, S, hd]. The backward gathers dq, dk, dv
+    straight into the packed [B, S, 3*H] layout with one kernel (autograd would stack them and then
+    run a permuting copy: two extra passes)."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads):
+        B, S, H3 = qkv.shape
+        hd = H3 // 3 // heads
+        ctx.dims = (B, S, heads, hd)
+        t = qkv.view(B, S, 3, heads, hd)
+        return t[:, :, 0].transpose(1, 2), t[:, :, 1].transpose(1, 2), t[:, :, 2].transpose(1, 2)
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        B, S, heads, hd = ctx.dims
+        ref = next(g for g in (dq, dk, dv) if g is not None)
+        gs = []
+        for g in (dq, dk, dv):
+            if g is None:
+                g = torch.zeros((B, heads, S, hd), dtype=ref.dtype, device=ref.device)
+            if g.stride(-1) != 1 or any(s % 8 for s in g.stride()[:3]) or g.data_ptr() % 16:
+                g = g.contiguous()
+            gs.append(g)
+        out = torch.empty((B, S, 3 * heads * hd), dtype=ref.dtype, device=ref.device)
+        strides = []
+        for g in gs:
+            strides += [g.stride(0), g.stride(1), g.stride(2)]
+        arr = (K.C.c_longlong * 9)(*strides)
+        K.call('kfb_pack_qkv_grad', gs[0].data_ptr(), gs[1].data_ptr(), gs[2].data_ptr(), arr, B, heads, S, hd,
+               out.data_ptr(), K.stream_ptr())
+        return out, None
+
+
+def split_qkv(qkv, heads):
+    """q, k, v [B, heads, S, hd] from a packed projection [B, S, 3*H]."""
+    B, S, H3 = qkv.shape
+    hd = H3 // 3 // heads
+    if qkv.is_cuda and qkv.dtype in (torch.bfloat16, torch.float16) and hd % 8 == 0 and qkv.is_contiguous():
+        return _SplitQKV.apply(qkv, heads)
+    return qkv.view(B, S, 3, heads, hd).permute(2, 0, 3, 1, 4)

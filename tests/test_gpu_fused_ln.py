@@ -100,3 +100,66 @@ def test_bert_fused_ln_matches_unfused_in_eval_and_trains():
     loss.backward()
     assert torch.isfinite(loss)
     assert all(p.grad is not None and bool(torch.isfinite(p.grad).all()) for p in b.parameters())
+
+
+@pytest.mark.parametrize('M,N', [(4096, 768), (4096, 3072), (640, 2304), (3, 64), (5000, 1024)])
+def test_col_sum_matches_fp32_and_is_deterministic(M, N):
+    from kungfu_b200.ops.fused_ln import col_sum
+    g = torch.Generator(device='cuda').manual_seed(M + N)
+    a = torch.randn(M, N, device='cuda', generator=g).to(torch.bfloat16)
+    out = col_sum(a)
+    ref = a.float().sum(0)
+    assert out.shape == (N, ) and out.dtype == torch.bfloat16
+    assert float((out.float() - ref).abs().max()) <= 0.01 * float(ref.abs().max()) + 0.05
+    for _ in range(3):  # tickets reset themselves: repeated calls on the same scratch agree bit for bit
+        assert torch.equal(col_sum(a), out)
+
+
+def test_split_qkv_forward_views_and_backward_gather():
+    from kungfu_b200.ops.fused_ln import split_qkv
+    B, S, heads, hd = 3, 40, 4, 64
+    qkv = torch.randn(B, S, 3 * heads * hd, device='cuda').to(torch.bfloat16).requires_grad_(True)
+    q, k, v = split_qkv(qkv, heads)
+    qr, kr, vr = qkv.detach().view(B, S, 3, heads, hd).permute(2, 0, 3, 1, 4)
+    assert torch.equal(q, qr) and torch.equal(k, kr) and torch.equal(v, vr)
+    gq, gk, gv = [torch.randn(B, heads, S, hd, device='cuda').to(torch.bfloat16) for _ in range(3)]
+    # one gradient arrives transposed in memory (strided), like attention backward may produce
+    gk_strided = gk.transpose(1, 2).contiguous().transpose(1, 2)
+    torch.autograd.backward([q, k, v], [gq, gk_strided, gv])
+    ref = torch.stack([gq, gk, gv], 0).permute(1, 3, 0, 2, 4).reshape(B, S, 3 * heads * hd)
+    assert torch.equal(qkv.grad, ref)
+
+
+def test_linear_fast_bias_grad_matches_autograd():
+    from kungfu_b200.ops.fused_ln import linear_fast_bias_grad
+    x = torch.randn(6, 100, 256, device='cuda').to(torch.bfloat16).requires_grad_(True)
+    w = (torch.randn(512, 256, device='cuda') / 16).to(torch.bfloat16).requires_grad_(True)
+    b = torch.randn(512, device='cuda').to(torch.bfloat16).requires_grad_(True)
+    y = linear_fast_bias_grad(x, w, b)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    x2, w2, b2 = [t.detach().clone().requires_grad_(True) for t in (x, w, b)]
+    F.linear(x2, w2, b2).backward(dy)
+    assert torch.equal(y, F.linear(x2, w2, b2))
+    assert float((x.grad.float() - x2.grad.float()).norm() / x2.grad.float().norm()) < 1e-2
+    assert float((w.grad.float() - w2.grad.float()).norm() / w2.grad.float().norm()) < 1e-2
+    assert float((b.grad.float() - b2.grad.float()).norm() / b2.grad.float().norm()) < 1e-2
+
+
+def test_bert_fused_grads_match_unfused_grads():
+    from kungfu_b200 import models
+    torch.manual_seed(0)
+    kw = dict(vocab_size=1000, hidden=256, layers=2, heads=4, intermediate=1024, max_pos=128, dropout=0.0)
+    a = models.bert_base(**kw).cuda().to(torch.bfloat16)
+    b = models.bert_base(fused_grads=True, fused_ln=True, **kw).cuda().to(torch.bfloat16)
+    b.load_state_dict(a.state_dict())
+    ids = torch.randint(0, 1000, (4, 64), device='cuda')
+    labels = torch.randint(0, 1000, (4, 64), device='cuda')
+    nsp = torch.randint(0, 2, (4, ), device='cuda')
+    la = a(ids, mlm_labels=labels, nsp_labels=nsp)
+    lb = b(ids, mlm_labels=labels, nsp_labels=nsp)
+    la.backward(), lb.backward()
+    assert abs(float(la) - float(lb)) < 5e-2
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        rel = float((p.grad.float() - q.grad.float()).norm() / p.grad.float().norm().clamp_min(1e-6))
+        assert rel < 0.15, '%s: %g' % (n, rel)
