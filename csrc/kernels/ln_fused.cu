@@ -302,48 +302,56 @@ static int ln_grid(long long M, int per_sm)
 // stride over the rows, combine through shared memory and write one partial row. The last block
 // of a column group to finish (ticket counter, reset for the next call) adds the R partials in
 // order - deterministic, one launch, no atomics on the data.
+// V = bf16 elements per lane: 8 (16-byte loads, a warp spans 256 columns) when N % 256 == 0, else 2
+template <int V>
 __global__ void __launch_bounds__(256)
-    k_colsum(const __nv_bfloat162 *__restrict__ a, long long M, int N, __nv_bfloat16 *__restrict__ out,
+    k_colsum(const __nv_bfloat16 *__restrict__ a, long long M, int N, __nv_bfloat16 *__restrict__ out,
              float *__restrict__ partial, unsigned int *__restrict__ tickets)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int R        = gridDim.y;
-    const int col2     = blockIdx.x * 32 + lane;  // index of the bf16 pair within a row
+    const int col      = (blockIdx.x * 32 + lane) * V;  // first column of this lane
     const long long r0 = (M * blockIdx.y) / R, r1 = (M * (blockIdx.y + 1)) / R;
-    float2 acc = make_float2(0.f, 0.f);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
 #pragma unroll 4
     for (long long r = r0 + warp; r < r1; r += 8) {
-        const float2 v = __bfloat1622float2(a[r * (N / 2) + col2]);
-        acc.x += v.x;
-        acc.y += v.y;
-    }
-    __shared__ float2 red[8][32];
-    __shared__ bool is_last;
-    red[warp][lane] = acc;
-    __syncthreads();
-    if (warp == 0) {
-        float2 t = red[0][lane];
+        if (V == 8) {
+            float f[8];
+            unpack8(*reinterpret_cast<const uint4 *>(a + r * N + col), f);
 #pragma unroll
-        for (int w = 1; w < 8; ++w) {
-            t.x += red[w][lane].x;
-            t.y += red[w][lane].y;
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        } else {
+            const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(a + r * N + col));
+            acc[0] += v.x;
+            acc[1] += v.y;
         }
-        reinterpret_cast<float2 *>(partial)[(size_t)blockIdx.y * (N / 2) + col2] = t;
+    }
+    __shared__ float red[8][32 * V + 1];
+    __shared__ bool is_last;
+#pragma unroll
+    for (int j = 0; j < V; ++j) red[warp][lane * V + j] = acc[j];
+    __syncthreads();
+    // all 256 threads combine the 8 warps' rows: thread t owns columns t, t + 256, ...
+    for (int c = threadIdx.x; c < 32 * V; c += 256) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += red[w][c];
+        partial[(size_t)blockIdx.y * N + blockIdx.x * 32 * V + c] = t;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(&tickets[blockIdx.x], 1u) == (unsigned)R - 1;
+    __syncthreads();
+    if (is_last) {
         __threadfence();
-        __syncwarp();
-        if (lane == 0) is_last = atomicAdd(&tickets[blockIdx.x], 1u) == (unsigned)R - 1;
-        __syncwarp();
-        if (is_last) {
-            __threadfence();
-            float2 s = make_float2(0.f, 0.f);
-            for (int y = 0; y < R; ++y) {
-                const float2 p = __ldcg(reinterpret_cast<const float2 *>(partial) + (size_t)y * (N / 2) + col2);
-                s.x += p.x;
-                s.y += p.y;
-            }
-            reinterpret_cast<__nv_bfloat162 *>(out)[col2] = __floats2bfloat162_rn(s.x, s.y);
-            if (lane == 0) tickets[blockIdx.x] = 0u;
+        for (int c = threadIdx.x; c < 32 * V; c += 256) {
+            float s = 0.f;
+            for (int y = 0; y < R; ++y) s += __ldcg(partial + (size_t)y * N + blockIdx.x * 32 * V + c);
+            out[blockIdx.x * 32 * V + c] = __float2bfloat16(s);
         }
+        if (threadIdx.x == 0) tickets[blockIdx.x] = 0u;
     }
 }
 
@@ -394,14 +402,20 @@ extern "C" int kfb_colsum(const void *a, long long M, int N, void *out, float *s
         set_last_error("colsum: N must be a positive multiple of 64 and M > 0 (got M=%lld N=%d)", M, N);
         return (int)cudaErrorInvalidValue;
     }
-    const int groups = N / 64;
+    const bool wide  = (N % 256) == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0;
+    const int groups = wide ? N / 256 : N / 64;
     int R            = (3 * sm_count() + groups - 1) / groups;
     if (R > 64) R = 64;
     if (R > M) R = (int)M;
     if (R < 1) R = 1;
     unsigned int *tickets = reinterpret_cast<unsigned int *>(scratch + (size_t)64 * N);
-    k_colsum<<<dim3(groups, R), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const __nv_bfloat162 *>(a), M, N, static_cast<__nv_bfloat16 *>(out), scratch, tickets);
+    cudaStream_t st       = static_cast<cudaStream_t>(stream);
+    if (wide)
+        k_colsum<8><<<dim3(groups, R), 256, 0, st>>>(static_cast<const __nv_bfloat16 *>(a), M, N,
+                                                      static_cast<__nv_bfloat16 *>(out), scratch, tickets);
+    else
+        k_colsum<2><<<dim3(groups, R), 256, 0, st>>>(static_cast<const __nv_bfloat16 *>(a), M, N,
+                                                      static_cast<__nv_bfloat16 *>(out), scratch, tickets);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) set_last_error("colsum launch: %s", cudaGetErrorString(e));
     return (int)e;
