@@ -348,6 +348,7 @@ __global__ void __launch_bounds__(256)
         __threadfence();
         for (int c = threadIdx.x; c < 32 * V; c += 256) {
             float s = 0.f;
+#pragma unroll 8  // independent loads in flight: the chain of R L2 round trips was the kernel's critical path
             for (int y = 0; y < R; ++y) s += __ldcg(partial + (size_t)y * N + blockIdx.x * 32 * V + c);
             out[blockIdx.x * 32 * V + c] = __float2bfloat16(s);
         }
