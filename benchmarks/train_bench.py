@@ -42,7 +42,8 @@ ap.add_argument('--pad-vocab', type=int, default=1, help='BERT: round the vocabu
 ap.add_argument('--mlm-positions', type=int, default=0,
                 help='BERT: masked positions per sequence fed as masked_lm_positions (original BERT uses 20 at seq 128); '
                      '0 = MLM head on every position with -100 labels')
-ap.add_argument('--graph', action='store_true', help='capture the step in a CUDA graph (not for pair averaging)')
+ap.add_argument('--graph', action='store_true', help='capture the step in a CUDA graph (pair averaging: needs --pair-device-select 1)')
+ap.add_argument('--pair-device-select', type=int, default=0, help='pair averaging: the kernel draws its peer on the device (graph-capturable)')
 ap.add_argument('--momentum', type=float, default=0.9)
 args = ap.parse_args()
 
@@ -99,6 +100,8 @@ opt = {
     'ada': lambda: O.AdaptiveSGDOptimizer(base, named, change_step=args.warmup + args.steps // 2),
     'none': lambda: base,
 }[args.optimizer]()
+if args.optimizer == 'pair':
+    opt.device_select = bool(args.pair_device_select)
 if hasattr(opt, 'arenas'):
     opt.arenas()
 kf.broadcast_parameters(model.state_dict())
@@ -112,7 +115,7 @@ def step():
     return loss
 
 
-if args.graph and args.optimizer != 'pair':
+if args.graph and (args.optimizer != 'pair' or args.pair_device_select):
     # warm up on a side stream: autograd must not tie the capture to the legacy stream
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
@@ -125,7 +128,7 @@ else:
         loss = step()
 torch.cuda.synchronize()
 run = step
-if args.graph and args.optimizer != 'pair':
+if args.graph and (args.optimizer != 'pair' or args.pair_device_select):
     g = torch.cuda.CUDAGraph()
     kf.run_barrier()
     with torch.cuda.graph(g):

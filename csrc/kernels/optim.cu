@@ -526,6 +526,14 @@ struct PairArgs {
     SgdH h;
     int32_t *torn_out;
     int has_peer;
+    // Device-side peer selection (sel_np > 1): the target of this step is drawn in the kernel from
+    // (seed, *sel_step, rank), so nothing in the launch depends on the host's choice and the whole
+    // training step can live in one CUDA graph. The caller advances *sel_step once per step.
+    int sel_np, sel_rank;
+    const long long *sel_step;
+    unsigned long long sel_seed;
+    uint32_t *seq_all[KFB_MAX_RANKS];
+    const void *snap_all[KFB_MAX_RANKS];
 };
 
 template <typename G, typename P>
@@ -533,14 +541,32 @@ __global__ void __launch_bounds__(512)
     k_pair_avg(const __grid_constant__ PairArgs a)
 {
     __shared__ uint32_t s_k, s_self;
+    __shared__ uint32_t *s_seq_peer;
+    __shared__ const void *s_snap_peer;
     if (threadIdx.x == 0) {
-        s_k    = a.has_peer ? ld_acquire_sys(a.seq_peer) : 0u;
-        s_self = ld_relaxed_sys(a.seq_self);
+        uint32_t *seq_peer    = a.seq_peer;
+        const void *snap_peer = a.snap_peer;
+        if (a.sel_np > 1) {
+            // splitmix64 of (seed, step, rank): uniform over the OTHER np-1 ranks (the reference draws
+            // U[0, np) and bumps a self-hit to the next rank, async_sgd.py:71-75)
+            unsigned long long z =
+                a.sel_seed + 0x9E3779B97F4A7C15ull * ((unsigned long long)*a.sel_step * KFB_MAX_RANKS + a.sel_rank + 1);
+            z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+            z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+            z ^= z >> 31;
+            const int target = (a.sel_rank + 1 + (int)(z % (unsigned long long)(a.sel_np - 1))) % a.sel_np;
+            seq_peer         = a.seq_all[target];
+            snap_peer        = a.snap_all[target];
+        }
+        s_seq_peer  = seq_peer;
+        s_snap_peer = snap_peer;
+        s_k         = a.has_peer ? ld_acquire_sys(seq_peer) : 0u;
+        s_self      = ld_relaxed_sys(a.seq_self);
     }
     __syncthreads();
     const uint32_t k = s_k, kself = s_self;
     const char *peer =
-        reinterpret_cast<const char *>(a.snap_peer) + (k & 1) * a.slot_bytes;
+        reinterpret_cast<const char *>(s_snap_peer) + (k & 1) * a.slot_bytes;
     char *mine =
         reinterpret_cast<char *>(a.snap_self) + ((kself + 1) & 1) * a.slot_bytes;
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -578,7 +604,7 @@ __global__ void __launch_bounds__(512)
             __threadfence_system();
             st_release_sys(a.seq_self, kself + 1);
             if (a.has_peer && a.torn_out && k != 0) {
-                const uint32_t k2 = ld_acquire_sys(a.seq_peer);
+                const uint32_t k2 = ld_acquire_sys(s_seq_peer);
                 if (k2 - k >= 2u) atomicAdd(a.torn_out, 1);
             }
         }
@@ -1084,6 +1110,54 @@ extern "C" int kfb_pair_avg_step(const kfb_comm *comm, int target,
     a.grad_scale = grad_scale;
     a.h          = to_h(h);
     a.torn_out   = torn_out;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(grad_dtype, G,
+        KFB_DISPATCH_FLOAT(param_dtype, P,
+            (k_pair_avg<G, P><<<blocks, threads, 0, s>>>(a))));
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+// Same step with the peer chosen on the device: snaps[r] is rank r's snapshot buffer as mapped here.
+extern "C" int kfb_pair_avg_step_dev(const kfb_comm *comm, void *const *snaps, int64_t slot_bytes,
+                                     void *param, int param_dtype, const void *grad, int grad_dtype,
+                                     float *master, float *mom, int64_t count, float grad_scale,
+                                     const kfb_sgd_hyper *h, int32_t *torn_out, const long long *step,
+                                     unsigned long long seed, int blocks, int threads, void *stream)
+{
+    if (!comm || comm->rank < 0 || comm->rank >= comm->np || comm->np > KFB_MAX_RANKS) {
+        set_last_error("pair averaging needs a real rank");
+        return KFB_ERR_ARG;
+    }
+    if (count % 8 || blocks < 1 || blocks > KFB_MAX_BLOCKS || !snaps || !step) {
+        set_last_error("bad count/blocks/snaps/step");
+        return KFB_ERR_ARG;
+    }
+    PairArgs a;
+    memset(&a, 0, sizeof(a));
+    a.has_peer = comm->np > 1;
+    a.seq_self = reinterpret_cast<uint32_t *>(comm->pads[comm->rank]) + KFB_PAD_MISC_WORD;
+    a.seq_peer = a.seq_self;
+    a.snap_peer  = snaps[comm->rank];
+    a.snap_self  = snaps[comm->rank];
+    a.slot_bytes = slot_bytes;
+    a.param      = param;
+    a.grad       = grad;
+    a.master     = master;
+    a.mom        = mom;
+    a.scratch    = reinterpret_cast<float *>(comm->scratch);
+    a.npk        = count / 8;
+    a.grad_scale = grad_scale;
+    a.h          = to_h(h);
+    a.torn_out   = torn_out;
+    a.sel_np     = comm->np;
+    a.sel_rank   = comm->rank;
+    a.sel_step   = step;
+    a.sel_seed   = seed;
+    for (int r = 0; r < comm->np; ++r) {
+        a.seq_all[r]  = reinterpret_cast<uint32_t *>(comm->pads[r]) + KFB_PAD_MISC_WORD;
+        a.snap_all[r] = snaps[r];
+    }
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     KFB_DISPATCH_FLOAT(grad_dtype, G,
         KFB_DISPATCH_FLOAT(param_dtype, P,

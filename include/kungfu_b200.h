@@ -230,6 +230,18 @@ int kfb_pair_avg_step(const kfb_comm *comm, int target, const void *snap_peer,
                       float grad_scale, const kfb_sgd_hyper *h,
                       int32_t *torn_out, int blocks, int threads,
                       void *stream);
+/* The same step with the target drawn ON THE DEVICE from (seed, *step, rank),
+ * uniformly over the other ranks: no launch argument depends on the host's
+ * choice, so the whole training step can be captured in one CUDA graph.
+ * snaps[r] = rank r's snapshot area as mapped in this process (np entries);
+ * `step` is a device scalar the caller advances once per step. */
+int kfb_pair_avg_step_dev(const kfb_comm *comm, void *const *snaps,
+                          int64_t slot_bytes, void *param, int param_dtype,
+                          const void *grad, int grad_dtype, float *master,
+                          float *mom, int64_t count, float grad_scale,
+                          const kfb_sgd_hyper *h, int32_t *torn_out,
+                          const long long *step, unsigned long long seed,
+                          int blocks, int threads, void *stream);
 /* Publish the current parameters as snapshot version (seq+1) (init_store). */
 int kfb_pair_publish(const kfb_comm *comm, const void *param, void *snap_self,
                      int64_t slot_bytes, int64_t bytes, int blocks,

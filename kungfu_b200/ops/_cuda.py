@@ -90,6 +90,7 @@ _SIGS = {
     'kfb_ssgd_fused_step_nvls': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_sgd_flat': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_void_p]),
     'kfb_sma_fused_step': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_void_p]),
+    'kfb_pair_avg_step_dev': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_void_p, C.c_ulonglong, C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_avg_step': (C.c_int, [C.POINTER(KfbComm), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_publish': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
     'kfb_grad_variance': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),

@@ -58,8 +58,9 @@ class _PairAveraging(object):
         if not self._kf_started:
             self._fused_init()
             self._kf_started = True
-        target = self._pick()
         me = max(comm.rank, 0)
+        device_select = getattr(self, 'device_select', False) and comm.np > 1
+        target = -1 if device_select else self._pick()
         # one peer pull (NVLink) + a full-model local update (HBM): no CTA-indexed barrier in this kernel, so
         # it takes as many CTAs as the launch check allows instead of the NVLink-sized comm default
         blocks = self._blocks or max(comm.default_blocks, K.MAX_BLOCKS)
@@ -69,6 +70,18 @@ class _PairAveraging(object):
             for a in arenas:
                 a.fuse_grads()
                 snap = self._kf_snap[id(a)]
+                if device_select:
+                    # the kernel draws its own peer from (seed, step counter, rank): nothing in this launch
+                    # depends on a host-side choice, so the step can be captured in a CUDA graph
+                    if getattr(self, '_kf_step_t', None) is None:
+                        self._kf_step_t = torch.zeros(1, dtype=torch.int64, device=comm.device)
+                    sa, _keep = K.ptr_array(snap.ptrs)
+                    K.call('kfb_pair_avg_step_dev', comm.cstruct, sa, a.nbytes, a.params_buf.ptrs[me], a.code,
+                           a.grads_buf.ptrs[me], a.code, a.master.data_ptr(), a.mom.data_ptr(), a.count, 1.0,
+                           C.byref(h), self.torn_reads.data_ptr(), self._kf_step_t.data_ptr(),
+                           int(self._kf_seed) & 0xFFFFFFFFFFFFFFFF, blocks, threads, K.stream_ptr())
+                    self._kf_step_t.add_(1)
+                    continue
                 K.call('kfb_pair_avg_step', comm.cstruct, target,
                        snap.ptrs[target] if target >= 0 else snap.ptrs[me], snap.ptrs[me], a.nbytes,
                        a.params_buf.ptrs[me], a.code, a.grads_buf.ptrs[me], a.code,

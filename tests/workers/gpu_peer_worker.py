@@ -179,6 +179,48 @@ def check_fused_optimizers():
     kf.run_barrier()
     if rank == 0:
         print('SMA / PairAveraging ok; torn reads', int(opt.torn_reads), flush=True)
+    # PairAveraging with the peer drawn ON THE DEVICE: the whole step (forward, backward, pull + blend +
+    # update + publish) is one CUDA graph; lr = 0 makes it pure gossip averaging, so replicas must contract
+    if np_ > 1:
+        m = make()
+        for p in m.parameters():
+            p.data += 0.1 * rank
+        opt = kf.optimizers.PairAveragingOptimizer(FusedSGD(m.parameters(), lr=0.0), m.named_parameters())
+        opt.device_select = True
+        opt.arenas()
+        first = next(m.parameters())
+        w0 = kf.ops.all_gather(first.data.clone())
+        x, y = batch(rank, 0)
+
+        def pair_step():
+            opt.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                pair_step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        kf.run_barrier()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            pair_step()
+        for _ in range(8):
+            graph.replay()
+        torch.cuda.synchronize()
+        kf.run_barrier()
+        assert int(opt._kf_step_t) == 3 + 8, int(opt._kf_step_t)
+        w1 = kf.ops.all_gather(first.data.clone())
+        spread0 = float((w0.max(0).values - w0.min(0).values).max())
+        spread1 = float((w1.max(0).values - w1.min(0).values).max())
+        assert all(torch.isfinite(p).all() for p in m.parameters())
+        assert spread1 < 0.25 * spread0, (spread0, spread1)
+        if rank == 0:
+            print('PairAveraging device-selected peer under a CUDA graph ok: spread %.4f -> %.4f' % (spread0, spread1),
+                  flush=True)
     # monitors
     m = make()
     opt = kf.optimizers.MonitorGradientNoiseScaleOptimizer(FusedSGD(m.parameters(), lr=0.05), m.named_parameters(), device_batch_size=32)
