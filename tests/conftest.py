@@ -29,7 +29,7 @@ def run_workers(np_, script, args=(), strategy='AUTO', timeout=120, extra_flags=
     """Launch `script` on np_ loopback workers with our own kungfu-run; returns CompletedProcess."""
     import subprocess
     exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
-    port_base = 20000 + (os.getpid() * 37) % 20000
+    port_base = 20000 + (os.getpid() * 37) % 12000  # stay below the ephemeral range (32768+)
     cmd = [exe, '-q', '-np', str(np_), '-H', '127.0.0.1:%d' % max(np_, 8), '-strategy', strategy,
            '-port-range', '%d-%d' % (port_base, port_base + 64), '-port', str(port_base + 100),
            '-timeout', '%ds' % timeout] + list(extra_flags) + [sys.executable, script] + list(args)

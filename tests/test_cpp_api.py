@@ -21,7 +21,7 @@ def fake_agent(tmp_path_factory):
                                           (4, 'MULTI_BINARY_TREE_STAR'), (3, 'TREE')])
 def test_fake_agent(fake_agent, np_, strategy):
     exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
-    base = 21000 + (os.getpid() * 53) % 15000
+    base = 21000 + (os.getpid() * 53) % 11000
     res = subprocess.run([exe, '-q', '-np', str(np_), '-strategy', strategy, '-timeout', '60s', '-port-range',
                           '%d-%d' % (base, base + 32), '-port', str(base + 40), fake_agent],
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=90)
@@ -46,7 +46,7 @@ def test_cpp_utils_header(tmp_path):
 def test_native_bench_tools(tool, args, np_):
     """Host data-plane micro-benchmarks (reference: tests/go/cmd/kungfu-bench-allreduce, kungfu-bench-p2p)."""
     bindir = os.path.join(ROOT, 'kungfu_b200', 'bin')
-    base = 21000 + (os.getpid() * 59 + len(args) * 101) % 15000
+    base = 21000 + (os.getpid() * 59 + len(args) * 101) % 11000
     res = subprocess.run([os.path.join(bindir, 'kungfu-run'), '-q', '-np', str(np_), '-timeout', '60s', '-port-range',
                           '%d-%d' % (base, base + 32), '-port', str(base + 40), os.path.join(bindir, tool)] + args,
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
@@ -62,7 +62,7 @@ def test_fake_adaptive_trainer(tmp_path):
                            os.path.join(ROOT, 'tests', 'cpp', 'fake_adaptive_trainer.cpp'), '-o', out,
                            '-L', lib, '-lkungfu_host', '-Wl,-rpath,' + lib])
     exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
-    base = 21000 + (os.getpid() * 71) % 15000
+    base = 21000 + (os.getpid() * 71) % 11000
     res = subprocess.run([exe, '-q', '-w', '-np', '1', '-H', '127.0.0.1:4', '-timeout', '90s', '-port-range',
                           '%d-%d' % (base, base + 32), '-port', str(base + 40), out, '3:1,3:3,3:4,3:2', '50000'],
                          stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)

@@ -9,7 +9,7 @@ RUN = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
 
 
 def _base(salt):
-    return 21000 + (os.getpid() * 67 + salt * 991) % 15000
+    return 21000 + (os.getpid() * 67 + salt * 991) % 11000
 
 
 def test_rl_policy_gradient_two_workers(tmp_path):

@@ -12,7 +12,7 @@ from conftest import ROOT
 @pytest.mark.parametrize('strategy', ['BINARY_TREE_STAR', 'TREE', 'MULTI_STAR', 'MULTI_BINARY_TREE_STAR', 'RING', 'AUTO'])
 def test_three_hosts_on_loopback(strategy):
     exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
-    base = 22000 + (os.getpid() * 31) % 12000
+    base = 22000 + (os.getpid() * 31) % 10000
     hosts = '127.0.0.1:2,127.0.0.2:2,127.0.0.3:1'
     env = dict(os.environ, PYTHONPATH=ROOT)
     procs = []

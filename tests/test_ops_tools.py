@@ -14,7 +14,7 @@ BIN = os.path.join(ROOT, 'kungfu_b200', 'bin')
 
 
 def _base(salt):
-    return 21000 + (os.getpid() * 61 + salt * 977) % 15000
+    return 21000 + (os.getpid() * 61 + salt * 977) % 11000
 
 
 def _get(url):
