@@ -89,3 +89,6 @@ class ElasticShardedDataset(object):
         idx = [(self.offset + self.rank * local + i) % n for i in range(local)]
         self.offset += self.global_batch_size
         return self.xs[idx], self.ys[idx]
+
+
+from .vision import (ImageFolder, gpu_augment, load_cifar10, npz_to_idx_tar, random_input)  # noqa: E402,F401
