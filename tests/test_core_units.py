@@ -202,3 +202,23 @@ def test_python_utils_helpers():
     with utils.StallDetector('slow op', period=0.05, out=buf) as sd:
         time.sleep(0.2)
     assert sd.reports >= 2 and 'slow op stalled for' in buf.getvalue()
+
+
+def test_experiment_matrix_dry_run_and_noise_scale_scraper(tmp_path):
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, 'benchmarks', 'experiments.py'), '--models', 'resnet50,vgg16',
+                          '--optimizers', 'ssgd,pair', '--np', '1,4', '--batch-sizes', '64', '--graph', '--dry-run'],
+                         stdout=subprocess.PIPE, text=True, check=True).stdout.strip().splitlines()
+    assert len(out) == 8
+    assert sum('--graph' in line for line in out) == 4  # never for pair averaging
+    assert all('kungfu-run' in line and 'train_bench.py' in line for line in out)
+    log = tmp_path / 'run.log'
+    log.write_text('step 10 np 2 loss 2.1 noise scale 120.5\nnoise\nstep 20 np 2 noise_scale=340.1\nstep 30 noise scale: 1e3\n')
+    csv = tmp_path / 'gns.csv'
+    res = subprocess.run([sys.executable, os.path.join(root, 'benchmarks', 'monitoring', 'noise_scale_from_log.py'), str(log),
+                          '--csv', str(csv)], stdout=subprocess.PIPE, text=True, check=True).stdout
+    assert '3 readings' in res
+    assert csv.read_text().splitlines() == ['step,noise_scale', '10,120.5', '20,340.1', '30,1000']
