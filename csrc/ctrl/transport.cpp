@@ -281,6 +281,48 @@ std::string NetMonitor::metrics_text() const
 // ---- mailbox ----------------------------------------------------------------------------
 std::string Mailbox::key(const PeerID &src, const std::string &name) { return src.str() + "/" + name; }
 
+size_t BodyPool::size_class(size_t n)
+{
+    size_t c = kMinClass;
+    while (c < n) c <<= 1;
+    return c;
+}
+
+BodyPool &BodyPool::instance()
+{
+    static BodyPool pool;
+    return pool;
+}
+
+Body BodyPool::acquire(size_t len)
+{
+    Body b;
+    b.len = len;
+    if (len == 0) return b;
+    b.cap = size_class(len);
+    if (b.cap <= kMaxPooled) {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto it = free_.find(b.cap);
+        if (it != free_.end() && !it->second.empty()) {
+            b.data = std::move(it->second.back());
+            it->second.pop_back();
+            ++hits_;
+            return b;
+        }
+        ++misses_;
+    }
+    b.data.reset(new uint8_t[b.cap]);  // not value-initialised: the socket read fills it
+    return b;
+}
+
+void BodyPool::release(Body &&b)
+{
+    if (!b.data || b.cap > kMaxPooled) return;
+    std::lock_guard<std::mutex> lk(mu_);
+    auto &v = free_[b.cap];
+    if (v.size() < kKeepPerClass) v.push_back(std::move(b.data));
+}
+
 bool Mailbox::deliver(const PeerID &src, const std::string &name, int fd, uint64_t len)
 {
     const std::string k = key(src, name);
@@ -304,8 +346,11 @@ bool Mailbox::deliver(const PeerID &src, const std::string &name, int fd, uint64
         cv_.notify_all();
         return ok;
     }
-    std::vector<uint8_t> body(len);
-    if (len && !read_full(fd, body.data(), len)) return false;
+    Body body = BodyPool::instance().acquire(len);
+    if (len && !read_full(fd, body.data.get(), len)) {
+        BodyPool::instance().release(std::move(body));
+        return false;
+    }
     std::unique_lock<std::mutex> lk(mu_);
     boxes_[k].ready.push_back(std::move(body));
     cv_.notify_all();
@@ -325,12 +370,13 @@ long Mailbox::recv_into(const PeerID &src, const std::string &name, void *buf, s
         if (w.done) return (long)w.got;
         if (!w.busy && !b.ready.empty()) {
             if (b.waiter == &w) b.waiter = nullptr;
-            std::vector<uint8_t> body = std::move(b.ready.front());
+            Body body = std::move(b.ready.front());
             b.ready.pop_front();
-            const size_t n = std::min(cap, body.size());
+            const size_t n = std::min(cap, body.len), total = body.len;
             lk.unlock();
-            if (n) memcpy(buf, body.data(), n);
-            return (long)body.size();
+            if (n) memcpy(buf, body.data.get(), n);
+            BodyPool::instance().release(std::move(body));
+            return (long)total;
         }
         if (closed_) {
             if (b.waiter == &w && !w.busy) b.waiter = nullptr;

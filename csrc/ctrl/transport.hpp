@@ -87,6 +87,31 @@ class NetMonitor
 };
 
 // ---- rendezvous of named messages ----------------------------------------------------------
+// Message bodies that arrive before their receiver is parked are held in pooled buffers:
+// power-of-two size classes from 512 B, a few buffers kept per class, so the steady stream of
+// 1 MiB chunks of a graph walk does not malloc / zero-fill / free once per message.
+// Parity: /root/reference/srcs/go/rchannel/connection/byte_slice_pool.go:7-60 (size-keyed sync.Pool).
+struct Body {
+    std::unique_ptr<uint8_t[]> data;
+    size_t cap = 0, len = 0;
+};
+
+class BodyPool
+{
+    static constexpr size_t kMinClass = 512, kKeepPerClass = 8, kMaxPooled = size_t(64) << 20;
+    std::mutex mu_;
+    std::map<size_t, std::vector<std::unique_ptr<uint8_t[]>>> free_;
+    uint64_t hits_ = 0, misses_ = 0;
+    static size_t size_class(size_t n);
+
+  public:
+    Body acquire(size_t len);
+    void release(Body &&b);
+    uint64_t hits() const { return hits_; }
+    uint64_t misses() const { return misses_; }
+    static BodyPool &instance();
+};
+
 class Mailbox
 {
     struct Waiter {
@@ -97,7 +122,7 @@ class Mailbox
         size_t got = 0;
     };
     struct Box {
-        std::deque<std::vector<uint8_t>> ready;
+        std::deque<Body> ready;
         Waiter *waiter = nullptr;
     };
     std::mutex mu_;
