@@ -6,8 +6,10 @@ import torch
 def test_torchvision_parity():
     torchvision = pytest.importorskip('torchvision')
     from kungfu_b200 import models
-    for name in ('resnet50', 'densenet121', 'vgg16'):
-        ours, theirs = getattr(models, name)(), getattr(torchvision.models, name)()
+    for name in ('resnet50', 'densenet121', 'vgg16', 'inception_v3'):
+        kw = dict(aux_logits=True, init_weights=False) if name == 'inception_v3' else {}
+        ours = getattr(models, name)(**({'aux_logits': True} if name == 'inception_v3' else {}))
+        theirs = getattr(torchvision.models, name)(**kw)
         assert set(ours.state_dict().keys()) == set(theirs.state_dict().keys()), name
         theirs.load_state_dict(ours.state_dict())  # checkpoints interchange
         assert sum(p.numel() for p in ours.parameters()) == sum(p.numel() for p in theirs.parameters())
@@ -56,3 +58,14 @@ def test_bert_masked_positions_give_the_same_loss():
     a = m(ids, mlm_labels=lab_full, nsp_labels=nsp)
     b = m(ids, mlm_labels=lab_p, nsp_labels=nsp, mlm_positions=pos)
     assert abs(float(a) - float(b)) < 1e-5
+
+
+def test_inception_v3_shapes_and_size():
+    """The third model of the reference's published plots: 23.8 M parameters (27.2 M with the auxiliary head)."""
+    from kungfu_b200 import models
+    m = models.inception_v3()
+    assert sum(p.numel() for p in m.parameters()) == 23834568
+    assert sum(p.numel() for p in models.inception_v3(aux_logits=True).parameters()) == 27161264
+    m.eval()
+    with torch.no_grad():
+        assert m(torch.randn(1, 3, 299, 299)).shape == (1, 1000)
