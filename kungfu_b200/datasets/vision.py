@@ -6,7 +6,6 @@ distortion, resize) and idx.py:83 (npz -> tar of idx files). There is no TensorF
 B200 has cycles to spare next to a 148-SM training step, so the augmentation runs ON THE GPU on
 whole uint8 batches: the host only reads bytes and issues one pinned H2D copy per batch.
 """
-import io
 import os
 import pickle
 import tarfile

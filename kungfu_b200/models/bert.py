@@ -6,8 +6,6 @@ The reference only knows BERT as a list of gradient sizes
 this is the architecture itself, bf16-friendly, attention through
 torch.nn.functional.scaled_dot_product_attention (library flash kernels: model
 math stays a library call, like in the reference)."""
-import math
-
 import torch
 import torch.nn as nn
 import torch.nn.functional as F

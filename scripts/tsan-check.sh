@@ -1,0 +1,25 @@
+#!/bin/sh
+# ThreadSanitizer pass over the host runtime: builds every C++ source of libkungfu_host together with
+# the C++ agent test (tests/cpp/fake_agent.cpp: all collectives, async ops with callbacks, p2p store,
+# consensus, AllGatherTransform) with -fsanitize=thread and runs it as a 2- and a 3-worker job.
+# The reference has no sanitizer run at all. Exit code != 0 on any TSAN report.
+set -e
+cd "$(dirname "$0")/.."
+out=${TMPDIR:-/tmp}/kungfu-tsan
+mkdir -p "$out"
+srcs=$(ls csrc/core/*.cpp csrc/ctrl/*.cpp csrc/elastic/*.cpp csrc/capi/*.cpp)
+g++ -O1 -g -std=c++17 -fsanitize=thread -fPIE -pie -pthread -mavx2 -mf16c -Icsrc -Iinclude \
+    $srcs tests/cpp/fake_agent.cpp -o "$out/fake-agent-tsan" -ldl
+status=0
+for cfg in "2 STAR" "3 BINARY_TREE_STAR" "3 RING"; do
+    set -- $cfg
+    base=$((24000 + $$ % 4000))
+    log="$out/tsan-np$1-$2.log"
+    TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" timeout 300 kungfu_b200/bin/kungfu-run -q -np "$1" -strategy "$2" \
+        -timeout 250s -port-range "$base-$((base + 16))" -port "$((base + 20))" "$out/fake-agent-tsan" >"$log" 2>&1 || status=1
+    reports=$(grep -c "WARNING: ThreadSanitizer" "$log" || true)
+    ok=$(grep -c "OK fake-agent" "$log" || true)
+    echo "np=$1 strategy=$2: $ok/$1 workers ok, $reports TSAN reports ($log)"
+    [ "$reports" = "0" ] && [ "$ok" = "$1" ] || status=1
+done
+exit $status

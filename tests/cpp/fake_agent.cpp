@@ -8,6 +8,7 @@
 #include <vector>
 
 #include <kungfu/peer.hpp>
+#include <kungfu/utils.hpp>
 
 #define CHECK(cond)                                                            \
     do {                                                                       \
@@ -43,9 +44,9 @@ int main()
     // async AllReduce with callback
     {
         std::vector<float> x(1000, 1.0f), y(1000, 0.0f);
-        volatile bool done = false;
-        peer.AllReduce(x.data(), y.data(), 1000, kungfu::F32, kungfu::SUM, "async", [&] { done = true; });
-        while (!done) std::this_thread::yield();
+        kungfu::Latch done;  // a real happens-before edge from the callback to this thread (TSAN-clean)
+        peer.AllReduce(x.data(), y.data(), 1000, kungfu::F32, kungfu::SUM, "async", [&] { done.done(); });
+        done.wait();
         CHECK(y[999] == (float)np);
     }
     // Gather / AllGather
