@@ -22,4 +22,16 @@ for cfg in "2 STAR" "3 BINARY_TREE_STAR" "3 RING"; do
     echo "np=$1 strategy=$2: $ok/$1 workers ok, $reports TSAN reports ($log)"
     [ "$reports" = "0" ] && [ "$ok" = "$1" ] || status=1
 done
+# AddressSanitizer + UndefinedBehaviorSanitizer + leak check over the same program
+g++ -O1 -g -std=c++17 -fsanitize=address,undefined -fno-omit-frame-pointer -pthread -mavx2 -mf16c -Icsrc -Iinclude \
+    $srcs tests/cpp/fake_agent.cpp -o "$out/fake-agent-asan" -ldl
+base=$((28000 + $$ % 2000))
+log="$out/asan-np3.log"
+ASAN_OPTIONS="detect_leaks=1:halt_on_error=0" UBSAN_OPTIONS="print_stacktrace=1" timeout 300 kungfu_b200/bin/kungfu-run -q -np 3 \
+    -strategy MULTI_BINARY_TREE_STAR -timeout 250s -port-range "$base-$((base + 16))" -port "$((base + 20))" \
+    "$out/fake-agent-asan" >"$log" 2>&1 || status=1
+reports=$(grep -c -E "ERROR: AddressSanitizer|runtime error|LeakSanitizer" "$log" || true)
+ok=$(grep -c "OK fake-agent" "$log" || true)
+echo "asan+ubsan np=3: $ok/3 workers ok, $reports reports ($log)"
+[ "$reports" = "0" ] && [ "$ok" = "3" ] || status=1
 exit $status
