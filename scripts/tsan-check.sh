@@ -22,6 +22,25 @@ for cfg in "2 STAR" "3 BINARY_TREE_STAR" "3 RING"; do
     echo "np=$1 strategy=$2: $ok/$1 workers ok, $reports TSAN reports ($log)"
     [ "$reports" = "0" ] && [ "$ok" = "$1" ] || status=1
 done
+# elastic paths: an instrumented trainer that resizes 1 -> 3 -> 4 -> 2 under a normal watch-mode runner, then
+# a normal trainer under an instrumented runner
+g++ -O1 -g -std=c++17 -fsanitize=thread -fPIE -pie -pthread -mavx2 -mf16c -Icsrc -Iinclude \
+    $srcs tests/cpp/fake_adaptive_trainer.cpp -o "$out/adaptive-tsan" -ldl
+g++ -O1 -g -std=c++17 -fsanitize=thread -fPIE -pie -pthread -mavx2 -mf16c -Icsrc -Iinclude \
+    $srcs csrc/launch/kungfu_run_main.cpp -o "$out/kungfu-run-tsan" -ldl
+g++ -O1 -std=c++17 -pthread -Iinclude tests/cpp/fake_adaptive_trainer.cpp -o "$out/adaptive" \
+    -Lkungfu_b200/lib -lkungfu_host -Wl,-rpath,"$PWD/kungfu_b200/lib"
+for pair in "kungfu_b200/bin/kungfu-run $out/adaptive-tsan worker" "$out/kungfu-run-tsan $out/adaptive runner"; do
+    set -- $pair
+    base=$((26000 + $$ % 1500))
+    log="$out/tsan-elastic-$3.log"
+    TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" timeout 300 "$1" -q -w -np 1 -H 127.0.0.1:4 -timeout 250s \
+        -port-range "$base-$((base + 32))" -port "$((base + 40))" "$2" 3:1,3:3,3:4,3:2 20000 >"$log" 2>&1 || status=1
+    reports=$(grep -c "WARNING: ThreadSanitizer" "$log" || true)
+    ok=$(grep -c "OK fake-adaptive-trainer" "$log" || true)
+    echo "elastic 1->3->4->2, instrumented $3: $ok/2 survivors ok, $reports TSAN reports ($log)"
+    [ "$reports" = "0" ] && [ "$ok" = "2" ] || status=1
+done
 # AddressSanitizer + UndefinedBehaviorSanitizer + leak check over the same program
 g++ -O1 -g -std=c++17 -fsanitize=address,undefined -fno-omit-frame-pointer -pthread -mavx2 -mf16c -Icsrc -Iinclude \
     $srcs tests/cpp/fake_agent.cpp -o "$out/fake-agent-asan" -ldl
