@@ -56,6 +56,8 @@ is_bert = args.model.startswith('bert')
 B = args.batch_size
 
 if is_bert:
+    from kungfu_b200.ops.fused_ln import DropoutState
+    DropoutState.manual_seed(1234, rank)  # every worker draws its own dropout masks
     model = getattr(models, args.model)(fused_linear=bool(args.fused_linear), fused_ln=bool(args.fused_ln), fused_grads=bool(args.fused_grads),
                                        pad_vocab=args.pad_vocab).to(dev).to(torch.bfloat16)
     ids = torch.randint(0, 30522, (B, args.seq_len), device=dev)

@@ -24,8 +24,9 @@ class DropoutState(object):
     _steps = {}
 
     @classmethod
-    def manual_seed(cls, seed):
-        cls.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    def manual_seed(cls, seed, rank=0):
+        """Workers of one job should pass their rank: same seed + different rank = decorrelated masks."""
+        cls.seed = (int(seed) + 0x9E3779B97F4A7C15 * (int(rank) + 1)) & 0xFFFFFFFFFFFFFFFF
 
     @classmethod
     def step_tensor(cls, device):
