@@ -222,3 +222,36 @@ def test_experiment_matrix_dry_run_and_noise_scale_scraper(tmp_path):
                           '--csv', str(csv)], stdout=subprocess.PIPE, text=True, check=True).stdout
     assert '3 readings' in res
     assert csv.read_text().splitlines() == ['step,noise_scale', '10,120.5', '20,340.1', '30,1000']
+
+
+def test_cuda_entry_points_reject_bad_arguments_before_touching_the_device():
+    """Argument checks of the device C ABI run on the host: clear errors, no GPU needed."""
+    from kungfu_b200.ops import _cuda as K
+    lib = K.lib()
+    buf = (C.c_char * 4096)()
+    p = C.addressof(buf)
+    p16 = (p + 15) // 16 * 16
+    # linear: K and N must be multiples of 8; pointers 16-byte aligned; bias dtype f32/bf16
+    assert lib.kfb_linear_act(p16, p16, None, 0, p16, None, 8, 12, 16, 0, None) != 0
+    assert b'multiples of 8' in lib.kfb_last_error()
+    assert lib.kfb_linear_act(p16 + 2, p16, None, 0, p16, None, 8, 16, 16, 0, None) != 0
+    assert b'aligned' in lib.kfb_last_error()
+    assert lib.kfb_linear_act(p16, p16, p16, K.I32, p16, None, 8, 16, 16, 0, None) != 0
+    assert b'bias' in lib.kfb_last_error()
+    assert lib.kfb_linear_act(p16, p16, None, 0, p16, None, 0, 16, 16, 0, None) == 0  # empty problem: nothing to do
+    # activation backward: element count multiple of 8, known activation
+    assert lib.kfb_act_bwd(p16, p16, p16, 12, 1, None) != 0
+    assert lib.kfb_act_bwd(p16, p16, p16, 16, 7, None) != 0
+    # add & norm: hidden size and dropout range
+    assert lib.kfb_add_dropout_ln_fwd(p16, None, p16, p16, p16, None, None, None, 4, 100, 1e-5, 0.0, 1, None, 0, None) != 0
+    assert b'hidden size' in lib.kfb_last_error()
+    assert lib.kfb_add_dropout_ln_fwd(p16, None, p16, p16, p16, None, None, None, 4, 256, 1e-5, 1.5, 1, None, 0, None) != 0
+    assert b'dropout' in lib.kfb_last_error()
+    # column sum and qkv gather
+    assert lib.kfb_colsum(p16, 4, 100, p16, p16, None) != 0
+    assert b'multiple of 64' in lib.kfb_last_error()
+    strides = (C.c_longlong * 9)(*([64, 8, 8] * 3))
+    assert lib.kfb_pack_qkv_grad(p16, p16, p16, strides, 1, 1, 1, 12, p16, None) != 0
+    assert b'head dim' in lib.kfb_last_error()
+    assert lib.kfb_colsum_scratch_floats(768) >= 64 * 768
+    assert lib.kfb_ln_partial_floats(4096, 768) % (2 * 768) == 0
