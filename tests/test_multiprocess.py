@@ -58,3 +58,11 @@ def test_bad_worker_tears_down_job(tmp_path):
                       "time.sleep(60)\n")
     res = run_workers(3, str(script), timeout=40)
     assert res.returncode != 0
+
+
+@pytest.mark.parametrize('np_', [1, 3])
+def test_ssgd_on_a_quadratic_follows_the_closed_form(np_):
+    """x <- x - lr * mean_r(2x) = (1 - 2 lr) x on every worker, for any np, to 1e-6."""
+    res = run_workers(np_, os.path.join(W, 'quadratic_worker.py'))
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert res.stdout.count('OK quadratic') == np_
