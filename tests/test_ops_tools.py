@@ -139,3 +139,29 @@ def test_cluster_manager_example():
     assert res.returncode == 0, res.stdout[-3000:]
     assert 'runners exited with [0, 0]' in res.stdout
     assert res.stdout.count('finished 50 steps with np=3') == 3
+
+
+def test_random_resize_soak():
+    """A config client PUTs a cluster of random size (1..4) every 300 ms while the workers poll the config
+    server after every step (reference: the docker-compose cluster tests with kungfu-config-client-example)."""
+    base = _base(5)
+    cfg_port = base + 60
+    url = 'http://127.0.0.1:%d/config' % cfg_port
+    worker = [sys.executable, os.path.join(ROOT, 'examples', 'cluster_manager.py'), '--worker', '--max-step', '70']
+    run = subprocess.Popen([os.path.join(BIN, 'kungfu-run'), '-q', '-w', '-np', '2', '-H', '127.0.0.1:4', '-port',
+                            str(base + 40), '-port-range', '%d-%d' % (base, base + 16), '-builtin-config-port',
+                            str(cfg_port), '-config-server', url, '-timeout', '150s'] + worker,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        time.sleep(4)  # let the first workers import torch and start stepping
+        client = subprocess.run([os.path.join(BIN, 'kungfu-config-client'), '-server', url, '-H', '127.0.0.1:4', '-port',
+                                 str(base + 40), '-port-range', '%d-%d' % (base, base + 16), '-period', '300ms',
+                                 '-ttl', '5s'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+        assert client.stdout.count('-> 200') >= 5, client.stdout
+        log, _ = run.communicate(timeout=170)
+    finally:
+        if run.poll() is None:
+            run.kill()
+    assert run.returncode == 0, log[-3000:]
+    assert 'finished 70 steps' in log
+    assert 'now rank' in log or 'leaves at step' in log  # at least one membership change was observed
