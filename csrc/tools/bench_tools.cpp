@@ -4,6 +4,8 @@
 //
 //   kungfu-run -np 4 kungfu-bench-allreduce -model resnet50 -mode par -epochs 5
 //   kungfu-run -np 4 kungfu-bench-p2p -model vgg16 -epochs 3
+//   kungfu-run -np 4 kungfu-bench-allreduce -model resnet50 -fuse -batch 32     (fake trainer: Img/sec lines,
+//       /root/reference/tests/cpp/integration/fake_trainer.hpp:169-176)
 //
 // Metrics follow the reference's tools so numbers are comparable:
 //   all-reduce "rate" = 4 (np-1) bytes / time   (/root/reference/tests/go/cmd/kungfu-bench-allreduce/kungfu-bench-allreduce.go:74-75)
@@ -111,7 +113,7 @@ double now_s()
 
 struct Args {
     std::string model = "resnet50", mode = "par";
-    int epochs = 5, warmup = 2;
+    int epochs = 5, warmup = 2, batch = 0;
     bool fuse = false;
 };
 
@@ -131,6 +133,7 @@ bool parse_args(int argc, char **argv, Args *a)
         else if (f == "-epochs") a->epochs = atoi(val("-epochs"));
         else if (f == "-warmup") a->warmup = atoi(val("-warmup"));
         else if (f == "-fuse") a->fuse = true;
+        else if (f == "-batch") a->batch = atoi(val("-batch"));
         else return false;
     }
     return a->mode == "par" || a->mode == "seq";
@@ -176,6 +179,9 @@ int bench_allreduce(const Args &a, const Sizes &sizes_in)
                 fprintf(stderr, "wrong result in tensor %zu: %f (np=%d)\n", i, recv[i][0], np);
                 return 1;
             }
+        if (peer.Rank() == 0 && a.batch > 0 && ep >= a.warmup)
+            // fake-trainer view (no compute, communication only): one epoch = one training step of `batch` samples
+            printf("Img/sec %.1f per worker, %.1f per cluster (communication bound)\n", a.batch / dt, a.batch * np / dt);
         if (peer.Rank() == 0) {
             const double rate = 4.0 * (np - 1) * total * 4.0 / dt / (1 << 30);
             printf("%s epoch %d: %zu tensors, %.1f MiB, %.2f ms, rate %.3f GiB/s (4(np-1)bytes/t), algbw %.3f GiB/s\n",
@@ -224,7 +230,7 @@ int main(int argc, char **argv)
     Sizes sizes;
     if (!parse_args(argc, argv, &a) || !parse_model(a.model, &sizes)) {
         fprintf(stderr,
-                "usage: kungfu-run -np N %s [-model resnet50|vgg16|bert|<count>x<elems>] [-mode par|seq] [-fuse] "
+                "usage: kungfu-run -np N %s [-model resnet50|vgg16|bert|<count>x<elems>] [-mode par|seq] [-fuse] [-batch N] "
                 "[-epochs 5] [-warmup 2]\n",
                 argv[0]);
         return 2;
