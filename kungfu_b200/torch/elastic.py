@@ -96,3 +96,31 @@ class ElasticTrainHook(object):
         self.state.end_step(batch_size)
         want = step_based_schedule(self.schedule, self.state.step, default=kfpy.current_cluster_size(), strict=False)
         return self.state.resize(want) and not self.state.should_stop()
+
+
+# reference names (tensorflow/hooks/elastic.py:14, tensorflow/experimental/hook/elastic.py:50)
+KungFuElasticTrainHook = ElasticTrainHook
+
+
+class ElasticHook(object):
+    """``ElasticHook(local_batch_size, epochs, epoch_size)``: counts trained samples, stops after
+    ``epochs * epoch_size`` of them or when detached, re-syncs state after every membership change
+    (resizes themselves are requested elsewhere, e.g. ``kf.ops.resize`` or a config server)."""
+
+    def __init__(self, local_batch_size, epochs, epoch_size, model, optimizer=None):
+        self.local_batch_size = local_batch_size
+        self.total_samples = int(epochs * epoch_size)
+        self.state = ElasticState(model, optimizer)
+        self._np = kfpy.current_cluster_size()
+
+    def after_step(self):
+        """Returns False when this worker should stop."""
+        self.state.end_step(self.local_batch_size)
+        if kfpy.detached():
+            return False
+        if kfpy.current_cluster_size() != self._np:  # somebody resized the cluster since the last step
+            self.state.profiler.begin()
+            old, self._np = self._np, kfpy.current_cluster_size()
+            self.state.sync()
+            self.state.profiler.end(old, self._np)
+        return self.state.trained_samples < self.total_samples

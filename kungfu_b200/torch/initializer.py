@@ -35,3 +35,17 @@ class BroadcastGlobalVariablesCallback(object):
         if self.optimizer is not None:
             broadcast_optimizer_state(self.optimizer)
         self.done = True
+
+
+def BroadcastGlobalVariablesOp(model, optimizer=None):
+    """Reference name (initializer/__init__.py:30): broadcast everything now. Returns None (eager)."""
+    broadcast_parameters(model.state_dict())
+    if optimizer is not None:
+        broadcast_optimizer_state(optimizer)
+
+
+class BroadcastGlobalVariablesHook(BroadcastGlobalVariablesCallback):
+    """Reference name for the session hook flavour: ``after_create_session()`` broadcasts once."""
+
+    def after_create_session(self, *_):
+        self.on_batch_end()

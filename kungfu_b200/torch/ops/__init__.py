@@ -32,3 +32,20 @@ def defuse(flat, shapes):
         out.append(flat[off:off + n].view(s))
         off += n
     return out
+
+
+# ---- names of the reference's TensorFlow op wrappers (srcs/python/kungfu/tensorflow/ops/collective.py:8-133) ----
+def all_reduce(t, op='sum', name=None):
+    """``kungfu.tensorflow.ops.all_reduce``: returns the reduced tensor."""
+    return all_reduce_fn(t, op, name=name)
+
+
+def group_nccl_all_reduce(tensors, op='sum'):
+    """The reference's NCCL group all-reduce; CUDA tensors here take the peer-memory / NVLS kernels."""
+    return group_all_reduce(tensors, op)
+
+
+def group_hierarchical_nccl_all_reduce(tensors, op='sum'):
+    """Local reduce -> cross-host all-reduce -> local broadcast in the reference; the device communicator
+    does exactly that by itself when a job spans hosts (kungfu_b200.ops.collective.hier_all_reduce)."""
+    return group_all_reduce(tensors, op)

@@ -119,3 +119,7 @@ class NoiseScaleElasticPolicy(BasePolicy):
             V.set_value(V.GraphKeys.GRADIENT_NOISE_SCALE, float(ns) if ns is not None else None)
             self._last_resize = state.step
             state.resize(min(self.max_size, np_ * 2))
+
+
+# reference name (tensorflow/policy/policy_hook.py:8): the Estimator hook that drives the policies
+PolicyHook = PolicyRunner

@@ -183,3 +183,33 @@ def test_monitoring_endpoint():
     res = run_workers(2, script, env={'KUNGFU_CONFIG_ENABLE_MONITORING': 'true', 'KUNGFU_CONFIG_MONITORING_PERIOD': '30s'})
     assert res.returncode == 0, res.stdout[-3000:]
     assert res.stdout.count('OK monitor') == 2
+
+
+def test_reference_tensorflow_layout_resolves_to_the_torch_front_end():
+    """`kungfu.tensorflow.*` keeps the reference's module layout and names (backed by the torch objects)."""
+    import torch
+
+    import kungfu
+    from kungfu.tensorflow.experimental.hook import ElasticHook, ResizeProfiler  # noqa: F401
+    from kungfu.tensorflow.hooks import KungFuElasticTrainHook  # noqa: F401
+    from kungfu.tensorflow.initializer import (BroadcastGlobalVariablesCallback, BroadcastGlobalVariablesHook,  # noqa: F401
+                                               BroadcastGlobalVariablesOp, broadcast_variables)
+    from kungfu.tensorflow.ops import (all_reduce, barrier, broadcast, group_all_reduce,  # noqa: F401
+                                       group_hierarchical_nccl_all_reduce, group_nccl_all_reduce, resize)
+    from kungfu.tensorflow.optimizers import (AdaptiveSGDOptimizer, MonitorGradientNoiseScaleOptimizer,  # noqa: F401
+                                              MonitorGradientVarianceOptimizer, PairAveragingOptimizer,
+                                              SynchronousAveragingOptimizer, SynchronousSGDOptimizer)
+    from kungfu.tensorflow.policy import BasePolicy, PolicyHook  # noqa: F401
+    from kungfu.tensorflow.v1.helpers import load_cifar10, load_mnist  # noqa: F401
+    from kungfu.tensorflow.variables import GraphKeys, get_or_create_batch_size  # noqa: F401
+    assert kungfu.tensorflow.optimizers is kungfu.torch.optimizers
+    assert torch.equal(all_reduce(torch.ones(3)), torch.ones(3))
+    got = group_nccl_all_reduce([torch.ones(2), None, torch.full((1, ), 3.0)])
+    assert got[1] is None and float(got[2]) == 3.0
+    m = torch.nn.Linear(2, 2)
+    BroadcastGlobalVariablesOp(m)
+    hook = ElasticHook(8, 1, 32, m)
+    steps = 1
+    while hook.after_step():
+        steps += 1
+    assert steps == 4 and hook.state.trained_samples == 32
