@@ -30,7 +30,8 @@ for _alias, _target in (('ops', 'torch.ops'), ('optimizers', 'torch.optimizers')
     _mod = importlib.import_module('kungfu_b200.' + _target)
     sys.modules['kungfu.tensorflow.' + _alias] = _mod
     setattr(_tf, _alias, _mod)
-for _alias, _target in (('benchmarks', 'benchmarks'), ('helpers', 'datasets'), ('datasets', 'datasets'), ('utils', 'utils')):
+for _alias, _target in (('benchmarks', 'benchmarks'), ('helpers', 'datasets'), ('datasets', 'datasets'), ('utils', 'utils'),
+                        ('examples', 'torch.examples')):
     _mod = importlib.import_module('kungfu_b200.' + _target)
     sys.modules['kungfu.tensorflow.v1.' + _alias] = _mod
     setattr(_v1, _alias, _mod)

@@ -32,3 +32,18 @@ class MnistCNN(nn.Module):
         x = F.relu(F.max_pool2d(self.drop(self.conv2(x)), 2))
         x = F.relu(self.fc1(x.flatten(1)))
         return F.log_softmax(self.fc2(F.dropout(x, training=self.training)), dim=1)
+
+
+def slp(input_size=784, num_classes=10):
+    """Single-layer perceptron (reference: v1/benchmarks/mnist.py slp)."""
+    return SLP(input_size, num_classes, zero_init=False)
+
+
+def mlp(input_size=784, hidden=(500, 300), num_classes=10):
+    """Multi-layer perceptron with ReLU hidden layers (reference: v1/benchmarks/mnist.py mlp)."""
+    layers, c = [nn.Flatten()], input_size
+    for h in hidden:
+        layers += [nn.Linear(c, h), nn.ReLU(inplace=True)]
+        c = h
+    layers.append(nn.Linear(c, num_classes))
+    return nn.Sequential(*layers)

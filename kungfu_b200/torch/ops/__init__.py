@@ -8,7 +8,7 @@ from .collective import (all_gather, all_reduce_fn, barrier, broadcast,  # noqa:
 from .local import request_model, request_variable_with_template, save_model, save_variables  # noqa: F401
 from .monitor import egress_rates, global_noise_scale  # noqa: F401
 from .state import counter, exponential_moving_average  # noqa: F401
-from .topology import (cluster_size, get_neighbour_mask, get_peer_latencies,  # noqa: F401
+from .topology import (cluster_size, get_neighbour_mask, get_peer_latencies, get_random_peer,  # noqa: F401
                        global_minimum_spanning_tree, minimum_spanning_tree, mst_to_tree,
                        peer_info, rank, round_robin)
 

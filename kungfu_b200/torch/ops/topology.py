@@ -83,3 +83,13 @@ class RoundRobin(object):
 
 def round_robin(mask):
     return RoundRobin(mask)
+
+
+def get_random_peer(cluster_size, self_rank, rng=None):
+    """Uniform draw from the OTHER ranks: t ~ U[0, np), a self-hit moves to the next rank
+    (/root/reference/srcs/python/kungfu/tensorflow/optimizers/async_sgd.py:71-75)."""
+    import random
+    if cluster_size <= 1:
+        return self_rank
+    t = (rng or random).randrange(cluster_size)
+    return (t + 1) % cluster_size if t == self_rank else t

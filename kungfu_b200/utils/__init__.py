@@ -118,3 +118,47 @@ class StallDetector(object):
         self._done.set()
         self._th.join()
         return False
+
+
+def map_maybe(f, lst):
+    """f over the non-None entries, None stays None (reference: kungfu/_utils.py:5-6)."""
+    return [f(x) if x is not None else None for x in lst]
+
+
+def one_based_range(n):
+    return range(1, 1 + n)
+
+
+def show_duration(seconds):
+    """'12.00ms' / '3.20s' / '2m5s' / '1h2m3s' (reference: kungfu/_utils.py:20-30)."""
+    if seconds < 1:
+        return '%.2fms' % (seconds * 1e3)
+    if seconds < 60:
+        return '%.2fs' % seconds
+    sec = int(seconds)
+    mm, ss = sec // 60, sec % 60
+    if seconds < 3600:
+        return '%dm%ds' % (mm, ss)
+    return '%dh%dm%ds' % (mm // 60, mm % 60, ss)
+
+
+class EMA(ExponentialMovingAverage):
+    """Moving average whose input is clamped to [value / scale_cap, value * scale_cap] first: one wild
+    reading (a noise-scale spike) cannot move the average by more than that factor
+    (reference: kungfu/tensorflow/v1/utils/ema.py)."""
+
+    def __init__(self, alpha, scale_cap=None):
+        super().__init__(alpha)
+        self.scale_cap = scale_cap
+
+    def update(self, x):
+        if self.value is not None and self.scale_cap is not None:
+            lo, hi = sorted((self.value / self.scale_cap, self.value * self.scale_cap))
+            x = min(max(x, lo), hi)
+        return super().update(x)
+
+    def get(self):
+        return self.value
+
+    def reset(self):
+        self.value = None

@@ -42,3 +42,35 @@ def eval_batch_size():
 def eval_gradient_noise_scale():
     v = _vars.get(GraphKeys.GRADIENT_NOISE_SCALE)
     return float(v) if v is not None else None
+
+
+# ---- generic accessors under the reference's names (tensorflow/variables.py:17-82) ---------------
+def create_global_variable(key, init=0):
+    _vars[key] = init
+    return init
+
+
+def get_global_variable(key):
+    return _vars[key]
+
+
+def get_or_create_global_variable(key, init=0):
+    return get_or_create(key, init)
+
+
+def eval_global_variable(key):
+    return _vars.get(key)
+
+
+def create_assign_op_for(key):
+    """A callable that stores its argument (the eager counterpart of an assign op)."""
+    return create_setter(key)
+
+
+def create_placeholder_for(key):
+    """Eager code has no placeholders: the current value stands in for it."""
+    return _vars.get(key)
+
+
+def get_batch_size():
+    return eval_batch_size()

@@ -213,3 +213,43 @@ def test_reference_tensorflow_layout_resolves_to_the_torch_front_end():
     while hook.after_step():
         steps += 1
     assert steps == 4 and hook.state.trained_samples == 32
+
+
+def test_every_public_python_name_of_the_reference_exists_here():
+    """Top-level public functions / classes of the reference's Python package, module by module, against the
+    union of our front-end modules. What may be missing is listed explicitly: TensorFlow/Keras/Horovod-only
+    plumbing that has no meaning outside a TF graph."""
+    import ast
+    import importlib
+    ref = '/root/reference/srcs/python/kungfu'
+    if not os.path.isdir(ref):
+        pytest.skip('reference tree not present')
+    mods = ['python', 'torch', 'torch.ops', 'torch.optimizers', 'torch.initializer', 'torch.policy', 'torch.elastic',
+            'variables', 'datasets', 'utils', 'benchmarks', 'benchmarks.model_sizes', 'cmd', 'info', 'models',
+            'torch.ops.collective', 'torch.ops.adapt', 'torch.ops.monitor', 'torch.ops.local', 'torch.ops.state',
+            'torch.ops.topology', 'torch.examples.__main__']
+    ours = set()
+    for m in mods:
+        ours |= set(dir(importlib.import_module('kungfu_b200.' + m)))
+    tf_only = {
+        'AdaSGDHook', 'KungFuTFOptimizer', 'KungFuTFKerasOptimizer', 'KungFuKerasOptimizer',  # TF optimizer base classes
+        'hvd_init', 'hvd_group_all_reduce', 'get_cluster_size', 'get_rank', 'parse_args', 'log_detailed_result',
+        'log_final_result', 'all_reduce_benchmark', 'main',  # benchmark script internals (Horovod arm)
+        'new_conv_kernel', 'new_bias', 'new_dense_weight', 'conv2d', 'max_pool', 'Layer', 'seq_apply', 'Pool', 'Dense',
+        'Conv',  # TF layer helpers of the benchmark models
+        'write_idx_header', 'write_idx_to', 'read_idx_header', 'read_idx_from',  # file-object halves of read/write_idx_file
+        'record_to_labeled_image', 'create_dataset_from_files',  # TFRecord parsing
+        'training_step', 'test_gradient_tape',  # TF2 GradientTape demo
+        'import_op_lib',  # loader of the TF/torch op .so (ours is kungfu_b200.ops._cuda.lib)
+    }
+    missing = {}
+    for base, _, files in os.walk(ref):
+        for f in files:
+            if not f.endswith('.py'):
+                continue
+            path = os.path.join(base, f)
+            for node in ast.parse(open(path).read()).body:
+                if isinstance(node, (ast.FunctionDef, ast.ClassDef)) and not node.name.startswith('_'):
+                    if node.name not in ours and node.name not in tf_only:
+                        missing.setdefault(os.path.relpath(path, ref), []).append(node.name)
+    assert not missing, missing
