@@ -69,6 +69,28 @@ class Peer
         async([=] { kf_all_reduce(p_, send, recv, count, dtype, op, n.c_str()); }, done);
         return 0;
     }
+    // all-reduce along `tree` (father array of Size() entries, nullptr = active strategy) that also feeds the
+    // per-strategy throughput statistics CheckInterference() votes on
+    int MonitoredAllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const int32_t *tree,
+                           const char *name)
+    {
+        return kf_monitored_all_reduce(p_, send, recv, count, dtype, op, tree, tree ? Size() : 0, name);
+    }
+    int MonitoredAllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const int32_t *tree,
+                           const char *name, DoneCallback done)
+    {
+        std::string n(name);
+        std::vector<int32_t> t(tree ? tree : nullptr, tree ? tree + Size() : nullptr);
+        async([=] { kf_monitored_all_reduce(p_, send, recv, count, dtype, op, t.empty() ? nullptr : t.data(), (int)t.size(), n.c_str()); },
+              done);
+        return 0;
+    }
+    // runs `done` on the runtime's callback path without doing any communication (ordering / wake-up hook)
+    int Noop(DoneCallback done)
+    {
+        async([] {}, done);
+        return 0;
+    }
     int CrossAllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
     {
         return kf_cross_all_reduce(p_, send, recv, count, dtype, op, name);

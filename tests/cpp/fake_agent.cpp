@@ -96,6 +96,20 @@ int main()
         CHECK(peer.AllReduce(&one, &sum, 1, kungfu::I32, kungfu::SUM, "after-set-tree") == 0);
         CHECK(sum == np);
     }
+    // MonitoredAllReduce along an explicit star rooted at the last rank (sync and callback forms), Noop
+    {
+        std::vector<int32_t> star(np, np - 1);
+        std::vector<int64_t> x(1000, rank + 1), y(1000, 0), z(1000, 0);
+        CHECK(peer.MonitoredAllReduce(x.data(), y.data(), 1000, kungfu::I64, kungfu::SUM, star.data(), "monitored") == 0);
+        CHECK(y[0] == (int64_t)np * (np + 1) / 2 && y[999] == y[0]);
+        kungfu::Latch done(2);
+        peer.MonitoredAllReduce(x.data(), z.data(), 1000, kungfu::I64, kungfu::SUM, nullptr, "monitored-async",
+                                [&] { done.done(); });
+        peer.Noop([&] { done.done(); });
+        done.wait();
+        CHECK(z[500] == y[0]);
+        peer.CalcStats();
+    }
     peer.Barrier();
     printf("OK fake-agent rank %d/%d\n", rank, np);
     return 0;
