@@ -169,10 +169,14 @@ uint64_t Peer::uid() const
 bool Peer::update_to(const PeerList &workers)
 {
     StallDetector sd("peer update");
-    server_->set_token((uint32_t)version_);
-    client_->set_token((uint32_t)version_);
+    // Order matters: drop what belongs to the previous epoch while the server still answers with the OLD
+    // token (members already in the new epoch are refused and retry), and only then open the new epoch.
+    // The other way round a fast peer's first message of the new epoch could land between the two steps
+    // and be discarded, leaving everybody in the barrier below forever (seen once in ~5 runs under TSAN).
     client_->reset();
     server_->mailbox.reset();
+    client_->set_token((uint32_t)version_);
+    server_->set_token((uint32_t)version_);
     {
         std::lock_guard<std::mutex> lk(mu_);
         session_.reset(new Session(workers, cfg_.self, cfg_.strategy, client_.get(), server_.get()));

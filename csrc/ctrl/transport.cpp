@@ -609,9 +609,15 @@ void Server::serve(int fd)
 // ---- client -----------------------------------------------------------------------------
 int Client::dial(const PeerID &dst, ConnType type, bool retry, std::string *err)
 {
-    const int attempts = retry ? std::max(1, cfg_.conn_retry_count) : 1;
-    for (int i = 0; i < attempts; ++i) {
-        int fd = -1;
+    // Total patience = retry count x retry period (500 x 200 ms by default, like the reference). A peer that
+    // answers with another epoch's token is alive and merely has not reached the same membership yet (it
+    // is still starting, or still finishing the previous epoch): poll it quickly instead of sleeping a
+    // whole retry period, so start-up and resizes do not pay 200 ms for losing a race by a microsecond.
+    const double budget = retry ? std::max(1, cfg_.conn_retry_count) * cfg_.conn_retry_period : 0.0;
+    const double t0     = now_seconds();
+    for (;;) {
+        int fd        = -1;
+        bool mismatch = false;
         if (cfg_.use_unix_sock && dst.colocated_with(self_)) fd = unix_connect(dst.sock_file());
         if (fd < 0 && type != CONN_FD) fd = tcp_connect(dst.ipv4, dst.port);
         if (fd >= 0) {
@@ -619,11 +625,15 @@ int Client::dial(const PeerID &dst, ConnType type, bool retry, std::string *err)
             uint32_t remote = 0;
             if (write_full(fd, &hello, sizeof(hello)) && read_full(fd, &remote, 4)) {
                 if ((type != CONN_COLLECTIVE && type != CONN_FD) || remote == hello.token) return fd;
+                mismatch = true;
                 KF_DEBUG("token mismatch dialing %s: mine %u theirs %u", dst.str().c_str(), hello.token, remote);
             }
             ::close(fd);
         }
-        if (i + 1 < attempts) std::this_thread::sleep_for(std::chrono::duration<double>(cfg_.conn_retry_period));
+        const double left = budget - (now_seconds() - t0);
+        if (left <= 0) break;
+        std::this_thread::sleep_for(
+            std::chrono::duration<double>(std::min(left, mismatch ? std::min(0.005, cfg_.conn_retry_period) : cfg_.conn_retry_period)));
     }
     if (err) *err = "cannot connect to " + dst.str();
     return -1;

@@ -178,7 +178,9 @@ class Server
     PeerID self_;
     bool use_unix_;
     int tcp_fd_ = -1, unix_fd_ = -1;
-    std::atomic<uint32_t> token_{0};
+    // Until the owner joins an epoch (set_token) collective connections are refused: a faster peer must not
+    // be able to park messages in the mailbox that the owner's first reset() would then throw away.
+    std::atomic<uint32_t> token_{0xFFFFFFFFu};
     std::atomic<bool> stopping_{false};
     std::thread tcp_thread_, unix_thread_;
     std::mutex conn_mu_;
