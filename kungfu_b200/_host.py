@@ -118,7 +118,7 @@ def _adopt_torchrun_env():
     if ws <= 1 or 'RANK' not in os.environ:
         return
     rank = int(os.environ['RANK'])
-    base = int(os.environ.get('KUNGFU_PORT_BASE', str(20000 + (int(os.environ.get('MASTER_PORT', '29500')) * 7) % 20000)))
+    base = int(os.environ.get('KUNGFU_PORT_BASE', str(20000 + (int(os.environ.get('MASTER_PORT', '29500')) * 7) % 12000)))  # below the ephemeral range
     peers = ','.join('127.0.0.1:%d' % (base + r) for r in range(ws))
     os.environ['KUNGFU_SELF_SPEC'] = '127.0.0.1:%d' % (base + rank)
     os.environ['KUNGFU_INIT_PEERS'] = peers

@@ -66,3 +66,35 @@ def test_ssgd_on_a_quadratic_follows_the_closed_form(np_):
     res = run_workers(np_, os.path.join(W, 'quadratic_worker.py'))
     assert res.returncode == 0, res.stdout[-3000:]
     assert res.stdout.count('OK quadratic') == np_
+
+
+@pytest.mark.parametrize('np_', [2, 4])
+def test_descriptor_passing_between_colocated_workers(np_):
+    """SCM_RIGHTS over the control plane: the path every multi-GPU job uses to share its VMM handles."""
+    res = run_workers(np_, os.path.join(W, 'fd_worker.py'))
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert res.stdout.count('OK fd passing') == np_
+
+
+def test_torchrun_environment_is_adopted(tmp_path):
+    """bench.py is launched by torchrun (RANK / WORLD_SIZE / MASTER_PORT, no kungfu-run): the runtime derives an
+    equivalent single-host peer list from that environment."""
+    import subprocess
+    import sys
+    script = tmp_path / 'w.py'
+    script.write_text("import torch\nimport kungfu_b200.torch as kf\n"
+                      "r, n = kf.current_rank(), kf.current_cluster_size()\n"
+                      "y = kf.ops.all_reduce_fn(torch.full((5,), float(r + 1)), name='t')\n"
+                      "assert n == 3 and float(y[0]) == 6.0, (n, y)\n"
+                      "kf.run_barrier()\nprint('OK torchrun-env rank', r, flush=True)\n")
+    port = 29000 + os.getpid() % 900
+    procs = []
+    for r in range(3):
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE='3', MASTER_ADDR='127.0.0.1',
+                   MASTER_PORT=str(port), PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+        env.pop('KUNGFU_SELF_SPEC', None)
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert sum('OK torchrun-env' in o for o in outs) == 3
