@@ -387,9 +387,18 @@ struct RunningProc {
     std::thread out_th, err_th;
     int exit_code = -1;
     bool done     = false;
+    int attempt   = 0;
+    std::atomic<bool> loader_bug{false};  // stderr carried the dynamic-linker assertion (see kLoaderBug)
 };
 
-void pump(int fd, const std::string &prefix, const char *color, bool echo, FILE *copy, bool to_stderr)
+// glibc's dynamic linker occasionally dies at start-up with this assertion when many processes load the
+// same CUDA / NCCL libraries at once; the process has done nothing yet, so starting it again is safe.
+// (/root/reference/srcs/go/utils/runner/local/hack.go:14-35, srcs/go/nccl/bug.go:10)
+constexpr const char *kLoaderBug = "Inconsistency detected by ld.so";
+constexpr int kLoaderBugRetries  = 3;
+
+void pump(int fd, const std::string &prefix, const char *color, bool echo, FILE *copy, bool to_stderr,
+          std::atomic<bool> *loader_bug = nullptr)
 {
     FILE *in = fdopen(fd, "r");
     if (!in) return;
@@ -397,6 +406,7 @@ void pump(int fd, const std::string &prefix, const char *color, bool echo, FILE 
     size_t cap = 0;
     ssize_t n;
     while ((n = getline(&line, &cap, in)) > 0) {
+        if (loader_bug && strstr(line, kLoaderBug)) *loader_bug = true;
         if (copy) {
             fwrite(line, 1, (size_t)n, copy);
             fflush(copy);
@@ -424,7 +434,7 @@ class ProcTable
   public:
     explicit ProcTable(bool verbose) : verbose_(verbose) {}
 
-    bool spawn(const ProcSpec &spec, std::string *err)
+    bool spawn(const ProcSpec &spec, std::string *err, int attempt = 0)
     {
         int po[2], pe[2];
         if (pipe2(po, O_CLOEXEC) != 0 || pipe2(pe, O_CLOEXEC) != 0) {
@@ -467,6 +477,7 @@ class ProcTable
         auto rp  = std::make_shared<RunningProc>();
         rp->pid  = pid;
         rp->spec = spec;
+        rp->attempt = attempt;
         FILE *lo = nullptr, *le = nullptr;
         if (!spec.logdir.empty()) {
             mkdir(spec.logdir.c_str(), 0755);
@@ -475,7 +486,7 @@ class ProcTable
         }
         const char *color = kColors[color_++ % 6];
         rp->out_th = std::thread([=] { pump(po[0], spec.name + "::stdout", color, verbose_, lo, false); if (lo) fclose(lo); });
-        rp->err_th = std::thread([=] { pump(pe[0], spec.name + "::stderr", color, verbose_, le, true); if (le) fclose(le); });
+        rp->err_th = std::thread([=] { pump(pe[0], spec.name + "::stderr", color, verbose_, le, true, &rp->loader_bug); if (le) fclose(le); });
         {
             std::lock_guard<std::mutex> lk(mu_);
             procs_[spec.self] = rp;
@@ -486,6 +497,20 @@ class ProcTable
             rp->out_th.join();
             rp->err_th.join();
             const int code = WIFEXITED(status) ? WEXITSTATUS(status) : 128 + (WIFSIGNALED(status) ? WTERMSIG(status) : 0);
+            if (code != 0 && rp->loader_bug && rp->attempt < kLoaderBugRetries) {
+                KF_WARN("runner: %s hit the dynamic-linker start-up assertion (exit %d): starting it again (%d/%d)",
+                        rp->spec.name.c_str(), code, rp->attempt + 1, kLoaderBugRetries);
+                std::string e;
+                if (spawn(rp->spec, &e, rp->attempt + 1)) {
+                    // PR_SET_PDEATHSIG follows the forking THREAD: this thread has to outlive the child it just
+                    // started, or the kernel kills the child the moment we return
+                    std::unique_lock<std::mutex> lk(mu_);
+                    std::shared_ptr<RunningProc> child = procs_[rp->spec.self];
+                    cv_.wait(lk, [&] { return child->done; });
+                    return;
+                }
+                KF_ERROR("runner: restart of %s failed: %s", rp->spec.name.c_str(), e.c_str());
+            }
             std::lock_guard<std::mutex> lk(mu_);
             rp->exit_code = code;
             rp->done      = true;

@@ -98,3 +98,27 @@ def test_torchrun_environment_is_adopted(tmp_path):
     outs = [p.communicate(timeout=120)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert sum('OK torchrun-env' in o for o in outs) == 3
+
+
+def test_runner_restarts_a_worker_that_hit_the_loader_assertion(tmp_path):
+    """Fault injection (reference: kungfu-bench-allreduce -rand-nccl-failure + the runner's retry hack): one worker dies
+    once at start-up with glibc's dynamic-linker assertion on stderr; the runner starts it again and the job succeeds.
+    A worker that fails for any other reason still fails the job."""
+    script = tmp_path / 'flaky.py'
+    script.write_text("import os, sys\n"
+                      "flag = %r + '/crashed-once'\n"
+                      "try:\n"
+                      "    os.close(os.open(flag, os.O_CREAT | os.O_EXCL | os.O_WRONLY))  # exactly one worker wins\n"
+                      "    first = True\n"
+                      "except FileExistsError:\n"
+                      "    first = False\n"
+                      "if first:\n"
+                      "    sys.stderr.write('Inconsistency detected by ld.so: dl-open.c: 272: dl_open_worker: Assertion failed!\\n')\n"
+                      "    sys.exit(127)\n"
+                      "import kungfu_b200.torch as kf\n"
+                      "kf.run_barrier()\n"
+                      "print('OK after restart rank', kf.current_rank(), flush=True)\n" % str(tmp_path))
+    res = run_workers(2, str(script), timeout=90)
+    assert res.returncode == 0, res.stdout[-3000:]
+    assert res.stdout.count('OK after restart') == 2
+    assert os.path.exists(str(tmp_path / 'crashed-once'))
