@@ -3,6 +3,7 @@ Mirrors the reference's Go/C++ unit tests: /root/reference/srcs/go/plan/*_test.g
 /root/reference/tests/cpp/unit/test_{dtype,mst,op}.cpp."""
 import ctypes as C
 import json
+import os
 
 import numpy as np
 import pytest
@@ -255,3 +256,23 @@ def test_cuda_entry_points_reject_bad_arguments_before_touching_the_device():
     assert b'head dim' in lib.kfb_last_error()
     assert lib.kfb_colsum_scratch_floats(768) >= 64 * 768
     assert lib.kfb_ln_partial_floats(4096, 768) % (2 * 768) == 0
+
+
+def test_built_library_contains_the_blackwell_instructions():
+    """The device library is sm_100a code that really uses the 5th-generation tensor cores, TMA, tensor memory,
+    cluster barriers and NVLS multimem: check the SASS of the built .so (no GPU needed, cuobjdump ships with CUDA)."""
+    import re
+    import shutil
+    import subprocess
+    from kungfu_b200.ops import _cuda as K
+    tool = shutil.which('cuobjdump') or '/usr/local/cuda/bin/cuobjdump'
+    if not os.path.exists(tool):
+        pytest.skip('cuobjdump not available')
+    elf = subprocess.run([tool, '-lelf', K.LIB_PATH], stdout=subprocess.PIPE, text=True).stdout
+    assert 'sm_100a' in elf, elf[:500]
+    sass = subprocess.run([tool, '-sass', K.LIB_PATH], stdout=subprocess.PIPE, text=True, timeout=300).stdout
+    for mnemonic, meaning in (('UTCHMMA', 'tcgen05.mma'), ('UTCHMMA.2CTA', 'tcgen05.mma.cta_group::2'),
+                              ('UTMALDG.2D', 'cp.async.bulk.tensor (TMA)'), ('UTCBAR', 'tcgen05.commit'),
+                              ('LDTM', 'tcgen05.ld'), ('UCGABAR_ARV', 'barrier.cluster'), ('LDGMC', 'multimem.ld_reduce'),
+                              ('SYNCS.PHASECHK', 'mbarrier.try_wait')):
+        assert re.search(r'\b' + re.escape(mnemonic), sass), '%s (%s) not found in the SASS' % (mnemonic, meaning)
