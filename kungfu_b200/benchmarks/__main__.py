@@ -21,13 +21,19 @@ from kungfu_b200.benchmarks.model_sizes import model_sizes
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--method', default='CPU', choices=['CPU', 'P2P', 'NCCL'])
+    # the reference's method names are accepted too: NCCL+CPU (its hierarchical NCCL + TCP path) is what the device
+    # communicator does by itself when a job spans hosts, i.e. P2P here; HOROVOD is not in this image
+    ap.add_argument('--method', default='CPU', choices=['CPU', 'P2P', 'NCCL', 'NCCL+CPU', 'HOROVOD'])
     ap.add_argument('--model', default='ResNet50')
     ap.add_argument('--fuse', action='store_true')
     ap.add_argument('--warmup-steps', type=int, default=3)
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--dtype', default='float32', choices=['float32', 'bfloat16'])
     args = ap.parse_args()
+    if args.method == 'HOROVOD':
+        raise SystemExit('--method HOROVOD: Horovod is not installed in this environment (use NCCL for the library baseline)')
+    if args.method == 'NCCL+CPU':
+        args.method = 'P2P'
     rank, np_ = kf.current_rank(), kf.current_cluster_size()
     sizes = model_sizes(args.model)
     if args.fuse:
