@@ -35,6 +35,7 @@ def init():
 
 
 def finalize():
+    """Stop the control plane (also registered with atexit)."""
     _finalize()
 
 
@@ -49,26 +50,32 @@ def detached():
 
 
 def current_rank():
+    """Rank of this worker in the current cluster, 0 .. size-1 (changes after a resize)."""
     return _p().rank()
 
 
 def current_local_rank():
+    """Rank among the workers of this host (the GPU index by default)."""
     return _p().local_rank()
 
 
 def current_cluster_size():
+    """Number of workers in the current cluster (changes after a resize)."""
     return _p().size()
 
 
 def current_local_size():
+    """Number of workers on this host."""
     return _p().local_size()
 
 
 def host_count():
+    """Number of hosts the current cluster spans."""
     return _p().host_count()
 
 
 def run_barrier():
+    """Block until every worker of the current cluster has called it."""
     _p().barrier()
 
 
@@ -89,6 +96,8 @@ def resize_cluster(new_size):
 
 
 def resize_cluster_from_url():
+    """Adopt the cluster the config server currently publishes (-config-server / -builtin-config-port).
+    Returns (changed, detached) like resize_cluster."""
     changed, det = _p().resize_cluster_from_url()
     if changed:
         _on_membership_change()
@@ -107,18 +116,23 @@ def _on_membership_change():
 
 
 def check_interference():
+    """Majority vote over the workers: has the active strategy dropped well below its reference throughput?
+    (reference: session/adaptiveStrategies.go:18-127)"""
     return _p().check_interference()
 
 
 def calc_stats():
+    """Fold the traffic counters since the last call into the per-strategy throughput statistics."""
     _p().calc_stats()
 
 
 def log_stats():
+    """Log the per-strategy throughput statistics."""
     _p().log_stats()
 
 
 def print_strategy_stats():
+    """Print the per-strategy throughput statistics of this worker."""
     _p().print_strategy_stats()
 
 
@@ -129,14 +143,18 @@ def set_tree(forest):
 
 
 def set_strategy(name):
+    """Switch every worker to a named strategy (STAR, RING, CLIQUE, TREE, BINARY_TREE, BINARY_TREE_STAR,
+    MULTI_BINARY_TREE_STAR, AUTO) after consensus."""
     _p().set_strategy(name)
 
 
 def get_peer_latencies():
+    """Round-trip ping time to every peer in seconds (0 for self): the input of the minimum-spanning-tree strategy."""
     return _p().peer_latencies()
 
 
 def egress_rates():
+    """Bytes per second sent to every peer over the last monitoring period (KUNGFU_CONFIG_ENABLE_MONITORING)."""
     return _p().egress_rates()
 
 
@@ -164,11 +182,13 @@ def _get_other_ranks():
 
 
 def show_cuda_version():
+    """Print the CUDA version PyTorch was built with."""
     import torch
     print('CUDA (torch build): %s' % torch.version.cuda)
 
 
 def show_nccl_version():
+    """Print the NCCL version bundled with PyTorch (NCCL is only the comparison baseline here)."""
     import torch
     try:
         print('NCCL (torch bundled, baseline only): %s' % '.'.join(map(str, torch.cuda.nccl.version())))
@@ -182,4 +202,5 @@ def control_exchange():
 
 
 def peer():
+    """The process-wide kungfu_b200._host.Peer (started on first use)."""
     return _p()
