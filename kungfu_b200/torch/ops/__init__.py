@@ -25,6 +25,7 @@ def fuse(tensors):
 
 
 def defuse(flat, shapes):
+    """Inverse of fuse: slice ``flat`` back into tensors of the given ``shapes``."""
     import torch
     out, off = [], 0
     for s in shapes:

@@ -167,6 +167,7 @@ def _cuda_all_gather(x, y):
 
 # ---- public API ------------------------------------------------------------------------------
 def inplace_all_reduce_op(x, op=None, name=None):
+    """All-reduce ``x`` in place (CPU tensors: host runtime; CUDA tensors: peer-memory / NVLS kernels). Returns ``x``."""
     if op is None:
         op = 'sum'
     if x.is_cuda:
@@ -253,6 +254,7 @@ def inplace_broadcast_async_op(x, name=None):
 
 
 def wait_handle(handle):
+    """Block until the asynchronous op behind ``handle`` has finished."""
     with _lock:
         entry = _handles.pop(handle)
     if entry[0] == 'cuda':
@@ -262,6 +264,7 @@ def wait_handle(handle):
 
 
 def wait_all_handles(handles):
+    """Block until every handle in ``handles`` has finished."""
     for h in handles:
         wait_handle(h)
 
@@ -301,6 +304,7 @@ def broadcast(x, name=None):
 
 
 def barrier():
+    """Block until every worker has called it (CPU control plane)."""
     kfpy.run_barrier()
 
 

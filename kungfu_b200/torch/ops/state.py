@@ -18,6 +18,7 @@ class Counter(object):
 
 
 def counter(init=0, incr=1):
+    """A callable that returns init, init + incr, init + 2 incr, ... (the reference's Counter op)."""
     return Counter(init, incr)
 
 

@@ -11,10 +11,12 @@ from . import collective as tops
 
 
 def rank():
+    """Rank of this worker (same as kf.current_rank())."""
     return kfpy.current_rank()
 
 
 def cluster_size():
+    """Number of workers (same as kf.current_cluster_size())."""
     return kfpy.current_cluster_size()
 
 
@@ -82,6 +84,7 @@ class RoundRobin(object):
 
 
 def round_robin(mask):
+    """Iterator-like object: each call returns the next index whose ``mask`` entry is true (peer selector of the reference)."""
     return RoundRobin(mask)
 
 

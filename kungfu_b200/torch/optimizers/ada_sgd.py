@@ -33,6 +33,9 @@ def _ada_step(self, closure=None):
 
 
 def AdaptiveSGDOptimizer(optimizer, named_parameters=None, change_step=0, alpha=0.1):
+    """Synchronous model averaging (SMA, blend factor ``alpha``) until ``change_step``, then S-SGD; the switch
+    broadcasts rank 0's model once so that every replica starts the synchronous phase from the same point
+    (reference: tensorflow/optimizers/ada_sgd.py:12-83)."""
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]
     else:

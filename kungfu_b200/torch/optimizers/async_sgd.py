@@ -128,6 +128,10 @@ class _PairAveraging(object):
 
 def PairAveragingOptimizer(optimizer, named_parameters=None, fuse_requests=True,
                            fused_model_name=None, seed=None):
+    """AD-PSGD: every step average the model with ONE randomly chosen peer (``v <- (v + v_peer) / 2``), then apply the
+    local gradients; no barrier, no all-reduce. With FusedSGD the pull, blend, update and publication are one kernel
+    over peer memory; set ``opt.device_select = True`` to let the kernel draw the peer (CUDA-graph capturable).
+    ``seed`` seeds the peer choice (default: a function of the rank)."""
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]
     else:

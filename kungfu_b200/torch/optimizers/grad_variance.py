@@ -73,6 +73,9 @@ def _var_step(self, closure=None):
 
 
 def MonitorGradientVarianceOptimizer(optimizer, named_parameters=None, monitor_interval=1, verbose=False):
+    """S-SGD that also measures the gradient variance across workers every ``monitor_interval`` steps:
+    ``opt.variance`` = sum over tensors of ``|| E[g^2] - E[g]^2 ||`` (reference: optimizers/grad_variance.py:46-59);
+    with FusedSGD both moments come out of one pass over peer memory."""
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]
     else:

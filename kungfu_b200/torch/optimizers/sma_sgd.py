@@ -64,6 +64,8 @@ class _SynchronousAveraging(object):
 
 
 def SynchronousAveragingOptimizer(optimizer, named_parameters=None, alpha=0.1):
+    """Synchronous model averaging (EA-SGD): ``v <- (1 - alpha) v + alpha * mean_over_workers(v)``, then the LOCAL
+    gradients are applied (reference: optimizers/sma_sgd.py:50-74). With FusedSGD: average + blend + update in one kernel."""
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]
     else:
