@@ -147,6 +147,8 @@ class BertForPreTraining(nn.Module):
 
 
 def bert_base(**kw):
+    """BERT-base for MLM + NSP pre-training (12 layers, hidden 768). Keyword arguments: any BertConfig field,
+    e.g. fused_ln, fused_grads, fused_linear, pad_vocab, dropout."""
     return BertForPreTraining(BertConfig(**kw))
 
 
@@ -157,5 +159,6 @@ def bert_tiny(**kw):
 
 
 def bert_large(**kw):
+    """BERT-large (24 layers, hidden 1024, 16 heads). Keyword arguments as for bert_base."""
     kw = dict(dict(hidden=1024, layers=24, heads=16, intermediate=4096), **kw)
     return BertForPreTraining(BertConfig(**kw))

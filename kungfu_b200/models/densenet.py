@@ -88,12 +88,15 @@ class DenseNet(nn.Module):
 
 
 def densenet121(**kw):
+    """DenseNet-121. Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16)."""
     return DenseNet(32, (6, 12, 24, 16), 64, **kw)
 
 
 def densenet169(**kw):
+    """DenseNet-169. Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16)."""
     return DenseNet(32, (6, 12, 32, 32), 64, **kw)
 
 
 def densenet201(**kw):
+    """DenseNet-201. Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16)."""
     return DenseNet(32, (6, 12, 48, 32), 64, **kw)

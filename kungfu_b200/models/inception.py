@@ -175,4 +175,5 @@ class Inception3(nn.Module):
 
 
 def inception_v3(**kw):
+    """Inception v3 for 299x299 inputs (23.8 M parameters, 27.2 M with aux_logits=True). Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), aux_logits, dropout."""
     return Inception3(**kw)

@@ -154,22 +154,27 @@ class ResNet(nn.Module):
 
 
 def resnet18(**kw):
+    """ResNet-18 (BasicBlock, [2, 2, 2, 2]). Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), s2d_stem."""
     return ResNet(BasicBlock, [2, 2, 2, 2], **kw)
 
 
 def resnet34(**kw):
+    """ResNet-34 (BasicBlock, [3, 4, 6, 3]). Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), s2d_stem."""
     return ResNet(BasicBlock, [3, 4, 6, 3], **kw)
 
 
 def resnet50(**kw):
+    """ResNet-50 (Bottleneck, [3, 4, 6, 3]; 25.6 M parameters): the headline benchmark model. Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), s2d_stem."""
     return ResNet(Bottleneck, [3, 4, 6, 3], **kw)
 
 
 def resnet101(**kw):
+    """ResNet-101 (Bottleneck, [3, 4, 23, 3]). Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), s2d_stem."""
     return ResNet(Bottleneck, [3, 4, 23, 3], **kw)
 
 
 def resnet152(**kw):
+    """ResNet-152 (Bottleneck, [3, 8, 36, 3]). Keyword arguments: num_classes, fused_bn (fused BN+ReLU(+residual) kernels on channels-last bf16), s2d_stem."""
     return ResNet(Bottleneck, [3, 8, 36, 3], **kw)
 
 

@@ -34,12 +34,15 @@ class VGG(nn.Module):
 
 
 def vgg11(**kw):
+    """VGG-11 (torchvision keys)."""
     return VGG(11, **kw)
 
 
 def vgg16(**kw):
+    """VGG-16 (138 M parameters; the communication-heavy benchmark model)."""
     return VGG(16, **kw)
 
 
 def vgg19(**kw):
+    """VGG-19."""
     return VGG(19, **kw)

@@ -14,51 +14,62 @@ _vars = {}
 
 
 def get_or_create(key, init=0):
+    """Value stored under ``key``, created with ``init`` if absent."""
     return _vars.setdefault(key, init)
 
 
 def set_value(key, value):
+    """Store ``value`` under ``key``."""
     _vars[key] = value
 
 
 def get_value(key, default=None):
+    """Value stored under ``key`` or ``default``."""
     return _vars.get(key, default)
 
 
 def create_setter(key):
+    """A one-argument callable that stores its argument under ``key``."""
     return lambda v: set_value(key, v)
 
 
 def get_or_create_batch_size(init=None):
+    """The per-worker batch size variable (set once with ``init``)."""
     if init is not None and GraphKeys.BATCH_SIZE not in _vars:
         _vars[GraphKeys.BATCH_SIZE] = init
     return _vars.get(GraphKeys.BATCH_SIZE)
 
 
 def eval_batch_size():
+    """Current per-worker batch size or None."""
     return _vars.get(GraphKeys.BATCH_SIZE)
 
 
 def eval_gradient_noise_scale():
+    """Last gradient noise scale published by the GNS monitor, as a float, or None."""
     v = _vars.get(GraphKeys.GRADIENT_NOISE_SCALE)
     return float(v) if v is not None else None
 
 
 # ---- generic accessors under the reference's names (tensorflow/variables.py:17-82) ---------------
 def create_global_variable(key, init=0):
+    """Create (or overwrite) ``key`` with ``init``."""
     _vars[key] = init
     return init
 
 
 def get_global_variable(key):
+    """Value of an existing variable (KeyError if absent)."""
     return _vars[key]
 
 
 def get_or_create_global_variable(key, init=0):
+    """Same as get_or_create (reference name)."""
     return get_or_create(key, init)
 
 
 def eval_global_variable(key):
+    """Value of ``key`` or None."""
     return _vars.get(key)
 
 
@@ -73,4 +84,5 @@ def create_placeholder_for(key):
 
 
 def get_batch_size():
+    """Same as eval_batch_size (reference name)."""
     return eval_batch_size()
