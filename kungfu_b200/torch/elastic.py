@@ -103,24 +103,42 @@ KungFuElasticTrainHook = ElasticTrainHook
 
 
 class ElasticHook(object):
-    """``ElasticHook(local_batch_size, epochs, epoch_size)``: counts trained samples, stops after
-    ``epochs * epoch_size`` of them or when detached, re-syncs state after every membership change
-    (resizes themselves are requested elsewhere, e.g. ``kf.ops.resize`` or a config server)."""
+    """``ElasticHook(local_batch_size, epochs, epoch_size, model)``: the reference's elastic session hook for plain
+    training loops. After every step it counts the trained samples, asks the config server for the current cluster
+    (``resize_cluster_from_url``, when the job was started with ``-config-server`` / ``-builtin-config-port``) and,
+    if the membership changed, re-syncs progress counters and state before the next step. ``after_step()`` returns
+    False when this worker should stop: detached by a shrink, or ``epochs * epoch_size`` samples trained."""
 
     def __init__(self, local_batch_size, epochs, epoch_size, model, optimizer=None):
+        import os
         self.local_batch_size = local_batch_size
         self.total_samples = int(epochs * epoch_size)
         self.state = ElasticState(model, optimizer)
+        self.exit_reason = None
         self._np = kfpy.current_cluster_size()
+        self._poll = bool(os.environ.get('KUNGFU_CONFIG_SERVER'))
 
     def after_step(self):
-        """Returns False when this worker should stop."""
         self.state.end_step(self.local_batch_size)
-        if kfpy.detached():
-            return False
-        if kfpy.current_cluster_size() != self._np:  # somebody resized the cluster since the last step
+        changed = False
+        if self._poll:
             self.state.profiler.begin()
+            if hasattr(self.state.optimizer, 'consolidate'):
+                self.state.optimizer.consolidate()
+            changed, detached = kfpy.resize_cluster_from_url()
+            if detached:
+                self.exit_reason = 'change cluster'
+                return False
+        elif kfpy.detached():
+            self.exit_reason = 'change cluster'
+            return False
+        if changed or kfpy.current_cluster_size() != self._np:
+            if not self._poll:
+                self.state.profiler.begin()
             old, self._np = self._np, kfpy.current_cluster_size()
             self.state.sync()
             self.state.profiler.end(old, self._np)
-        return self.state.trained_samples < self.total_samples
+        if self.state.trained_samples >= self.total_samples:
+            self.exit_reason = 'finished'
+            return False
+        return True

@@ -165,3 +165,37 @@ def test_random_resize_soak():
     assert run.returncode == 0, log[-3000:]
     assert 'finished 70 steps' in log
     assert 'now rank' in log or 'leaves at step' in log  # at least one membership change was observed
+
+
+def test_elastic_hook_follows_config_server(tmp_path):
+    """ElasticHook (reference: tensorflow/experimental/hook/elastic.py) under kungfu-run -w with a built-in config
+    server: an operator PUTs 3 workers, then 1; the hook grows, shrinks (detached workers stop) and finishes."""
+    base = _base(6)
+    cfg_port = base + 60
+    url = 'http://127.0.0.1:%d/config' % cfg_port
+    worker = [sys.executable, os.path.join(ROOT, 'tests', 'workers', 'elastic_hook_worker.py'), '1200']
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+    run = subprocess.Popen([os.path.join(BIN, 'kungfu-run'), '-q', '-w', '-np', '1', '-H', '127.0.0.1:4', '-port',
+                            str(base + 40), '-port-range', '%d-%d' % (base, base + 16), '-builtin-config-port',
+                            str(cfg_port), '-config-server', url, '-timeout', '150s'] + worker,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
+
+    def put(n):
+        c = {'Runners': ['127.0.0.1:%d' % (base + 40)], 'Workers': ['127.0.0.1:%d' % (base + i) for i in range(n)]}
+        f = tmp_path / ('c%d.json' % n)
+        f.write_text(json.dumps(c))
+        return subprocess.run([os.path.join(BIN, 'kungfu-test-util'), '-propose', str(f), '-server', url],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=30)
+    try:
+        time.sleep(5)
+        assert put(3).returncode == 0
+        time.sleep(8)
+        assert put(1).returncode == 0
+        log, _ = run.communicate(timeout=170)
+    finally:
+        if run.poll() is None:
+            run.kill()
+    assert run.returncode == 0, log[-3000:]
+    assert log.count('OK elastic hook: change cluster') == 2, log[-3000:]
+    assert 'OK elastic hook: finished after' in log
+    assert 'resize 1 -> 3' in log and 'resize 3 -> 1' in log
