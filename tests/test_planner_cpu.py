@@ -1,0 +1,107 @@
+"""The device strategy executor (kungfu_b200.parallel.planner.GraphExecutor) simulated on the host: every rank is a
+thread, the device barrier is a threading.Barrier, the two edge kernels act on numpy arrays. Checks, for every named
+strategy and np = 2..8 (one and two hosts), that the compiled rounds leave the full sum on every rank - i.e. that the
+round / depth compilation of the reference's (reduce, broadcast) graph pairs is right - without a GPU."""
+import ctypes as C
+import re
+import threading
+
+import numpy as np
+import pytest
+
+from kungfu_b200 import _host as H
+
+STRATEGIES = ['STAR', 'RING', 'CLIQUE', 'TREE', 'BINARY_TREE', 'BINARY_TREE_STAR', 'MULTI_BINARY_TREE_STAR', 'AUTO']
+ES = 4  # float32
+
+
+def _graphs(peers, strategy):
+    l = H.lib()
+    l.kf_gen_strategy_graphs.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+    buf = C.create_string_buffer(1 << 18)
+    assert l.kf_gen_strategy_graphs(peers.encode(), strategy.encode(), buf, len(buf)) >= 0, l.kf_last_error()
+    out = []
+    for line in buf.value.decode().strip().split('\n'):
+        red, bc = line.split(' bcast=')
+        edges = lambda t: [(int(a), int(b)) for a, b in re.findall(r'\((\d+)->(\d+)\)', t)]  # noqa: E731
+        out.append({'loops': set(int(a) for a in re.findall(r'\((\d+)\)', red)), 'reduce': edges(red), 'bcast': edges(bc)})
+    return out
+
+
+class _FakeComm(object):
+    def __init__(self, rank, np_, barrier):
+        self.rank, self.np, self._b = rank, np_, barrier
+
+    def barrier(self, stream=None):
+        self._b.wait(timeout=30)
+
+
+class _FakeBuf(object):
+    """ptrs[r] = byte address of rank r's buffer inside one shared arena"""
+
+    def __init__(self, np_, stride):
+        self.ptrs = [r * stride for r in range(np_)]
+
+
+def _simulate(peers, strategy, count=1000):
+    from kungfu_b200.ops import collective as coll
+    from kungfu_b200.ops import _cuda as K
+    from kungfu_b200.parallel import planner
+    np_ = len(peers.split(','))
+    strategies = _graphs(peers, strategy)
+    stride = (count * ES + 255) // 256 * 256
+    arena = np.zeros(np_ * stride // ES, dtype=np.float32)
+    for r in range(np_):
+        arena[r * stride // ES:r * stride // ES + count] = np.arange(count, dtype=np.float32) * 0.001 + (r + 1)
+    want = sum(np.arange(count, dtype=np.float32) * 0.001 + (r + 1) for r in range(np_))
+    view = lambda ptr, n: arena[ptr // ES:ptr // ES + n]  # noqa: E731
+    lock = threading.Lock()
+
+    def edge_reduce(dst, src, n, dtype, op='sum', **_):
+        with lock:
+            view(dst, n)[:] += view(src, n)
+
+    def edge_copy(dst, src, nbytes, **_):
+        with lock:
+            view(dst, nbytes // ES)[:] = view(src, nbytes // ES)
+
+    barrier = threading.Barrier(np_)
+    buf = _FakeBuf(np_, stride)
+    errors = []
+
+    def run(rank):
+        try:
+            ex = planner.GraphExecutor(_FakeComm(rank, np_, barrier), strategies)
+            ex.all_reduce(buf, count, K.F32)
+        except Exception as e:  # noqa: BLE001
+            errors.append((rank, repr(e)))
+            barrier.abort()
+
+    old = coll.edge_reduce, coll.edge_copy
+    coll.edge_reduce, coll.edge_copy = edge_reduce, edge_copy
+    try:
+        ths = [threading.Thread(target=run, args=(r, )) for r in range(np_)]
+        [t.start() for t in ths]
+        [t.join(60) for t in ths]
+    finally:
+        coll.edge_reduce, coll.edge_copy = old
+    assert not errors, errors
+    for r in range(np_):
+        got = arena[r * stride // ES:r * stride // ES + count]
+        assert np.allclose(got, want, rtol=1e-6), (strategy, np_, r, got[:3], want[:3])
+    return len(strategies)
+
+
+@pytest.mark.parametrize('strategy', STRATEGIES)
+@pytest.mark.parametrize('np_', [2, 3, 4, 5, 8])
+def test_device_graph_executor_on_one_host(strategy, np_):
+    peers = ','.join('127.0.0.1:%d' % (10000 + i) for i in range(np_))
+    k = _simulate(peers, strategy)
+    if strategy in ('RING', 'CLIQUE'):
+        assert k == np_  # one rotation / root per rank: the buffer is cut into np chunks
+
+
+@pytest.mark.parametrize('strategy', ['BINARY_TREE_STAR', 'MULTI_BINARY_TREE_STAR', 'STAR', 'RING', 'AUTO'])
+def test_device_graph_executor_on_two_and_three_hosts(strategy):
+    _simulate('10.0.0.1:10000,10.0.0.1:10001,10.0.0.2:10000,10.0.0.2:10001,10.0.0.3:10000', strategy, count=777)
+    _simulate('10.0.0.1:10000,10.0.0.1:10001,10.0.0.1:10002,10.0.0.2:10000,10.0.0.2:10001,10.0.0.2:10002', strategy, count=64)
