@@ -105,3 +105,31 @@ def test_device_graph_executor_on_one_host(strategy, np_):
 def test_device_graph_executor_on_two_and_three_hosts(strategy):
     _simulate('10.0.0.1:10000,10.0.0.1:10001,10.0.0.2:10000,10.0.0.2:10001,10.0.0.3:10000', strategy, count=777)
     _simulate('10.0.0.1:10000,10.0.0.1:10001,10.0.0.1:10002,10.0.0.2:10000,10.0.0.2:10001,10.0.0.2:10002', strategy, count=64)
+
+
+def test_variant_chooser_turns_a_probe_table_into_thresholds():
+    """VariantChooser bookkeeping with a hand-written probe table (no GPU): the one-shot ceiling is the largest probe
+    size up to which one-shot kept winning, the large-message preference is the most frequent winner above it."""
+    from kungfu_b200.ops import _cuda as K
+    from kungfu_b200.ops import collective as coll
+    from kungfu_b200.parallel.planner import VariantChooser
+    saved = coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE
+    try:
+        vc = VariantChooser(_FakeComm(0, 8, None))
+        vc.table = {16 << 10: {K.ALGO_ONESHOT: 0.010, K.ALGO_TWOSHOT: 0.014},
+                    256 << 10: {K.ALGO_ONESHOT: 0.012, K.ALGO_TWOSHOT: 0.015, K.ALGO_NVLS: 0.013},
+                    2 << 20: {K.ALGO_ONESHOT: 0.060, K.ALGO_TWOSHOT: 0.030, K.ALGO_NVLS: 0.025},
+                    32 << 20: {K.ALGO_TWOSHOT: 0.110, K.ALGO_NVLS: 0.075}}
+        vc.best = {s: min(t, key=t.get) for s, t in vc.table.items()}
+        vc._install()
+        assert coll.ONESHOT_MAX_BYTES == 256 << 10
+        assert coll.PREFERRED_LARGE == K.ALGO_NVLS
+        assert vc.choose(20 << 10) == K.ALGO_ONESHOT and vc.choose(100 << 20) == K.ALGO_NVLS
+        # busBW = 2 (n-1)/n * bytes / time: 32 MiB in 75 us on 8 ranks
+        assert abs(vc.busbw(K.ALGO_NVLS) - (32 << 20) / 0.075 / 1e6 * 2 * 7 / 8) < 1e-6
+        # one-shot never wins: the ceiling falls back to its 4 KiB floor
+        vc.best = {s: K.ALGO_TWOSHOT for s in vc.table}
+        vc._install()
+        assert coll.ONESHOT_MAX_BYTES == 4 << 10 and coll.PREFERRED_LARGE == K.ALGO_TWOSHOT
+    finally:
+        coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE = saved
