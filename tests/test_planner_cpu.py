@@ -133,3 +133,28 @@ def test_variant_chooser_turns_a_probe_table_into_thresholds():
         assert coll.ONESHOT_MAX_BYTES == 4 << 10 and coll.PREFERRED_LARGE == K.ALGO_TWOSHOT
     finally:
         coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE = saved
+
+
+def test_choose_algo_decision_table():
+    from kungfu_b200.ops import _cuda as K
+    from kungfu_b200.ops import collective as coll
+
+    class Buf(object):
+        def __init__(self, mc):
+            self.mc_ptr = mc
+    saved = coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE
+    try:
+        coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE = 256 << 10, None
+        c1, c8 = _FakeComm(0, 1, None), _FakeComm(0, 8, None)
+        assert coll.choose_algo(c1, 1 << 30) == K.ALGO_ONESHOT                       # nothing to exchange
+        assert coll.choose_algo(c8, 4 << 10, Buf(1)) == K.ALGO_ONESHOT               # latency-bound sizes
+        assert coll.choose_algo(c8, 1 << 20, Buf(0)) == K.ALGO_TWOSHOT               # no multicast alias
+        assert coll.choose_algo(c8, 1 << 20, Buf(1), K.OP_SUM, K.BF16) == K.ALGO_NVLS
+        assert coll.choose_algo(c8, 1 << 20, Buf(1), K.OP_MAX, K.BF16) == K.ALGO_TWOSHOT   # the switch only adds
+        assert coll.choose_algo(c8, 1 << 20, Buf(1), K.OP_SUM, K.I32) == K.ALGO_TWOSHOT    # ... floating point
+        coll.PREFERRED_LARGE = K.ALGO_TWOSHOT                                         # what a probe may install
+        assert coll.choose_algo(c8, 1 << 20, Buf(1), K.OP_SUM, K.BF16) == K.ALGO_TWOSHOT
+        coll.PREFERRED_LARGE = K.ALGO_NVLS
+        assert coll.choose_algo(c8, 1 << 20, Buf(0)) == K.ALGO_TWOSHOT               # preferred but impossible here
+    finally:
+        coll.ONESHOT_MAX_BYTES, coll.PREFERRED_LARGE = saved
