@@ -53,8 +53,10 @@ static bool read_http(int fd, std::string *start_line, std::map<std::string, std
     bool has_len = false;
     auto it = headers->find("content-length");
     if (it != headers->end()) {
+        if (it->second.empty() || it->second[0] == '-') return false;
         len     = (size_t)strtoull(it->second.c_str(), nullptr, 10);
         has_len = true;
+        if (len > (size_t(64) << 20)) return false;  // a cluster document is a few KiB: refuse absurd bodies
     }
     if (has_len) {
         while (body->size() < len) {
