@@ -199,3 +199,46 @@ def test_elastic_hook_follows_config_server(tmp_path):
     assert log.count('OK elastic hook: change cluster') == 2, log[-3000:]
     assert 'OK elastic hook: finished after' in log
     assert 'resize 1 -> 3' in log and 'resize 3 -> 1' in log
+
+
+def test_config_server_survives_malformed_requests():
+    """Garbage, truncated heads, lying or negative Content-Length, broken JSON: every one is refused or ignored and
+    the server keeps serving."""
+    import socket
+    port = _base(7)
+    url = 'http://127.0.0.1:%d/config' % port
+    srv = subprocess.Popen([os.path.join(BIN, 'kungfu-config-server'), '-port', str(port)],
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+
+    def raw(data):
+        s = socket.create_connection(('127.0.0.1', port), timeout=5)
+        s.sendall(data)
+        try:
+            s.shutdown(socket.SHUT_WR)
+            out = s.recv(4096)
+        except OSError:
+            out = b''
+        s.close()
+        return out
+    try:
+        for _ in range(50):
+            try:
+                _get(url)
+                break
+            except Exception:
+                time.sleep(0.1)
+        assert raw(b'\x00\x01\x02garbage\r\n\r\n').startswith(b'HTTP/1.1 404')
+        assert raw(b'GET /config HTTP/1.1\r\n') == b''
+        assert raw(b'PUT /config HTTP/1.1\r\nContent-Length: 999999999999\r\n\r\nabc') == b''
+        assert raw(b'PUT /config HTTP/1.1\r\nContent-Length: -5\r\n\r\n{}') == b''
+        assert raw(b'PUT /config HTTP/1.1\r\nContent-Length: 12\r\n\r\n{"Runners":1').startswith(b'HTTP/1.1 400')
+        assert raw(b'A' * 200000) == b''
+        assert srv.poll() is None
+        good = json.dumps({'Runners': ['127.0.0.1:38080'], 'Workers': ['127.0.0.1:10000', '127.0.0.1:10001']}).encode()
+        req = urllib.request.Request(url, data=good, method='PUT')
+        assert urllib.request.urlopen(req, timeout=5).status == 200
+        status, body = _get(url)
+        assert status == 200 and len(json.loads(body)['Workers']) == 2
+    finally:
+        srv.kill()
+        srv.wait()
