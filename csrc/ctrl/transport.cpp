@@ -13,6 +13,7 @@
 
 #include <chrono>
 #include <cstring>
+#include <new>
 #include <sstream>
 
 #include "core/log.hpp"
@@ -227,7 +228,8 @@ bool read_message_header(int fd, MsgHeader *h)
     h->name.resize(nl);
     if (nl && !read_full(fd, &h->name[0], nl)) return false;
     if (!read_full(fd, &h->flags, 4)) return false;
-    return read_full(fd, &h->len, 8);
+    // no tensor of a model is anywhere near 64 GiB: a larger length is a corrupt or hostile header
+    return read_full(fd, &h->len, 8) && h->len <= (uint64_t(1) << 36);
 }
 
 // ---- monitor ----------------------------------------------------------------------------
@@ -311,7 +313,8 @@ Body BodyPool::acquire(size_t len)
         }
         ++misses_;
     }
-    b.data.reset(new uint8_t[b.cap]);  // not value-initialised: the socket read fills it
+    b.data.reset(new (std::nothrow) uint8_t[b.cap]);  // not value-initialised: the socket read fills it
+    if (!b.data) b.cap = b.len = 0;                    // out of memory: the caller drops the connection
     return b;
 }
 
@@ -347,6 +350,7 @@ bool Mailbox::deliver(const PeerID &src, const std::string &name, int fd, uint64
         return ok;
     }
     Body body = BodyPool::instance().acquire(len);
+    if (len && !body.data) return false;
     if (len && !read_full(fd, body.data.get(), len)) {
         BodyPool::instance().release(std::move(body));
         return false;
