@@ -122,3 +122,47 @@ def test_runner_restarts_a_worker_that_hit_the_loader_assertion(tmp_path):
     assert res.returncode == 0, res.stdout[-3000:]
     assert res.stdout.count('OK after restart') == 2
     assert os.path.exists(str(tmp_path / 'crashed-once'))
+
+
+def test_workers_survive_garbage_and_hostile_headers_on_their_ports(tmp_path):
+    """A port scanner, a stray client or a corrupt peer must cost a connection, never a worker: random bytes, a valid
+    hello followed by absurd name / body lengths, on every connection type, while a 2-worker job is running."""
+    import socket
+    import struct
+    import subprocess
+    import sys
+    import time
+    script = tmp_path / 'slow.py'
+    script.write_text("import time, torch\nimport kungfu_b200.torch as kf\nkf.run_barrier()\n"
+                      "open(%r + '/up-%%d' %% kf.current_rank(), 'w').close()\ntime.sleep(3)\n"
+                      "y = kf.ops.all_reduce_fn(torch.ones(100000), name='after-garbage')\n"
+                      "assert float(y[0]) == 2.0\nprint('OK survived', kf.current_rank(), flush=True)\n" % str(tmp_path))
+    base = 20000 + (os.getpid() * 41) % 11000
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get('PYTHONPATH', ''))
+    run = subprocess.Popen([os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run'), '-q', '-np', '2', '-port-range',
+                            '%d-%d' % (base, base + 8), '-port', str(base + 20), '-timeout', '80s', sys.executable, str(script)],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
+    try:
+        t0 = time.time()
+        while time.time() - t0 < 60 and not all(os.path.exists(str(tmp_path / ('up-%d' % r))) for r in (0, 1)):
+            time.sleep(0.1)
+        hello = lambda t: struct.pack('<IHHII', 0x4b46b200, t, 1, 0x7f000001, 0)  # noqa: E731
+        bad = [os.urandom(512), b'GET / HTTP/1.1\r\n\r\n',
+               struct.pack('<I', 5) + b'hello' + struct.pack('<IQ', 0, 2 ** 63 + 7),   # body length beyond any tensor
+               struct.pack('<I', 2 ** 31),                                              # name length beyond the limit
+               struct.pack('<I', 3) + b'abc' + struct.pack('<IQ', 0, 2 ** 30) + b'x' * 64]  # body that never arrives
+        for port in (base, base + 1):
+            for t in range(5):
+                for body in bad:
+                    try:
+                        s = socket.create_connection(('127.0.0.1', port), timeout=2)
+                        s.sendall((hello(t) if body is not bad[0] else b'') + body)
+                        s.close()
+                    except OSError:
+                        pass
+        log, _ = run.communicate(timeout=90)
+    finally:
+        if run.poll() is None:
+            run.kill()
+    assert run.returncode == 0, log[-3000:]
+    assert log.count('OK survived') == 2
