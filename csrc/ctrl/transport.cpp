@@ -21,6 +21,10 @@
 namespace kf {
 
 static constexpr uint32_t kMagic = 0x4b46b200u;  // "KF" b200
+// Bodies of the non-collective connection types are read into fresh zero-filled strings, so their announced
+// length must be bounded BEFORE the allocation: 600 hostile "1 GiB ping" headers used to cost 60 GB of RSS.
+static constexpr uint64_t kMaxSmallBody   = 64 << 10;
+static constexpr uint64_t kMaxControlBody = 16 << 20;
 
 TransportConfig TransportConfig::from_env()
 {
@@ -580,6 +584,7 @@ void Server::serve(int fd)
             break;
         }
         case CONN_P2P: {
+            if (h.len > kMaxSmallBody) return;  // a version label, not a payload
             std::string version(h.len, '\0');
             if (h.len && !read_full(fd, &version[0], h.len)) return;
             auto blob = version.empty() ? store.get(h.name) : vstore.get(version, h.name);
@@ -594,12 +599,14 @@ void Server::serve(int fd)
             break;
         }
         case CONN_CONTROL: {
+            if (h.len > kMaxControlBody) return;  // a stage document (cluster JSON)
             std::string body(h.len, '\0');
             if (h.len && !read_full(fd, &body[0], h.len)) return;
             if (on_control) on_control(src, h.name, body);
             break;
         }
         case CONN_PING: {
+            if (h.len > kMaxSmallBody) return;
             std::string body(h.len, '\0');
             if (h.len && !read_full(fd, &body[0], h.len)) return;
             if (!write_message(fd, h.name, FLAG_IS_RESPONSE, body.data(), body.size())) return;
