@@ -77,11 +77,22 @@ class JsonParser
         ++i_;
         return out;
     }
+    // Cluster and stage documents nest three levels deep. The limit keeps a hostile "[[[[..." (a 100 KB PUT to the
+    // config server is enough) from overflowing the stack of this recursive-descent parser.
+    static constexpr int kMaxDepth = 64;
+    int depth_ = 0;
+    struct DepthGuard {
+        int &d;
+        explicit DepthGuard(int &x) : d(x) { ++d; }
+        ~DepthGuard() { --d; }
+    };
+
     Json value()
     {
         Json j;
+        DepthGuard guard(depth_);
         ws();
-        if (i_ >= s_.size()) {
+        if (i_ >= s_.size() || depth_ > kMaxDepth) {
             ok_ = false;
             return j;
         }

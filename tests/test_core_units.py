@@ -276,3 +276,32 @@ def test_built_library_contains_the_blackwell_instructions():
                               ('LDTM', 'tcgen05.ld'), ('UCGABAR_ARV', 'barrier.cluster'), ('LDGMC', 'multimem.ld_reduce'),
                               ('SYNCS.PHASECHK', 'mbarrier.try_wait')):
         assert re.search(r'\b' + re.escape(mnemonic), sass), '%s (%s) not found in the SASS' % (mnemonic, meaning)
+
+
+def test_json_and_hostfile_parsers_survive_mutated_and_deeply_nested_input():
+    """Thousands of randomly mutated cluster documents, truncated ones, NUL / high bytes, and 100 000-level nesting
+    (which used to overflow the recursive parser's stack): every call returns, valid documents still resize."""
+    import random
+    l = _lib()
+    good = json.dumps({'Runners': ['127.0.0.1:38080'], 'Workers': ['127.0.0.1:10000', '127.0.0.1:10001']})
+    buf = C.create_string_buffer(1 << 16)
+    assert l.kf_cluster_resize(good.encode(), 3, buf, len(buf)) >= 0 and len(json.loads(buf.value.decode())['Workers']) == 3
+    rng = random.Random(7)
+    accepted = 0
+    for _ in range(3000):
+        s = list(good)
+        for _ in range(rng.randint(1, 6)):
+            op, pos = rng.random(), rng.randrange(len(s) + 1)
+            if op < 0.4 and s:
+                s.pop(min(pos, len(s) - 1))
+            elif op < 0.8:
+                s.insert(pos, rng.choice('{}[]":,\\0123456789.eE-+ntf\x00\xff abc'))
+            else:
+                s = s[:pos]
+        data = ''.join(s).encode('latin1')
+        accepted += l.kf_cluster_resize(data, rng.randint(-2, 9), buf, len(buf)) >= 0
+        l.kf_parse_hostfile(data, buf, len(buf))
+    assert accepted < 3000
+    for depth in (65, 1000, 100000):
+        assert l.kf_cluster_resize(b'[' * depth, 2, buf, len(buf)) < 0
+        assert l.kf_cluster_resize(b'{"a":' * depth, 2, buf, len(buf)) < 0
