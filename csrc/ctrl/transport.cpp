@@ -718,9 +718,10 @@ bool Client::request(const PeerID &dst, const std::string &version, const std::s
         return false;
     }
     if (h.len != len) {
-        // drain to keep the stream aligned, then report
-        std::vector<char> sink(h.len);
-        if (h.len) read_full(c->fd, sink.data(), h.len);
+        // wrong size: the stream can no longer be trusted to be aligned with what we expect - drop the
+        // connection (the next request dials again) instead of allocating a sink of the announced size
+        ::close(c->fd);
+        c->fd = -1;
         if (err) *err = "blob '" + name + "' has " + std::to_string(h.len) + " bytes, expected " + std::to_string(len);
         return false;
     }
@@ -758,6 +759,7 @@ double Client::ping(const PeerID &dst)
     MsgHeader h;
     char payload[8] = "kfping";
     bool ok         = write_message(fd, "ping", FLAG_NONE, payload, sizeof(payload)) && read_message_header(fd, &h);
+    if (ok && h.len > kMaxSmallBody) ok = false;  // an echo of our 8 bytes, nothing bigger
     if (ok && h.len) {
         std::vector<char> b(h.len);
         ok = read_full(fd, b.data(), h.len);
