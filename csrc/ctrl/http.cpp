@@ -98,6 +98,10 @@ void HttpServer::loop()
             if (errno == EINTR) continue;
             break;
         }
+        // a request that stalls (half a header, a body that never comes) must not pin a thread forever
+        timeval tv{10, 0};
+        setsockopt(c, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
+        setsockopt(c, SOL_SOCKET, SO_SNDTIMEO, &tv, sizeof(tv));
         ++inflight_;
         std::thread([this, c] {
             serve(c);
