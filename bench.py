@@ -31,6 +31,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 BASELINE_IMG_S = 5507.0  # KungFu S-SGD, ResNet-50, global batch 4096, 16 x V100
+BASELINE_NOTE = ('vs_baseline divides by the only published figure (KungFu S-SGD over TCP, TensorFlow fp32, global batch '
+                 '4096 on 16 x V100 = 5507 img/s): other hardware, precision and framework, context only; the same-box '
+                 'comparison is the `same_box_baseline` block (stock PyTorch DDP over NCCL on these GPUs)')
 
 
 def parse_args():
@@ -48,6 +51,13 @@ def parse_args():
                     help='evaluate the 7x7/2 stem as a 4x4 conv over a space-to-depth input (same maths)')
     ap.add_argument('--momentum', type=float, default=0.0)
     ap.add_argument('--skip-e2e', action='store_true')
+    ap.add_argument('--overlap', type=int, default=int(os.environ.get('KUNGFU_BENCH_OVERLAP', '1')),
+                    help='launch the fused exchange+update bucket by bucket from autograd hooks, under backward')
+    ap.add_argument('--same-box-baseline', default=os.environ.get('KUNGFU_BENCH_BASELINE', 'ddp'),
+                    choices=['ddp', 'none'],
+                    help='after the timed region, also time stock PyTorch (torchvision-style ResNet-50, torch BN, '
+                         'torch.optim.SGD, DistributedDataParallel over NCCL) with the same protocol')
+    ap.add_argument('--baseline-steps', type=int, default=10)
     return ap.parse_args()
 
 
@@ -113,6 +123,93 @@ def reference_arm(args):
     return 0
 
 
+def correctness_check(kf, K, opt, dev, rank, np_):
+    """Untimed, after the measurement: (1) every rank holds bit-identical
+    parameters (device-side byte consensus over the whole parameter arena);
+    (2) one fused exchange+update step on a 1 Mi-element bf16 buffer against a
+    host-computed fp32 result. The reference's NCCL trainer swept int32 sums
+    before timing (/root/reference/tests/cpp/integration/fake_nccl_trainer.cpp:34-63)."""
+    import torch
+
+    from kungfu_b200.ops import collective as coll
+    from kungfu_b200.optim import FusedSGD
+    comm = opt.comm
+    out = {'np': np_, 'algo': opt.last_algo, 'multicast': bool(getattr(comm, 'multicast_ok', False))}
+    identical = True
+    if np_ > 1:
+        agree = torch.zeros(1, dtype=torch.int32, device=dev)
+        for _, arenas in opt.arenas():
+            for a in arenas:
+                coll.consensus(comm, a.params_buf, a.nbytes, agree)
+                torch.cuda.synchronize()
+                identical = identical and bool(int(agree))
+    out['params_identical'] = identical
+    n = 1 << 20
+    w = torch.nn.Parameter(torch.zeros(n, device=dev, dtype=torch.bfloat16))
+    chk = kf.optimizers.SynchronousSGDOptimizer(FusedSGD([w], lr=1.0), named_parameters=[('check', w)])
+    idx = torch.arange(n, device=dev)
+    w.grad = ((idx % 7) + rank).to(torch.bfloat16)
+    chk.step()
+    torch.cuda.synchronize()
+    # mean over ranks of (i % 7 + r) = i % 7 + (np - 1) / 2: exact in bf16, so the only acceptable error is 0
+    want = -((idx % 7).float() + (np_ - 1) / 2.0)
+    out['fused_step_max_err'] = float((w.detach().float() - want).abs().max())
+    out['fused_step_algo'] = chk.last_algo
+    return out
+
+
+def ddp_baseline(args, kf, dev, rank, np_, local_rank):
+    """Stock PyTorch on the same GPUs, same protocol: plain ResNet-50 (torch
+    BatchNorm / ReLU / pooling, cuDNN convolutions), bf16 channels-last,
+    torch.optim.SGD, DistributedDataParallel over NCCL when N > 1. None of this
+    repo's kernels or optimizers are on this path."""
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+
+    from kungfu_b200 import models
+    torch.manual_seed(1234)
+    B, S = args.batch_size, args.image_size
+    model = models.resnet50(fused_bn=False, s2d_stem=False).to(dev).to(torch.bfloat16).to(memory_format=torch.channels_last)
+    model.train()
+    net = model
+    if np_ > 1:
+        if not dist.is_initialized():
+            if 'MASTER_ADDR' in os.environ and 'RANK' in os.environ:
+                dist.init_process_group('nccl', device_id=dev)
+            else:
+                dist.init_process_group('nccl', init_method='tcp://127.0.0.1:%d' % (29200 + np_), rank=rank,
+                                        world_size=np_, device_id=dev)
+        net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[dev.index], gradient_as_bucket_view=True)
+    opt = torch.optim.SGD(model.parameters(), lr=0.01 * np_)
+    x = torch.randn(B, 3, S, S, device=dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (B, ), device=dev)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        F.cross_entropy(net(x).float(), y).backward()
+        opt.step()
+
+    for _ in range(5):
+        step()
+    torch.cuda.synchronize()
+    kf.run_barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.baseline_steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    kf.run_barrier()
+    ms = float(kf.ops.all_reduce_fn(torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64), 'max')[0])
+    ms /= args.baseline_steps
+    if dist.is_initialized():
+        dist.destroy_process_group()
+    return {'impl': 'torch DDP (NCCL) + torch.optim.SGD, stock torch BN/ReLU, eager' if np_ > 1 else
+            'torch.optim.SGD, stock torch BN/ReLU, eager (single GPU)',
+            'value': B * np_ / (ms / 1e3), 'unit': 'img/s', 'ms_per_step': ms, 'steps': args.baseline_steps, 'warmup': 5}
+
+
 def main():
     args = parse_args()
     if args.impl == 'reference':
@@ -139,7 +236,8 @@ def main():
     model = models.to_b200_layout(model.to(dev), torch.bfloat16)
     model.train()
     opt = FusedSGD(model.parameters(), lr=0.01 * np_, momentum=args.momentum)
-    opt = kf.optimizers.SynchronousSGDOptimizer(opt, named_parameters=model.named_parameters())
+    opt = kf.optimizers.SynchronousSGDOptimizer(opt, named_parameters=model.named_parameters(),
+                                                overlap=bool(args.overlap))
     opt.arenas()  # move the parameters into symmetric memory before anything captures their addresses
     kf.broadcast_parameters(model.state_dict())
 
@@ -164,6 +262,7 @@ def main():
     torch.cuda.synchronize()
 
     launches_per_step = None
+    graph_holder = []
     if args.no_graph:
         run_step = train_step
     else:
@@ -180,6 +279,7 @@ def main():
         with torch.cuda.graph(graph):
             train_step()
         launches_per_step = K.launch_count - before
+        graph_holder.append(graph)
         run_step = graph.replay
         for _ in range(max(0, args.warmup - 3) + 3):
             run_step()
@@ -252,6 +352,15 @@ def main():
                'd2h_bytes_per_step': loss_host.element_size(), 'ms_per_step': e2e_ms / args.steps,
                'loss': float(loss_host)}
 
+    check = correctness_check(kf, K, opt, dev, rank, np_)
+    baseline = None
+    if args.same_box_baseline == 'ddp':
+        del graph_holder[:]
+        try:
+            baseline = ddp_baseline(args, kf, dev, rank, np_, local_rank)
+        except Exception as e:  # never lose the bench line to the comparison arm
+            baseline = {'impl': 'torch DDP (NCCL)', 'error': '%s: %s' % (type(e).__name__, str(e)[:200])}
+
     if rank == 0:
         out = {
             'metric': 'ResNet-50 S-SGD training throughput',
@@ -261,9 +370,12 @@ def main():
             'config': {'model': args.model, 'global_batch': B * np_, 'per_gpu_batch': B, 'seq_len': None,
                        'image_size': S, 'parallelism': 'dp%d' % np_, 'optimizer': 'SynchronousSGDOptimizer(FusedSGD)',
                        'cuda_graph': not args.no_graph, 'fused_bn': bool(args.fused_bn), 's2d_stem': bool(args.s2d_stem),
+                       'overlap': bool(args.overlap), 'buckets': len(opt._ov['buckets']) if opt._ov else 1,
+                       'fused_step': opt.last_algo,
                        'l2': 'working set per step (activations, bs%d) exceeds the 126 MB L2' % B,
                        'baseline': 'KungFu S-SGD ResNet-50 global batch 4096 on 16xV100 = 5507 img/s'},
             'clocks': clocks, 'e2e': e2e, 'gpu_launches': gpu_launches, 'loss': float(loss_dev),
+            'check': check, 'same_box_baseline': baseline, 'vs_baseline_note': BASELINE_NOTE,
         }
         print(json.dumps(out))
     kf.run_barrier()

@@ -52,6 +52,7 @@ struct Driver {
                                  unsigned long long);
     CUresult (*MulticastGetGranularity)(size_t *, const CUmulticastObjectProp *,
                                         CUmulticastGranularity_flags);
+    CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t);
     CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice);
     CUresult (*GetErrorString)(CUresult, const char **);
 };
@@ -92,6 +93,7 @@ const Driver *driver()
         load_sym("cuMulticastAddDevice", &d.MulticastAddDevice);
         load_sym("cuMulticastBindMem", &d.MulticastBindMem);
         load_sym("cuMulticastGetGranularity", &d.MulticastGetGranularity);
+        load_sym("cuMulticastUnbind", &d.MulticastUnbind);
         d.ok = ok;
     });
     return g_drv.ok ? &g_drv : nullptr;
@@ -428,6 +430,8 @@ extern "C" int kfb_mc_free(kfb_mc_object *mc)
         if (mc->mapped) {
             d->MemUnmap(mc->va, mc->bytes);
             d->MemAddressFree(mc->va, mc->bytes);
+            // give this device's physical pages back to the switch group before the handle goes
+            if (d->MulticastUnbind) d->MulticastUnbind(mc->handle, mc->device, 0, mc->bytes);
         }
         d->MemRelease(mc->handle);
     }

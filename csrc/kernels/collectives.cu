@@ -513,8 +513,8 @@ __global__ void __launch_bounds__(512)
     const int np   = a.np;
     uint32_t *epoch =
         a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
-    if (threadIdx.x == 0 && blockIdx.x == 0)
-        agree_out[a.rank < 0 ? rank : 0] = 1;
+    // agree_out holds 1 on entry (set by a launch of its own, kfb_consensus):
+    // CTAs only ever clear it, so no CTA's verdict can be overwritten.
     peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
     const long long stride = (long long)gridDim.x * blockDim.x;
     const uint4 *mine = reinterpret_cast<const uint4 *>(a.in_peers[rank]);
@@ -531,6 +531,11 @@ __global__ void __launch_bounds__(512)
     if (__syncthreads_or(differ) && threadIdx.x == 0)
         atomicAnd(agree_out + (a.rank < 0 ? rank : 0), 0);
     peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+}
+
+__global__ void k_set_i32(int32_t *p, int n, int32_t v)
+{
+    if ((int)threadIdx.x < n) p[threadIdx.x] = v;
 }
 
 // ---- single-edge kernels for the strategy-graph executor (K8) ---------------
@@ -669,10 +674,8 @@ extern "C" int kfb_device_info(int device, int *sm_count, int *cc_major,
     if (cc_major) *cc_major = p.major;
     if (cc_minor) *cc_minor = p.minor;
     if (multicast_supported) {
-        int v = 0;
-        // cudaDevAttrReserved / driver attribute 132 = MULTICAST_SUPPORTED;
-        // queried through the driver in symm.cu; here report "unknown" as 0.
-        *multicast_supported = v;
+        // CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, asked of the driver (symm.cu)
+        *multicast_supported = kfb_multicast_supported(device);
     }
     return KFB_OK;
 }
@@ -891,6 +894,8 @@ extern "C" int kfb_consensus(const kfb_comm *comm, void *const *in,
     MoveArgs m;
     fill_move(m, comm, bytes);
     for (int r = 0; r < comm->np; ++r) m.in_peers[r] = in[r];
+    k_set_i32<<<1, KFB_MAX_RANKS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(agree_out, comm->rank < 0 ? comm->np : 1, 1);
+    KFB_CUDA_OK(cudaGetLastError());
     return launch(comm, k_consensus, blocks, threads,
                   reinterpret_cast<cudaStream_t>(stream), m, agree_out);
 }

@@ -73,32 +73,101 @@ template <> struct Pk8<__half> {
 struct SgdH {
     float lr, momentum, dampening, wd;
     int nesterov, first;
+    // kind 0: torch.optim.SGD. kind 1: torch.optim.AdamW (decoupled decay),
+    // kind 2: torch.optim.Adam (L2 decay folded into the gradient).
+    int kind;
+    float beta1, beta2, eps;
+    float bc1, bc2;         // bias corrections when `step` is NULL
+    const long long *step;  // device scalar: completed steps (t = *step + 1)
+    float *v;               // Adam second moment, same indexing as the momentum
 };
 
-// torch.optim.SGD update on 8 lanes; p/m are fp32 master and momentum.
-__device__ __forceinline__ void
-sgd_update8(float *p, float *m, const float *g, const SgdH &h)
+// Adam's bias corrections are a function of the step number. Reading the
+// number from device memory keeps a captured CUDA graph valid from one replay
+// to the next (the caller advances *step once per training step).
+struct Bias {
+    float c1, rs2;  // 1 - beta1^t, 1/sqrt(1 - beta2^t)
+};
+__device__ __forceinline__ Bias opt_bias(const SgdH &h)
 {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        float d = fmaf(h.wd, p[k], g[k]);
-        if (h.momentum != 0.f) {
-            m[k] = h.first ? d : fmaf(h.momentum, m[k], (1.f - h.dampening) * d);
-            d    = h.nesterov ? fmaf(h.momentum, m[k], d) : m[k];
+    Bias b;
+    b.c1 = 1.f, b.rs2 = 1.f;
+    if (h.kind != 0) {
+        float c1 = h.bc1, c2 = h.bc2;
+        if (h.step) {
+            const float t = (float)(*h.step + 1);
+            c1 = 1.f - powf(h.beta1, t);
+            c2 = 1.f - powf(h.beta2, t);
         }
-        p[k] = fmaf(-h.lr, d, p[k]);
+        b.c1  = c1;
+        b.rs2 = rsqrtf(c2);
     }
+    return b;
+}
+
+// One update on 8 lanes; p/m/v are the fp32 master weights and optimizer slots.
+__device__ __forceinline__ void
+opt_update8(float *p, float *m, float *v, const float *g, const SgdH &h, const Bias &b)
+{
+    if (h.kind == 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float d = fmaf(h.wd, p[k], g[k]);
+            if (h.momentum != 0.f) {
+                m[k] = h.first ? d : fmaf(h.momentum, m[k], (1.f - h.dampening) * d);
+                d    = h.nesterov ? fmaf(h.momentum, m[k], d) : m[k];
+            }
+            p[k] = fmaf(-h.lr, d, p[k]);
+        }
+    } else {
+        const float step_size = h.lr / b.c1;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float gk = g[k];
+            if (h.kind == 1) p[k] *= 1.f - h.lr * h.wd;
+            else gk = fmaf(h.wd, p[k], gk);
+            m[k]            = fmaf(h.beta1, m[k], (1.f - h.beta1) * gk);
+            v[k]            = fmaf(h.beta2, v[k], (1.f - h.beta2) * gk * gk);
+            const float den = fmaf(sqrtf(v[k]), b.rs2, h.eps);
+            p[k]            = fmaf(-step_size, m[k] / den, p[k]);
+        }
+    }
+}
+
+// Which optimizer slots a packet update reads and writes.
+__device__ __forceinline__ bool opt_loads_m(const SgdH &h) { return h.kind != 0 || (h.momentum != 0.f && !h.first); }
+__device__ __forceinline__ bool opt_stores_m(const SgdH &h) { return h.kind != 0 || h.momentum != 0.f; }
+
+__device__ __forceinline__ void
+slots_load(const SgdH &h, const float *mom, const float *v2, long long i, float *m, float *v)
+{
+    if (opt_loads_m(h)) Pk8<float>::load(mom, i, m);
+    if (h.kind != 0) Pk8<float>::load(v2, i, v);
+}
+__device__ __forceinline__ void
+slots_store(const SgdH &h, float *mom, float *v2, long long i, const float *m, const float *v)
+{
+    if (opt_stores_m(h)) Pk8<float>::store(mom, i, m);
+    if (h.kind != 0) Pk8<float>::store(v2, i, v);
 }
 
 static SgdH to_h(const kfb_sgd_hyper *h)
 {
     SgdH r;
-    r.lr       = h->lr;
-    r.momentum = h->momentum;
+    r.lr        = h->lr;
+    r.momentum  = h->momentum;
     r.dampening = h->dampening;
-    r.wd       = h->weight_decay;
-    r.nesterov = h->nesterov;
-    r.first    = h->first_step;
+    r.wd        = h->weight_decay;
+    r.nesterov  = h->nesterov;
+    r.first     = h->first_step;
+    r.kind      = h->kind;
+    r.beta1     = h->beta1;
+    r.beta2     = h->beta2;
+    r.eps       = h->eps;
+    r.bc1       = h->bias_corr1;
+    r.bc2       = h->bias_corr2;
+    r.step      = reinterpret_cast<const long long *>(h->step);
+    r.v         = h->exp_avg_sq;
     return r;
 }
 
@@ -237,6 +306,8 @@ __global__ void __launch_bounds__(512)
     // emulation: each emulated rank has its own master/momentum copy
     float *master = a.master + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
     float *mom    = a.mom + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    float *mom2   = a.h.v ? a.h.v + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0) : nullptr;
+    const Bias bias = opt_bias(a.h);
     __shared__ float red[32];
 
     if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
@@ -267,17 +338,17 @@ __global__ void __launch_bounds__(512)
                 for (int k = 0; k < 8; ++k) g[k] += t[k];
             }
         }
-        float p[8], m[8];
+        float p[8], m[8], v[8];
         Pk8<float>::load(master, i, p);
-        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(mom, i, m);
+        slots_load(a.h, mom, mom2, i, m, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             g[k] *= a.grad_scale;
             if (NORM) ss = fmaf(g[k], g[k], ss);
         }
-        sgd_update8(p, m, g, a.h);
+        opt_update8(p, m, v, g, a.h, bias);
         Pk8<float>::store(master, i, p);
-        if (a.h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+        slots_store(a.h, mom, mom2, i, m, v);
         for (int k = 0; k < np; ++k) Pk8<P>::store(a.params[(rank + k) % np], i, p);
     }
     if (NORM) {
@@ -363,6 +434,7 @@ __global__ void __launch_bounds__(512)
     k_ssgd_fused_nvls(const __grid_constant__ StepArgs a)
 {
     const int rank = a.rank, np = a.np;
+    const Bias bias = opt_bias(a.h);
     __shared__ float red[32];
     peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
     const long long per    = (a.npk + np - 1) / np;
@@ -373,18 +445,18 @@ __global__ void __launch_bounds__(512)
     void *mc_p             = a.stage[1];
     float ss               = 0.f;
     for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
-        float g[8], p[8], m[8];
+        float g[8], p[8], m[8], v[8];
         Mc8<G>::ld_reduce(mc_g, i, g);
         Pk8<float>::load(a.master, i, p);
-        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(a.mom, i, m);
+        slots_load(a.h, a.mom, a.h.v, i, m, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             g[k] *= a.grad_scale;
             if (NORM) ss = fmaf(g[k], g[k], ss);
         }
-        sgd_update8(p, m, g, a.h);
+        opt_update8(p, m, v, g, a.h, bias);
         Pk8<float>::store(a.master, i, p);
-        if (a.h.momentum != 0.f) Pk8<float>::store(a.mom, i, m);
+        slots_store(a.h, a.mom, a.h.v, i, m, v);
         Mc8<P>::st(mc_p, i, p);
     }
     if (NORM) {
@@ -425,23 +497,31 @@ __global__ void __launch_bounds__(512)
                long long npk, float grad_scale, SgdH h)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
+    const Bias bias        = opt_bias(h);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
          i < npk; i += stride) {
-        float g[8], p[8], m[8];
+        float g[8], p[8], m[8], v[8];
         Pk8<G>::load(grad, i, g);
         Pk8<float>::load(master, i, p);
-        if (h.momentum != 0.f && !h.first) Pk8<float>::load(mom, i, m);
+        slots_load(h, mom, h.v, i, m, v);
 #pragma unroll
         for (int k = 0; k < 8; ++k) g[k] *= grad_scale;
-        sgd_update8(p, m, g, h);
+        opt_update8(p, m, v, g, h, bias);
         Pk8<float>::store(master, i, p);
-        if (h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+        slots_store(h, mom, h.v, i, m, v);
         if (param != (void *)master) Pk8<P>::store(param, i, p);
     }
 }
 
 // ---- SMA fused step -------------------------------------------------------------------
-template <typename G, typename P>
+// NVLS == true: the switch sums the parameter shard (multimem.ld_reduce on the
+// multicast alias a.stage[KFB_MAX_RANKS-2]) and multicasts the fp32 average
+// into every rank's staging buffer (multimem.st on a.stage[KFB_MAX_RANKS-1]),
+// so the NVLink leg moves ~1x the model instead of 2(n-1)/n x.
+// PHASE: 0 = everything, 1 = average only (can run while forward/backward of
+// this step are still executing: parameters are only read), 2 = blend + update
+// only (purely local).
+template <typename G, typename P, bool NVLS, int PHASE>
 __global__ void __launch_bounds__(512)
     k_sma_fused(const __grid_constant__ StepArgs a)
 {
@@ -451,13 +531,15 @@ __global__ void __launch_bounds__(512)
         a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
     float *master = a.master + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
     float *mom    = a.mom + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0);
+    float *mom2   = a.h.v ? a.h.v + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0) : nullptr;
     const void *grad =
         a.rank < 0 ? a.grads[rank] : a.grad_local;  // LOCAL gradient
     const long long per    = (a.npk + np - 1) / np;
     const long long stride = (long long)gridDim.x * blockDim.x;
     const float inv_np     = 1.f / (float)np;
+    const Bias bias        = opt_bias(a.h);
 
-    if (np > 1) {
+    if (np > 1 && PHASE != 2) {
         // phase 1: average my shard of everybody's parameters, push to all
         peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
         const long long lo = (long long)rank * per;
@@ -465,30 +547,41 @@ __global__ void __launch_bounds__(512)
         for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
              i < hi; i += stride) {
             float s[8];
-            Pk8<P>::load(a.params[0], i, s);
-            for (int r = 1; r < np; ++r) {
-                float t[8];
-                Pk8<P>::load(a.params[r], i, t);
+            if (NVLS) {
+                Mc8<P>::ld_reduce(a.stage[KFB_MAX_RANKS - 2], i, s);
+            } else {
+                Pk8<P>::load(a.params[0], i, s);
+                for (int r = 1; r < np; ++r) {
+                    float t[8];
+                    Pk8<P>::load(a.params[r], i, t);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) s[k] += t[k];
+                    for (int k = 0; k < 8; ++k) s[k] += t[k];
+                }
             }
 #pragma unroll
             for (int k = 0; k < 8; ++k) s[k] *= inv_np;
-            for (int k = 0; k < np; ++k)
-                Pk8<float>::store(a.stage[(rank + k) % np], i, s);
+            if (NVLS) {
+                Mc8<float>::st(a.stage[KFB_MAX_RANKS - 1], i, s);
+            } else {
+                for (int k = 0; k < np; ++k)
+                    Pk8<float>::store(a.stage[(rank + k) % np], i, s);
+            }
         }
         // CTA b of every rank has now (1) read the slice of my parameters it
         // needs and (2) delivered its slice of the average to me.
         peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
     }
-    // phase 2: blend + local SGD over exactly the packets CTA b of each rank
-    // touched in phase 1 (same grid-stride pattern inside every shard).
+    if (PHASE == 1) return;
+    // phase 2: blend + local update. In the single-launch form every CTA only
+    // touches the packets CTA b of each rank delivered in phase 1 (same
+    // grid-stride pattern inside every shard); as a launch of its own it may
+    // have any grid, the averages are complete before it starts.
     for (int s_ = 0; s_ < np; ++s_) {
         const long long lo = (long long)s_ * per;
         const long long hi = min(lo + per, a.npk);
         for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
              i < hi; i += stride) {
-            float p[8], m[8], g[8];
+            float p[8], m[8], v[8], g[8];
             Pk8<float>::load(master, i, p);
             if (np > 1) {
                 float avg[8];
@@ -498,12 +591,12 @@ __global__ void __launch_bounds__(512)
                     p[k] = fmaf(a.alpha, avg[k] - p[k], p[k]);
             }
             Pk8<G>::load(grad, i, g);
-            if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(mom, i, m);
+            slots_load(a.h, mom, mom2, i, m, v);
 #pragma unroll
             for (int k = 0; k < 8; ++k) g[k] *= a.grad_scale;
-            sgd_update8(p, m, g, a.h);
+            opt_update8(p, m, v, g, a.h, bias);
             Pk8<float>::store(master, i, p);
-            if (a.h.momentum != 0.f) Pk8<float>::store(mom, i, m);
+            slots_store(a.h, mom, mom2, i, m, v);
             Pk8<P>::store(a.params[rank], i, p);
         }
     }
@@ -536,7 +629,16 @@ struct PairArgs {
     const void *snap_all[KFB_MAX_RANKS];
 };
 
-template <typename G, typename P>
+// Snapshot protocol (per rank, words in its signal pad):
+//   seq  number of published versions; version k lives in slot (k & 1)
+//   wb   the version the owner is writing right now ("write begin")
+// The owner stores wb = seq + 1, fences, writes slot ((seq + 1) & 1), fences,
+// stores seq + 1 (release). A reader takes k = seq (acquire), reads slot
+// (k & 1), then re-reads wb (acquire): the slot it read is recycled by
+// version k + 2, so wb >= k + 2 means the copy may mix two versions. The
+// reference tolerates such reads silently (store/blob.go:20-26 copies without
+// a write lock); here they are counted in torn_out, without false negatives.
+template <typename G, typename P, bool UPDATE>
 __global__ void __launch_bounds__(512)
     k_pair_avg(const __grid_constant__ PairArgs a)
 {
@@ -562,6 +664,11 @@ __global__ void __launch_bounds__(512)
         s_snap_peer = snap_peer;
         s_k         = a.has_peer ? ld_acquire_sys(seq_peer) : 0u;
         s_self      = ld_relaxed_sys(a.seq_self);
+        if (UPDATE) {
+            // announce the version about to be written before any CTA touches its slot
+            st_release_sys(a.seq_self + 1, s_self + 1);
+            __threadfence_system();
+        }
     }
     __syncthreads();
     const uint32_t k = s_k, kself = s_self;
@@ -570,28 +677,32 @@ __global__ void __launch_bounds__(512)
     char *mine =
         reinterpret_cast<char *>(a.snap_self) + ((kself + 1) & 1) * a.slot_bytes;
     const long long stride = (long long)gridDim.x * blockDim.x;
+    const Bias bias        = opt_bias(a.h);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
          i < a.npk; i += stride) {
-        float p[8], m[8], g[8];
-        Pk8<float>::load(a.master, i, p);
+        float p[8], m[8], v[8], g[8];
+        if (UPDATE) Pk8<float>::load(a.master, i, p);
+        else Pk8<P>::load(a.param, i, p);
         if (k != 0) {  // peer has published at least once
             float o[8];
             Pk8<P>::load(peer, i, o);
 #pragma unroll
             for (int j = 0; j < 8; ++j) p[j] = 0.5f * (p[j] + o[j]);
         }
-        Pk8<G>::load(a.grad, i, g);
-        if (a.h.momentum != 0.f && !a.h.first) Pk8<float>::load(a.mom, i, m);
+        if (UPDATE) {
+            Pk8<G>::load(a.grad, i, g);
+            slots_load(a.h, a.mom, a.h.v, i, m, v);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] *= a.grad_scale;
-        sgd_update8(p, m, g, a.h);
-        Pk8<float>::store(a.master, i, p);
-        if (a.h.momentum != 0.f) Pk8<float>::store(a.mom, i, m);
+            for (int j = 0; j < 8; ++j) g[j] *= a.grad_scale;
+            opt_update8(p, m, v, g, a.h, bias);
+            Pk8<float>::store(a.master, i, p);
+            slots_store(a.h, a.mom, a.h.v, i, m, v);
+            Pk8<P>::store(mine, i, p);
+        }
         Pk8<P>::store(a.param, i, p);
-        Pk8<P>::store(mine, i, p);
     }
-    // The last CTA to finish publishes the new version; it also checks whether
-    // the slot we read was recycled underneath us (peer advanced >= 2).
+    // The last CTA to finish publishes the new version and checks whether the
+    // slot we read was being recycled underneath us.
     __shared__ bool is_last;
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -602,10 +713,10 @@ __global__ void __launch_bounds__(512)
         if (is_last) {
             *ticket = 0u;
             __threadfence_system();
-            st_release_sys(a.seq_self, kself + 1);
+            if (UPDATE) st_release_sys(a.seq_self, kself + 1);
             if (a.has_peer && a.torn_out && k != 0) {
-                const uint32_t k2 = ld_acquire_sys(s_seq_peer);
-                if (k2 - k >= 2u) atomicAdd(a.torn_out, 1);
+                const uint32_t wb = ld_acquire_sys(s_seq_peer + 1);
+                if ((int32_t)(wb - k) >= 2) atomicAdd(a.torn_out, 1);
             }
         }
     }
@@ -616,7 +727,11 @@ __global__ void __launch_bounds__(512)
                    long long slot_bytes, long long nvec, float *scratch)
 {
     __shared__ uint32_t s_self;
-    if (threadIdx.x == 0) s_self = ld_relaxed_sys(seq_self);
+    if (threadIdx.x == 0) {
+        s_self = ld_relaxed_sys(seq_self);
+        st_release_sys(seq_self + 1, s_self + 1);
+        __threadfence_system();
+    }
     __syncthreads();
     const uint32_t kself = s_self;
     uint4 *mine = reinterpret_cast<uint4 *>(snap_self + ((kself + 1) & 1) * slot_bytes);
@@ -637,6 +752,39 @@ __global__ void __launch_bounds__(512)
     }
 }
 
+// Byte copy of the target's current snapshot into a local buffer, with the same
+// version check as k_pair_avg (models of several dtypes: pull once, blend per
+// dtype afterwards). *got_out := 1 if the peer had published anything.
+__global__ void __launch_bounds__(512)
+    k_pair_pull(uint32_t *seq_peer, const char *snap_peer, long long slot_bytes, uint4 *dst, long long nvec,
+                float *scratch, int32_t *torn_out, int32_t *got_out)
+{
+    __shared__ uint32_t s_k;
+    if (threadIdx.x == 0) s_k = ld_acquire_sys(seq_peer);
+    __syncthreads();
+    const uint32_t k = s_k;
+    if (k != 0) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(snap_peer + (k & 1) * slot_bytes);
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride)
+            st_stream16(dst + i, ld_stream16(src + i));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        unsigned int *ticket = reinterpret_cast<unsigned int *>(scratch + KFB_MAX_BLOCKS + 1);
+        if (atomicAdd(ticket, 1u) == gridDim.x - 1) {
+            *ticket = 0u;
+            __threadfence_system();
+            if (got_out) *got_out = k != 0;
+            if (torn_out && k != 0) {
+                const uint32_t wb = ld_acquire_sys(seq_peer + 1);
+                if ((int32_t)(wb - k) >= 2) atomicAdd(torn_out, 1);
+            }
+        }
+    }
+}
+
 // ---- gradient variance -----------------------------------------------------------------
 struct VarArgs {
     PeerPads pads;
@@ -645,10 +793,18 @@ struct VarArgs {
     const long long *seg_ends;  // device, cumulative element offsets
     int n_seg;
     float *seg_out;  // device float[n_seg]: this rank's partial sum of v^2
+    float *work;     // device: per block {edge value x2, edge segment x2}, then a ticket
     long long npk;
     int rank, np;
 };
 
+
+// No atomics on the sums: the rank's shard is cut into one contiguous range
+// per CTA; inside its range a CTA walks the tensors (segments) in order and
+// reduces each with the fixed block tree. A tensor that lies inside one CTA's
+// range is written directly; a tensor that spans CTAs leaves one partial per
+// CTA in `work`, and the last CTA to finish adds those in CTA order. The
+// result is therefore bit-identical from run to run.
 template <typename G>
 __global__ void __launch_bounds__(512)
     k_grad_variance(const __grid_constant__ VarArgs a)
@@ -658,43 +814,103 @@ __global__ void __launch_bounds__(512)
     uint32_t *epoch =
         a.local_epoch + (a.rank < 0 ? rank * KFB_STATE_EPOCH_WORDS : 0);
     float *seg_out = a.seg_out + (a.rank < 0 ? rank * a.n_seg : 0);
+    float *work    = a.work + (a.rank < 0 ? rank * KFB_VAR_WORK_WORDS : 0);
+    __shared__ float red[32];
     if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
-    const long long per    = (a.npk + np - 1) / np;
-    const long long lo     = (long long)rank * per;
-    const long long hi     = min(lo + per, a.npk);
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    const float inv_np     = 1.f / (float)np;
-    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x;
-         i < hi; i += stride) {
-        float s1[8], s2[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-        for (int r = 0; r < np; ++r) {
-            float t[8];
-            Pk8<G>::load(a.grads[r], i, t);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                s1[k] += t[k];
-                s2[k] = fmaf(t[k], t[k], s2[k]);
+    const long long per = (a.npk + np - 1) / np;
+    const long long lo  = min((long long)rank * per, a.npk);
+    const long long hi  = min(lo + per, a.npk);
+    const long long G_  = gridDim.x;
+    const long long pb  = (hi - lo + G_ - 1) / G_;  // packets per CTA
+    const long long blo = min(lo + (long long)blockIdx.x * pb, hi);
+    const long long bhi = min(blo + pb, hi);
+    const float inv_np  = 1.f / (float)np;
+    float edge_val[2]   = {0.f, 0.f};
+    int edge_seg[2]     = {-1, -1};
+    if (blo < bhi) {
+        // first segment whose end lies beyond the first element of the range
+        int sgm = 0;
+        {
+            const long long e = blo * 8;
+            int l = 0, h = a.n_seg - 1;
+            while (l < h) {
+                const int mid = (l + h) >> 1;
+                if (a.seg_ends[mid] > e) h = mid;
+                else l = mid + 1;
             }
+            sgm = l;
         }
-        float acc = 0.f;
+        long long cur = blo;
+        while (cur < bhi) {
+            const long long seg_lo = sgm == 0 ? 0 : a.seg_ends[sgm - 1] / 8;
+            const long long seg_hi = a.seg_ends[sgm] / 8;
+            const long long end    = min(bhi, seg_hi);
+            float acc              = 0.f;
+            for (long long i = cur + threadIdx.x; i < end; i += blockDim.x) {
+                float s1[8], s2[8];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float mean = s1[k] * inv_np;
-            const float v    = s2[k] * inv_np - mean * mean;
-            acc              = fmaf(v, v, acc);
+                for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+                for (int r = 0; r < np; ++r) {
+                    float t[8];
+                    Pk8<G>::load(a.grads[r], i, t);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        s1[k] += t[k];
+                        s2[k] = fmaf(t[k], t[k], s2[k]);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float mean = s1[k] * inv_np;
+                    const float v    = s2[k] * inv_np - mean * mean;
+                    acc              = fmaf(v, v, acc);
+                }
+            }
+            const float tot = block_sum(acc, red);
+            // does this CTA see all of the tensor's packets that this rank owns?
+            const bool whole = max(seg_lo, lo) >= blo && min(seg_hi, hi) <= bhi;
+            if (threadIdx.x == 0) {
+                if (whole) seg_out[sgm] = tot;
+                else {
+                    const int slot = (edge_seg[0] < 0) ? 0 : 1;
+                    edge_val[slot] = tot;
+                    edge_seg[slot] = sgm;
+                }
+            }
+            cur = end;
+            if (++sgm >= a.n_seg) break;
         }
-        // segment of this packet: first seg whose end > element index
-        const long long e = i * 8;
-        int l = 0, h = a.n_seg - 1;
-        while (l < h) {
-            const int mid = (l + h) >> 1;
-            if (a.seg_ends[mid] > e) h = mid;
-            else l = mid + 1;
-        }
-        atomicAdd(seg_out + l, acc);
     }
+    __shared__ bool is_last;
+    if (threadIdx.x == 0) {
+        work[4 * blockIdx.x + 0] = edge_val[0];
+        work[4 * blockIdx.x + 1] = edge_val[1];
+        reinterpret_cast<int *>(work)[4 * blockIdx.x + 2] = edge_seg[0];
+        reinterpret_cast<int *>(work)[4 * blockIdx.x + 3] = edge_seg[1];
+        __threadfence();
+        unsigned int *ticket = reinterpret_cast<unsigned int *>(work + 4 * KFB_MAX_BLOCKS);
+        is_last              = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+        if (is_last) {
+            *ticket = 0u;
+            __threadfence();
+            int open_seg   = -1;
+            float open_sum = 0.f;
+            for (unsigned b = 0; b < gridDim.x; ++b)
+                for (int sl = 0; sl < 2; ++sl) {
+                    const int sg = *reinterpret_cast<volatile int *>(reinterpret_cast<int *>(work) + 4 * b + 2 + sl);
+                    if (sg < 0) continue;
+                    const float val = *reinterpret_cast<volatile float *>(work + 4 * b + sl);
+                    if (sg != open_seg) {
+                        if (open_seg >= 0) seg_out[open_seg] = open_sum;
+                        open_seg = sg;
+                        open_sum = 0.f;
+                    }
+                    open_sum += val;
+                }
+            if (open_seg >= 0) seg_out[open_seg] = open_sum;
+        }
+    }
+    __syncthreads();
     if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
 }
 
@@ -822,6 +1038,17 @@ extern "C" int kfb_fuse(void *const *srcs, const int64_t *counts,
         }
         first = false;
     }
+    return KFB_OK;
+}
+
+extern "C" int kfb_sum_slots(const float *slots, int n, float *out, void *stream)
+{
+    if (n < 0 || !slots || !out) {
+        set_last_error("kfb_sum_slots: bad arguments");
+        return KFB_ERR_ARG;
+    }
+    k_sum_slots<<<1, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(slots, n, out, 0);
+    KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
 
@@ -1042,16 +1269,22 @@ extern "C" int kfb_sgd_flat(const void *grad, int grad_dtype, void *param,
     return KFB_OK;
 }
 
-extern "C" int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
-                                  int param_dtype, void *const *avg_stage,
-                                  const void *grad, int grad_dtype,
-                                  float *master, float *mom, int64_t count,
-                                  float alpha, float grad_scale,
-                                  const kfb_sgd_hyper *h, int blocks,
-                                  int threads, void *stream)
+extern "C" int kfb_sma_fused_step_ex(const kfb_comm *comm, void *const *params,
+                                     int param_dtype, void *const *avg_stage,
+                                     void *mc_params, void *mc_stage,
+                                     const void *grad, int grad_dtype,
+                                     float *master, float *mom, int64_t count,
+                                     float alpha, float grad_scale,
+                                     const kfb_sgd_hyper *h, int phase,
+                                     int blocks, int threads, void *stream)
 {
     int rc = check_launch(comm, blocks, threads);
     if (rc) return rc;
+    if (phase < 0 || phase > 2) {
+        set_last_error("kfb_sma_fused_step_ex: phase must be 0 (all), 1 (average) or 2 (update)");
+        return KFB_ERR_ARG;
+    }
+    const bool nvls = mc_params && mc_stage && comm->np > 1 && comm->rank >= 0 && phase != 2;
     StepArgs a;
     rc = fill_step(a, comm, count);
     if (rc) return rc;
@@ -1059,8 +1292,16 @@ extern "C" int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
         a.params[r] = params[r];
         a.stage[r]  = avg_stage ? avg_stage[r] : nullptr;
         // emulation: `grad` is a host array of np device pointers
-        if (comm->rank < 0)
+        if (comm->rank < 0 && grad)
             a.grads[r] = reinterpret_cast<void *const *>(grad)[r];
+    }
+    if (nvls) {
+        if (comm->np > KFB_MAX_RANKS - 2) {
+            set_last_error("NVLS SMA supports at most %d ranks", KFB_MAX_RANKS - 2);
+            return KFB_ERR_ARG;
+        }
+        a.stage[KFB_MAX_RANKS - 2] = mc_params;
+        a.stage[KFB_MAX_RANKS - 1] = mc_stage;
     }
     a.grad_local = grad;
     a.master     = master;
@@ -1069,9 +1310,62 @@ extern "C" int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
     a.grad_scale = grad_scale;
     a.h          = to_h(h);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define KFB_SMA(NV, PH) return launch_step(comm, k_sma_fused<G, P, NV, PH>, blocks, threads, s, a)
     KFB_DISPATCH_FLOAT(grad_dtype, G,
-        KFB_DISPATCH_FLOAT(param_dtype, P,
-            return launch_step(comm, k_sma_fused<G, P>, blocks, threads, s, a)));
+        KFB_DISPATCH_FLOAT(param_dtype, P, {
+            if (phase == 2) KFB_SMA(false, 2);
+            if (nvls) {
+                if (phase == 0) KFB_SMA(true, 0);
+                KFB_SMA(true, 1);
+            }
+            if (phase == 0) KFB_SMA(false, 0);
+            KFB_SMA(false, 1);
+        }));
+#undef KFB_SMA
+    return KFB_OK;
+}
+
+extern "C" int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
+                                  int param_dtype, void *const *avg_stage,
+                                  const void *grad, int grad_dtype,
+                                  float *master, float *mom, int64_t count,
+                                  float alpha, float grad_scale,
+                                  const kfb_sgd_hyper *h, int blocks,
+                                  int threads, void *stream)
+{
+    return kfb_sma_fused_step_ex(comm, params, param_dtype, avg_stage, nullptr, nullptr, grad, grad_dtype, master,
+                                 mom, count, alpha, grad_scale, h, 0, blocks, threads, stream);
+}
+
+// Pull + 1/2 blend only (no optimizer update, no publication): the device
+// path of PairAveraging around an arbitrary torch optimizer.
+extern "C" int kfb_pair_blend(const kfb_comm *comm, int target, const void *snap_peer, int64_t slot_bytes,
+                              void *param, int param_dtype, int64_t count, int32_t *torn_out, int blocks,
+                              int threads, void *stream)
+{
+    if (!comm || comm->rank < 0 || comm->rank >= comm->np) {
+        set_last_error("pair averaging needs a real rank");
+        return KFB_ERR_ARG;
+    }
+    if (count % 8 || blocks < 1 || blocks > KFB_MAX_BLOCKS) {
+        set_last_error("bad count/blocks");
+        return KFB_ERR_ARG;
+    }
+    PairArgs a;
+    memset(&a, 0, sizeof(a));
+    a.has_peer = (target >= 0 && target < comm->np && target != comm->rank);
+    if (!a.has_peer) return KFB_OK;
+    a.seq_self   = reinterpret_cast<uint32_t *>(comm->pads[comm->rank]) + KFB_PAD_MISC_WORD;
+    a.seq_peer   = reinterpret_cast<uint32_t *>(comm->pads[target]) + KFB_PAD_MISC_WORD;
+    a.snap_peer  = snap_peer;
+    a.slot_bytes = slot_bytes;
+    a.param      = param;
+    a.scratch    = reinterpret_cast<float *>(comm->scratch);
+    a.npk        = count / 8;
+    a.torn_out   = torn_out;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    KFB_DISPATCH_FLOAT(param_dtype, P, (k_pair_avg<P, P, false><<<blocks, threads, 0, s>>>(a)));
+    KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
 
@@ -1113,7 +1407,7 @@ extern "C" int kfb_pair_avg_step(const kfb_comm *comm, int target,
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     KFB_DISPATCH_FLOAT(grad_dtype, G,
         KFB_DISPATCH_FLOAT(param_dtype, P,
-            (k_pair_avg<G, P><<<blocks, threads, 0, s>>>(a))));
+            (k_pair_avg<G, P, true><<<blocks, threads, 0, s>>>(a))));
     KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
@@ -1161,7 +1455,27 @@ extern "C" int kfb_pair_avg_step_dev(const kfb_comm *comm, void *const *snaps, i
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     KFB_DISPATCH_FLOAT(grad_dtype, G,
         KFB_DISPATCH_FLOAT(param_dtype, P,
-            (k_pair_avg<G, P><<<blocks, threads, 0, s>>>(a))));
+            (k_pair_avg<G, P, true><<<blocks, threads, 0, s>>>(a))));
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+extern "C" int kfb_pair_pull(const kfb_comm *comm, int target, const void *snap_peer, int64_t slot_bytes, void *dst,
+                             int64_t bytes, int32_t *torn_out, int32_t *got_out, int blocks, int threads,
+                             void *stream)
+{
+    if (!comm || comm->rank < 0 || target < 0 || target >= comm->np || target == comm->rank) {
+        set_last_error("kfb_pair_pull: needs a real rank and another rank as target");
+        return KFB_ERR_ARG;
+    }
+    if (bytes % 16 || bytes > slot_bytes || blocks < 1 || blocks > KFB_MAX_BLOCKS) {
+        set_last_error("kfb_pair_pull: bytes must be a multiple of 16 and fit the slot");
+        return KFB_ERR_ARG;
+    }
+    uint32_t *seq = reinterpret_cast<uint32_t *>(comm->pads[target]) + KFB_PAD_MISC_WORD;
+    k_pair_pull<<<blocks, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        seq, reinterpret_cast<const char *>(snap_peer), slot_bytes, reinterpret_cast<uint4 *>(dst), bytes / 16,
+        reinterpret_cast<float *>(comm->scratch), torn_out, got_out);
     KFB_CUDA_OK(cudaGetLastError());
     return KFB_OK;
 }
@@ -1187,13 +1501,13 @@ extern "C" int kfb_pair_publish(const kfb_comm *comm, const void *param,
 extern "C" int kfb_grad_variance(const kfb_comm *comm, void *const *grads,
                                  int dtype, int64_t count,
                                  const int64_t *seg_ends_dev, int n_seg,
-                                 float *seg_out, int blocks, int threads,
-                                 void *stream)
+                                 float *seg_out, float *work, int blocks,
+                                 int threads, void *stream)
 {
     int rc = check_launch(comm, blocks, threads);
     if (rc) return rc;
-    if (count % 8 || n_seg < 1) {
-        set_last_error("bad count / n_seg");
+    if (count % 8 || n_seg < 1 || !work) {
+        set_last_error("bad count / n_seg / work");
         return KFB_ERR_ARG;
     }
     VarArgs a;
@@ -1204,6 +1518,7 @@ extern "C" int kfb_grad_variance(const kfb_comm *comm, void *const *grads,
     a.seg_ends = reinterpret_cast<const long long *>(seg_ends_dev);
     a.n_seg    = n_seg;
     a.seg_out  = seg_out;
+    a.work     = work;
     a.npk      = count / 8;
     a.rank     = comm->rank;
     a.np       = comm->np;

@@ -30,6 +30,7 @@ extern "C" {
 #define KFB_STATE_EPOCH_WORDS KFB_MAX_BLOCKS
 #define KFB_SCRATCH_FLOATS (KFB_MAX_BLOCKS + 8)
 #define KFB_FUSE_SCRATCH_FLOATS 1024
+#define KFB_VAR_WORK_WORDS (4 * KFB_MAX_BLOCKS + 8)
 
 enum kfb_error {
     KFB_OK          = 0,
@@ -158,6 +159,9 @@ int kfb_fuse(void *const *srcs, const int64_t *counts, const int64_t *dst_offs,
 int kfb_fuse_noalloc(void *const *srcs, const int64_t *counts,
                      const int64_t *dst_offs, int n, int src_dtype, void *dst,
                      int dst_dtype, float *sumsq_out, void *stream);
+/* out[0] = slots[0] + ... + slots[n-1], added in index order by one block:
+ * how per-bucket norm partials become one reproducible number (K17). */
+int kfb_sum_slots(const float *slots, int n, float *out, void *stream);
 /* Inverse: scatter flat buffer back into n tensors (cast dst_dtype<-src). */
 int kfb_defuse(const void *src, int src_dtype, void *const *dsts,
                const int64_t *counts, const int64_t *src_offs, int n,
@@ -172,6 +176,18 @@ typedef struct kfb_sgd_hyper {
     float weight_decay;
     int32_t nesterov;
     int32_t first_step; /* momentum buffer := grad (torch.optim.SGD rule) */
+    /* Update rule. 0: torch.optim.SGD (fields above). 1: torch.optim.AdamW
+     * (decoupled weight decay), 2: torch.optim.Adam (L2 decay). For 1 and 2
+     * the `mom` argument of the step functions is the first moment and
+     * exp_avg_sq the second (same layout); the step number t of the bias
+     * corrections 1 - beta^t is *step + 1 when `step` (a DEVICE int64 the
+     * caller advances once per training step; keeps a captured CUDA graph
+     * valid across replays) is given, otherwise bias_corr1/2 are used. */
+    int32_t kind;
+    float beta1, beta2, eps;
+    float bias_corr1, bias_corr2;
+    const void *step;
+    float *exp_avg_sq;
 } kfb_sgd_hyper;
 
 /* S-SGD fused step (K1+K14+optimizer): reduce-scatter the gradient shard over
@@ -216,13 +232,30 @@ int kfb_sma_fused_step(const kfb_comm *comm, void *const *params,
                        float grad_scale, const kfb_sgd_hyper *h, int blocks,
                        int threads, void *stream);
 
+/* The same step with two refinements (what the optimizer wrappers call):
+ *  - mc_params / mc_stage: multicast aliases of the parameter and staging
+ *    buffers; when both are given the switch does the averaging
+ *    (multimem.ld_reduce + multimem.st), moving ~1x the model per GPU;
+ *  - phase 1 runs only the averaging (it only READS parameters, so it may be
+ *    launched at the start of a step on a side stream and overlap forward and
+ *    backward), phase 2 only the blend + update (purely local); 0 = both. */
+int kfb_sma_fused_step_ex(const kfb_comm *comm, void *const *params,
+                          int param_dtype, void *const *avg_stage,
+                          void *mc_params, void *mc_stage, const void *grad,
+                          int grad_dtype, float *master, float *mom,
+                          int64_t count, float alpha, float grad_scale,
+                          const kfb_sgd_hyper *h, int phase, int blocks,
+                          int threads, void *stream);
+
 /* PairAveraging fused step (K16+K21): one-sided pull of the target peer's
  * published snapshot (seqlock + double buffer), v <- 0.5 (v + v_t), SGD with
  * the local gradient, publish own new snapshot. No barrier, no NCCL.
  * snap_peer: peer-mapped base of the target's 2-slot snapshot area
  * (2 * slot_bytes); snap_self: own area; seq words live in the pads.
- * torn_out (device int32, may be NULL) counts snapshots that were overwritten
- * while being read. (srcs/python/kungfu/tensorflow/optimizers/async_sgd.py:110-142) */
+ * torn_out (device int32, may be NULL) counts snapshots whose slot the owner
+ * had begun to overwrite before the read finished (the owner announces every
+ * write in a second pad word before touching the slot, so nothing is missed;
+ * such a blend is kept, as in the reference, and counted). (srcs/python/kungfu/tensorflow/optimizers/async_sgd.py:110-142) */
 int kfb_pair_avg_step(const kfb_comm *comm, int target, const void *snap_peer,
                       void *snap_self, int64_t slot_bytes, void *param,
                       int param_dtype, const void *grad, int grad_dtype,
@@ -242,6 +275,22 @@ int kfb_pair_avg_step_dev(const kfb_comm *comm, void *const *snaps,
                           const kfb_sgd_hyper *h, int32_t *torn_out,
                           const long long *step, unsigned long long seed,
                           int blocks, int threads, void *stream);
+/* Pull + blend only: param <- 0.5 (param + target's snapshot), no update and
+ * no publication. Device path of PairAveraging around any torch optimizer:
+ * kfb_pair_blend, the wrapped optimizer's own step, kfb_pair_publish.
+ * (async_sgd.py:130-133) */
+int kfb_pair_blend(const kfb_comm *comm, int target, const void *snap_peer,
+                   int64_t slot_bytes, void *param, int param_dtype,
+                   int64_t count, int32_t *torn_out, int blocks, int threads,
+                   void *stream);
+/* Copy the target's current snapshot (`bytes`, a multiple of 16) into the
+ * local buffer dst; *got_out (device int32, may be NULL) := whether the target
+ * had published anything yet. For models of several dtypes: one pull, then a
+ * blend per dtype. */
+int kfb_pair_pull(const kfb_comm *comm, int target, const void *snap_peer,
+                  int64_t slot_bytes, void *dst, int64_t bytes,
+                  int32_t *torn_out, int32_t *got_out, int blocks, int threads,
+                  void *stream);
 /* Publish the current parameters as snapshot version (seq+1) (init_store). */
 int kfb_pair_publish(const kfb_comm *comm, const void *param, void *snap_self,
                      int64_t slot_bytes, int64_t bytes, int blocks,
@@ -254,11 +303,14 @@ int kfb_pair_publish(const kfb_comm *comm, const void *param, void *snap_self,
  * sum((E[g^2] - E[g]^2)^2) into seg_out[s] (device float[n_seg], zeroed by the
  * caller); all-reducing seg_out and summing sqrt() over s gives the
  * reference's "sum of per-tensor norms". seg_ends_dev: device int64[n_seg]
- * cumulative end offsets (elements).
+ * cumulative end offsets (elements). work: device scratch of
+ * KFB_VAR_WORK_WORDS 32-bit words (x np under emulation), zeroed once by the
+ * caller; sums are formed without atomics, in one fixed order.
  * (srcs/python/kungfu/tensorflow/optimizers/grad_variance.py:46-59) */
 int kfb_grad_variance(const kfb_comm *comm, void *const *grads, int dtype,
                       int64_t count, const int64_t *seg_ends_dev, int n_seg,
-                      float *seg_out, int blocks, int threads, void *stream);
+                      float *seg_out, float *work, int blocks, int threads,
+                      void *stream);
 
 /* Gradient noise scale finalize (K17+K19) on device scalars: state[0..3] =
  * {g_ema, s_ema, initialised, last_noise_scale}.

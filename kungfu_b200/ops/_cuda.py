@@ -21,6 +21,7 @@ PAD_BYTES = 32768
 STATE_EPOCH_WORDS = MAX_BLOCKS
 SCRATCH_FLOATS = MAX_BLOCKS + 8
 FUSE_SCRATCH_FLOATS = 1024
+VAR_WORK_WORDS = 4 * MAX_BLOCKS + 8
 
 F32, BF16, F16, I32, F64, I64, U8 = range(7)
 OP_SUM, OP_MIN, OP_MAX, OP_PROD = range(4)
@@ -57,6 +58,15 @@ class SgdHyper(C.Structure):
         ('weight_decay', C.c_float),
         ('nesterov', C.c_int32),
         ('first_step', C.c_int32),
+        # kind 0 = SGD, 1 = AdamW, 2 = Adam (include/kungfu_b200.h)
+        ('kind', C.c_int32),
+        ('beta1', C.c_float),
+        ('beta2', C.c_float),
+        ('eps', C.c_float),
+        ('bias_corr1', C.c_float),
+        ('bias_corr2', C.c_float),
+        ('step', C.c_void_p),
+        ('exp_avg_sq', C.c_void_p),
     ]
 
 
@@ -85,6 +95,7 @@ _SIGS = {
     'kfb_edge_reduce': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     'kfb_edge_copy': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
     'kfb_fuse': (C.c_int, [_PTRS, _I64S, _I64S, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'kfb_sum_slots': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     'kfb_defuse': (C.c_int, [C.c_void_p, C.c_int, _PTRS, _I64S, _I64S, C.c_int, C.c_int, C.c_void_p]),
     'kfb_ssgd_fused_step': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_ssgd_fused_step_nvls': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -92,8 +103,11 @@ _SIGS = {
     'kfb_sma_fused_step': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_avg_step_dev': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_void_p, C.c_ulonglong, C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_avg_step': (C.c_int, [C.POINTER(KfbComm), C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_pair_pull': (C.c_int, [C.POINTER(KfbComm), C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_publish': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
-    'kfb_grad_variance': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_grad_variance': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_sma_fused_step_ex': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_pair_blend': (C.c_int, [C.POINTER(KfbComm), C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_gns_finalize': (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     'kfb_symm_alloc': (C.c_int, [C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]),
     'kfb_symm_export_fd': (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),

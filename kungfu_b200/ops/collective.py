@@ -22,6 +22,13 @@ ONESHOT_MAX_BYTES = 256 << 10
 PREFERRED_LARGE = None
 
 
+def _record(comm, algo, nbytes, stream):
+    """Feed the device traffic statistics (parallel/devstats.py)."""
+    st = getattr(comm, 'stats', None)
+    if st is not None:
+        st.record(algo, nbytes, stream)
+
+
 def choose_algo(comm, nbytes, buf=None, op=K.OP_SUM, dtype=K.F32):
     if comm.np == 1:
         return K.ALGO_ONESHOT
@@ -36,7 +43,7 @@ def choose_algo(comm, nbytes, buf=None, op=K.OP_SUM, dtype=K.F32):
 
 def all_reduce(comm, buf, count, dtype, op='sum', scale=1.0, algo=None, out=None,
                byte_offset=0, out_byte_offset=None, sumsq_out=None, blocks=None,
-               threads=None, stream=None):
+               threads=None, stream=None, channel=0):
     """out[r][:] = scale * op_r(buf[r][:]) for `count` elements at `byte_offset`.
 
     TWOSHOT/NVLS may run in place (out is None -> out = buf). ONESHOT always
@@ -60,11 +67,12 @@ def all_reduce(comm, buf, count, dtype, op='sum', scale=1.0, algo=None, out=None
     out_arr, _k2 = out.ptr_array(out_byte_offset)
     mc_in = (buf.mc_ptr + byte_offset) if buf.mc_ptr else None
     mc_out = (out.mc_ptr + out_byte_offset) if out.mc_ptr else None
-    K.call('kfb_allreduce', comm.cstruct, algo, in_arr, out_arr, mc_in, mc_out,
+    K.call('kfb_allreduce', comm.channel(channel), algo, in_arr, out_arr, mc_in, mc_out,
            count, code, opc, float(scale),
            sumsq_out.data_ptr() if sumsq_out is not None else None,
-           blocks or comm.default_blocks, threads or comm.default_threads,
+           comm.channel_blocks(channel, blocks), threads or comm.default_threads,
            K.stream_ptr(stream))
+    _record(comm, algo, nbytes, stream)
     return out
 
 

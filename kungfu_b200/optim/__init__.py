@@ -1,1 +1,1 @@
-from .fused_sgd import FusedSGD  # noqa: F401
+from .fused import FusedAdam, FusedAdamW, FusedOptimizer, FusedSGD  # noqa: F401

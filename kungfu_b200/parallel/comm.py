@@ -46,6 +46,7 @@ class SymmBuffer(object):
         self.ptrs = ptrs
         self.mc_ptr = mc_ptr
         self._handles = handles or []
+        self._mc = None  # multicast object handle (PeerComm._bind_multicast)
 
     def view(self, dtype, rank=None):
         """Typed tensor over this rank's copy (or emulated rank `rank`)."""
@@ -54,6 +55,29 @@ class SymmBuffer(object):
 
     def ptr_array(self, byte_offset=0):
         return K.ptr_array([p + byte_offset for p in self.ptrs])
+
+    def release(self):
+        """Unmap and release this buffer: the multicast alias, every peer's
+        import and this rank's own physical block. The caller guarantees that no
+        kernel still touches it (PeerComm.close synchronises first)."""
+        lib = K.lib()
+        if self._mc is not None:
+            lib.kfb_mc_free(self._mc)
+            self._mc = None
+            self.mc_ptr = None
+        for h in self._handles:
+            if isinstance(h, tuple):
+                kind, ptr = h
+                if kind == 'ipc':
+                    lib.kfb_ipc_free(C.c_void_p(ptr))
+                elif kind == 'ipc-peer':
+                    lib.kfb_ipc_close(C.c_void_p(ptr))
+            elif h is not None:
+                lib.kfb_symm_free(h)
+        self._handles = []
+        self.ptrs = []
+        self.locals = []
+        self.local = None
 
 
 class _CommBase(object):
@@ -68,7 +92,9 @@ class _CommBase(object):
         self.device = torch.device(device)
         self._struct = K.KfbComm()
         self._keep = []
-        self.default_blocks = int(os.environ.get('KUNGFU_COMM_BLOCKS', '32'))
+        self._channels = {}
+        self.closed = False
+        self.default_blocks = min(64, int(os.environ.get('KUNGFU_COMM_BLOCKS', '32')))
         self.default_threads = int(os.environ.get('KUNGFU_COMM_THREADS', '512'))
 
     def _init_struct(self, rank, np, pad_ptrs, n_state):
@@ -87,6 +113,38 @@ class _CommBase(object):
     @property
     def cstruct(self):
         return C.byref(self._struct)
+
+    # Collectives keep their barrier epochs, flags and reduction scratch per
+    # CTA index, so two kernels of one communicator may only be in flight at the
+    # same time if they use disjoint CTA rows. A channel is such a slice: the
+    # caller's stream uses channel 0, the asynchronous torch ops channel 1, the
+    # gradient buckets that overlap backward channel 2. Kernels of ONE channel
+    # must be stream-ordered.
+    CHANNELS = {0: (0, 64), 1: (64, 32), 2: (96, 32)}  # channel -> (first CTA row, rows)
+
+    def channel(self, ch):
+        """ctypes reference to the communicator as seen by channel `ch`."""
+        if ch == 0:
+            return self.cstruct
+        cs = self._channels.get(ch)
+        if cs is None:
+            base, _ = self.CHANNELS[ch]
+            s = K.KfbComm()
+            s.rank, s.np = self._struct.rank, self._struct.np
+            for r in range(K.MAX_RANKS):
+                p = self._struct.pads[r]
+                s.pads[r] = (p + base * K.MAX_RANKS * 4) if p else None
+            s.local_epoch = self._struct.local_epoch + base * 4
+            scratch = torch.zeros(K.SCRATCH_FLOATS * max(1, self.n_local_ranks), dtype=torch.float32,
+                                  device=self.device)
+            s.scratch = scratch.data_ptr()
+            s.mc_pad = None
+            cs = (s, scratch)
+            self._channels[ch] = cs
+        return C.byref(cs[0])
+
+    def channel_blocks(self, ch, want=None):
+        return max(1, min(want or self.default_blocks, self.CHANNELS[ch][1]))
 
     @property
     def n_local_ranks(self):
@@ -201,7 +259,7 @@ class PeerComm(_CommBase):
                 q = C.c_void_p()
                 K.check(lib.kfb_ipc_open(dev, all_h[r], C.byref(q)))
                 ptrs.append(q.value)
-        return nbytes, [('ipc', p.value)], ptrs
+        return nbytes, [('ipc', p.value)] + [('ipc-peer', q) for r, q in enumerate(ptrs) if r != self.rank], ptrs
 
     def alloc(self, nbytes, multicast=False):
         """Collective: every rank must call with the same size, in the same order."""
@@ -218,14 +276,26 @@ class PeerComm(_CommBase):
             size, handles, ptrs = self._alloc_vmm(nbytes)
         else:
             size, handles, ptrs = self._alloc_ipc(nbytes)
-        mc_ptr = None
+        mc_ptr, mc_obj = None, None
         if multicast and self.multicast_ok:
-            mc_ptr = self._bind_multicast(size, handles[self.rank])
-        local = K.tensor_from_ptr(ptrs[self.rank], size, self.device, owner=handles)
+            mc_ptr, mc_obj = self._bind_multicast(size, handles[self.rank])
+        elif multicast and self.np > 1 and require_nvls():
+            raise K.KungFuCudaError('KUNGFU_REQUIRE_NVLS=1 but no multicast (NVLS) alias can be bound on this '
+                                    'machine / in this mode (%s)' % self.mode)
+        local = K.tensor_from_ptr(ptrs[self.rank], size, self.device, owner=None)
         self.xchg.barrier()
         buf = SymmBuffer(self, size, [local], ptrs, mc_ptr, handles)
+        buf._mc = mc_obj
         self._keep.append(buf)
         return buf
+
+    def free(self, buf):
+        """Collective: release one buffer on every rank (nobody may still use it)."""
+        torch.cuda.synchronize(self.device)
+        self.xchg.barrier()
+        if buf in self._keep:
+            self._keep.remove(buf)
+        buf.release()
 
     def _bind_multicast(self, size, my_handle):
         lib = K.lib()
@@ -248,18 +318,45 @@ class PeerComm(_CommBase):
             p = C.c_void_p()
             K.check(lib.kfb_mc_bind(mc, my_handle, C.byref(p)))
             self.xchg.barrier()
-            self._keep.append(('mc', mc))
-            return p.value
+            return p.value, mc
         except K.KungFuCudaError:
             # a failed bind must fail on every rank or on none; ranks agree below
             self.multicast_ok = False
             raise
 
-    def close(self):
+    def close(self, collective=True):
+        """Give everything back: unmap the peers' memory (their GPUs can then
+        free it), release this rank's blocks and multicast objects. The
+        reference dropped the connections to removed peers and destroyed its
+        NCCL communicators at this point
+        (/root/reference/srcs/go/rchannel/client/connection_pool.go:29-51,
+        /root/reference/srcs/cpp/src/nccl/gpu_collective.cpp:84-94). With
+        collective=False no peer is consulted (a detached worker on its way
+        out, or a membership that no longer exists)."""
+        if self.closed:
+            return
+        self.closed = True
+        torch.cuda.synchronize(self.device)
+        if collective:
+            try:
+                self.xchg.barrier()
+            except Exception:
+                pass
+        for buf in self._keep:
+            buf.release()
         self._keep = []
+        self._channels = {}
+
+
+def require_nvls():
+    """KUNGFU_REQUIRE_NVLS=1: a missing multicast alias is an error instead of a
+    silent fall-back to the peer-to-peer kernels (multi-GPU tests set it, so a
+    box whose multicast setup fails cannot pass as if NVLS had been tested)."""
+    return os.environ.get('KUNGFU_REQUIRE_NVLS', '0') == '1'
 
 
 _default = None
+_retired = []
 
 
 def default_comm():
@@ -349,9 +446,35 @@ def set_default_comm(comm):
 
 
 def reset_default_comm():
-    """Drop the communicator (after a resize the next use re-maps peer memory
-    for the new membership; surviving processes are not restarted)."""
+    """Retire the communicator (after a resize the next use maps peer memory for
+    the new membership; surviving processes are not restarted). Its buffers
+    stay mapped until release_retired(): optimizers copy their state out of the
+    old arenas into the new ones first."""
     global _default
     if _default is not None:
-        _default.close()
+        _retired.append(_default)
     _default = None
+
+
+def release_retired():
+    """Unmap and free every buffer of communicators retired by a membership
+    change. Call once nothing refers to their memory any more (the fused
+    optimizers do after rebuild(); ElasticState after the state hand-over)."""
+    from ..torch.ops import collective as tops
+    while _retired:
+        c = _retired.pop()
+        tops.drop_staging(c)
+        c.close(collective=False)
+
+
+def shutdown():
+    """Release all device communication resources of this process (a detached
+    worker calls this before it exits so that the survivors' GPUs get the
+    peer mappings of its memory back)."""
+    global _default
+    release_retired()
+    if _default is not None:
+        from ..torch.ops import collective as tops
+        tops.drop_staging(_default)
+        _default.close(collective=False)
+        _default = None

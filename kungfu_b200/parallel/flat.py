@@ -61,8 +61,12 @@ class Arena(object):
             self._repoint()
         self.master = None
         self.mom = None
+        self.mom2 = None
         self._src_cache = None
         self.seg_ends = None
+        # element ranges over which sharded optimizer state is split between the ranks
+        # (rank r owns the r-th part of each range); one range unless the step is bucketed
+        self.segments = [(0, self.count)]
 
     def _repoint(self):
         """Make every parameter a view into the flat buffer (values preserved)."""
@@ -88,7 +92,11 @@ class Arena(object):
             return flat.view(N, H, W, Cc).permute(0, 3, 1, 2)
         return flat.view(p.shape)
 
-    def ensure_master(self):
+    def ensure_master(self, slots=1):
+        """fp32 master copy of the parameters plus `slots` zeroed optimizer
+        slots of the same layout (momentum; Adam: first and second moment)."""
+        if self.master is not None and slots > 1 and self.mom2 is None:
+            self.mom2 = torch.zeros_like(self.master)
         if self.master is None:
             R = self.comm.n_local_ranks
             if self.comm.emulated:
@@ -97,6 +105,7 @@ class Arena(object):
                 m = self.flat_params.float()
             self.master = m.contiguous()
             self.mom = torch.zeros_like(self.master)
+            self.mom2 = torch.zeros_like(self.master) if slots > 1 else None
         return self.master, self.mom
 
     def segment_ends(self):
@@ -106,14 +115,36 @@ class Arena(object):
             self.seg_ends = torch.tensor(ends, dtype=torch.int64, device=self.comm.device)
         return self.seg_ends
 
+    def state_view(self, flat, i):
+        """Parameter i's slice of any flat tensor laid out like this arena, in
+        the parameter's logical shape (channels-last aware)."""
+        p, off = self.params[i], self.offsets[i]
+        v = flat[off:off + p.numel()]
+        if self._cl[i]:
+            N, Cc, H, W = p.shape
+            return v.view(N, H, W, Cc).permute(0, 3, 1, 2)
+        return v.view(p.shape)
+
     # ---- gradient gather (fuse) ------------------------------------------------------
-    def fuse_grads(self, sumsq_out=None, stream=None):
-        """Copy every p.grad into its slot of the flat gradient buffer (one or
-        a few multi-tensor launches); optionally ||g||^2 -> sumsq_out[0]."""
-        srcs, counts, offs = [], [], []
-        for i, (p, off) in enumerate(zip(self.params, self.offsets)):
+    def fuse_grads(self, sumsq_out=None, stream=None, idx=None, scratch=None):
+        """Copy every p.grad (or those of the parameters `idx`) into its slot of
+        the flat gradient buffer (one or a few multi-tensor launches);
+        optionally ||g||^2 -> sumsq_out[0]. A parameter without a gradient
+        contributes zeros: its slot is cleared, so a stale gradient of an
+        earlier step can never be reduced or applied again. Returns the number
+        of gradients copied."""
+        srcs, counts, offs, keep, temps = [], [], [], [], []
+        which = range(len(self.params)) if idx is None else idx
+        ctx = torch.cuda.stream(stream) if stream is not None else None
+        for i in which:
+            p, off = self.params[i], self.offsets[i]
             g = p.grad
             if g is None:
+                if ctx is not None:
+                    with ctx:
+                        self.flat_grads[off:off + p.numel()].zero_()
+                else:
+                    self.flat_grads[off:off + p.numel()].zero_()
                 continue
             if g.dtype != self.dtype:
                 raise K.KungFuCudaError('gradient dtype %s != arena dtype %s' % (g.dtype, self.dtype))
@@ -122,17 +153,34 @@ class Arena(object):
                     g = g.contiguous(memory_format=torch.channels_last)
             elif not g.is_contiguous():
                 g = g.contiguous()
+            # a contiguous temporary must outlive the launch below: freed earlier, the caching
+            # allocator could hand its block to the next temporary and two sources would alias
+            keep.append(g)
+            if g is not p.grad:
+                temps.append(g)
             srcs.append(g.data_ptr())
             counts.append(g.numel())
             offs.append(off)
         if not srcs:
+            if sumsq_out is not None:
+                if ctx is not None:
+                    with ctx:
+                        sumsq_out.zero_()
+                else:
+                    sumsq_out.zero_()
             return 0
         pa, _k1 = K.ptr_array(srcs)
         ca, _k2 = K.i64_array(counts)
         oa, _k3 = K.i64_array(offs)
+        if scratch is None:
+            scratch = self.comm._fuse_scratch
         K.call('kfb_fuse', pa, ca, oa, len(srcs), self.code, self.flat_grads.data_ptr(),
                self.code, sumsq_out.data_ptr() if sumsq_out is not None else None,
-               self.comm._fuse_scratch.data_ptr(), K.stream_ptr(stream))
+               scratch.data_ptr(), K.stream_ptr(stream))
+        if stream is not None:
+            for g in temps:
+                g.record_stream(stream)
+        del keep, temps
         return len(srcs)
 
     def point_grads_at_flat(self):

@@ -91,7 +91,7 @@ def resize_cluster(new_size):
     memory (reference: /root/reference/srcs/go/kungfu/peer/peer.go:227-263)."""
     changed, det = _p().resize_cluster(int(new_size))
     if changed:
-        _on_membership_change()
+        _on_membership_change(det)
     return changed, det
 
 
@@ -100,17 +100,21 @@ def resize_cluster_from_url():
     Returns (changed, detached) like resize_cluster."""
     changed, det = _p().resize_cluster_from_url()
     if changed:
-        _on_membership_change()
+        _on_membership_change(det)
     return changed, det
 
 
-def _on_membership_change():
+def _on_membership_change(detached=False):
     try:
         from ..torch.ops import collective as tops
         tops._reset_names()
         tops.reset_staging()
         from ..parallel import comm
         comm.reset_default_comm()
+        if detached:
+            # a worker that left the cluster gives its peer mappings and blocks back right away:
+            # the survivors' GPUs hold imports of this memory until both sides have let go
+            comm.shutdown()
     except Exception:  # device layer not in use
         pass
 

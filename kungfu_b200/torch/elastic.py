@@ -56,6 +56,13 @@ class ElasticState(object):
         tops.broadcast_parameters(self.model.state_dict())
         if self.optimizer is not None and hasattr(self.optimizer, 'broadcast_state'):
             self.optimizer.broadcast_state()
+        # nothing refers to the previous membership's peer memory any more: once every member is
+        # past its last use (barrier), unmap the peers' blocks and free ours
+        from ..parallel import comm as pc
+        if torch.cuda.is_available() and torch.cuda.is_initialized():
+            torch.cuda.synchronize()
+        kfpy.run_barrier()
+        pc.release_retired()
 
     def end_step(self, batch_size=0):
         self.step += 1

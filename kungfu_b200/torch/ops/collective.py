@@ -85,6 +85,13 @@ def reset_staging():
     _comm_stream.clear()
 
 
+def drop_staging(comm):
+    """Forget the staging buffers / side stream of one communicator (it is being closed)."""
+    for k in [k for k in _staging if k[0] == id(comm)]:
+        del _staging[k]
+    _comm_stream.pop(id(comm), None)
+
+
 def _cuda_all_reduce(x, y, op):
     from ...ops import _cuda as K
     from ...ops import collective as coll
@@ -335,9 +342,14 @@ def monitored_all_reduce(x, tree=None, op=None, name=None):
     return y.to(x.device)
 
 
+def to_host(x):
+    """Host copy of a tensor (the one place where the host paths stage device data)."""
+    return x if not x.is_cuda else x.to('cpu')
+
+
 def save_variable(x, name, version=None):
     """Publish a tensor in this worker's p2p store (host path)."""
-    xc = x.detach().contiguous().cpu()
+    xc = to_host(x.detach().contiguous())
     kfpy.peer().save(name, xc.data_ptr(), xc.numel() * xc.element_size(),
                      None if version is None else str(version))
 

@@ -21,11 +21,16 @@ def _ada_step(self, closure=None):
         loss = _SynchronousAveraging.step(self, closure)
     else:
         if self._kf_global_step == self._kf_change_step:
+            # no more model averages from here on (zero_grad() used to start one per step)
+            self.overlap_average = False
+            if self._kf_avg_pending:
+                torch.cuda.current_stream().wait_stream(self._kf_side)
+                self._kf_avg_pending = False
             tops.broadcast_parameters({n: p.data for n, p in self._kf_named})
             if core.is_fused(self):
                 for _, arenas in self.arenas():
                     for a in arenas:
-                        a.ensure_master()
+                        a.ensure_master(slots=self._n_slots())
                         a.master.copy_(a.flat_params.float())
         loss = _SynchronousSGD.step(self, closure)
     self._kf_global_step += 1

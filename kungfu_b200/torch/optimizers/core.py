@@ -31,25 +31,29 @@ def wrap(optimizer, mixin, **attrs):
 
 
 def is_fused(optimizer):
-    from ...optim.fused_sgd import FusedSGD
-    return isinstance(optimizer, FusedSGD)
+    from ...optim.fused import FusedOptimizer
+    return isinstance(optimizer, FusedOptimizer)
 
 
 class GradSync(object):
     BUCKET_BYTES = 32 << 20
 
-    def __init__(self, named_parameters, overlap=False, bucket_bytes=None):
+    def __init__(self, named_parameters, overlap=False, bucket_bytes=None, average=True):
         self.named = [(n, p) for n, p in named_parameters if p.requires_grad]
         self.cuda_named = [(n, p) for n, p in self.named if p.is_cuda]
         self.cpu_named = [(n, p) for n, p in self.named if not p.is_cuda]
         self.overlap = overlap
         self.bucket_bytes = bucket_bytes or self.BUCKET_BYTES
         self._arenas = None
+        self._buckets = None
         self._hooks = []
         self._comm_id = None
         self.sumsq_local = None
         self.sumsq_global = None
         self.monitor_norms = False
+        # buckets are launched from autograd hooks, long before sync() is called:
+        # the reduction's scale has to be known when the hooks fire
+        self._average = bool(average)
 
     # -- lazily built per communicator (rebuilt after a resize) -----------------------
     def _ensure(self):
@@ -78,8 +82,11 @@ class GradSync(object):
         k = max(1, len(self._arenas))
         self._ss_local = torch.zeros(k, dtype=torch.float32, device=dev)
         self._ss_global = torch.zeros(k, dtype=torch.float32, device=dev)
-        if self.overlap and comm.np > 1:
+        if self.overlap and comm.np > 1 and not comm.cross:
+            # (several hosts: the cross-host leg runs on the host after backward, see _sync_cuda)
             self._build_buckets(comm)
+        else:
+            self._buckets = None
         return comm
 
     # -- plain (post-backward) path -------------------------------------------------------
@@ -91,7 +98,7 @@ class GradSync(object):
                 handles.append(tops.inplace_all_reduce_async_op(p.grad, n, 'sum'))
         if self.cuda_named:
             comm = self._ensure()
-            if self.overlap and comm.np > 1:
+            if self._buckets is not None:
                 self._finish_overlap(average)
             else:
                 self._sync_cuda(comm, average)
@@ -139,7 +146,7 @@ class GradSync(object):
                     last = max(cur)
                     hi = a.offsets[last + 1] if last + 1 < len(a.params) else a.count
                     self._buckets.append({'arena': a, 'idx': list(cur), 'lo': lo, 'hi': hi,
-                                          'pending': len(cur), 'launched': False})
+                                          'pending': len(cur), 'launched': False, 'slot': len(self._buckets)})
                     cur, nbytes = [], 0
         self._next_bucket = 0
         self._where = {}
@@ -148,7 +155,11 @@ class GradSync(object):
                 self._where[id(b['arena'].params[i])] = b_i
         for _, p in self.cuda_named:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
-        self._average = True
+        k = max(1, len(self._buckets))
+        self._ss_local = torch.zeros(k, dtype=torch.float32, device=comm.device)
+        self._ss_global = torch.zeros(k, dtype=torch.float32, device=comm.device)
+        self._ss_out = torch.zeros(2, dtype=torch.float32, device=comm.device)
+        self._fuse_scratch = torch.zeros(1024, dtype=torch.float32, device=comm.device)
 
     def _remove_hooks(self):
         for h in self._hooks:
@@ -171,41 +182,24 @@ class GradSync(object):
             self._next_bucket += 1
 
     def _launch_bucket(self, comm, b):
-        from ...ops import _cuda as K
         from ...ops import collective as coll
         a = b['arena']
         self._stream.wait_stream(torch.cuda.current_stream())
         scale = 1.0 / comm.np if self._average else 1.0
-        with torch.cuda.stream(self._stream):
-            srcs, counts, offs = [], [], []
-            for i in b['idx']:
-                p = a.params[i]
-                if p.grad is None:
-                    a.grad_view(i).zero_()
-                    continue
-                g = p.grad
-                if a.is_cl(i):
-                    g = g.contiguous(memory_format=torch.channels_last)
-                else:
-                    g = g.contiguous()
-                g.record_stream(self._stream)
-                srcs.append(g.data_ptr())
-                counts.append(g.numel())
-                offs.append(a.offsets[i])
-            if srcs:
-                pa, _k1 = K.ptr_array(srcs)
-                ca, _k2 = K.i64_array(counts)
-                oa, _k3 = K.i64_array(offs)
-                K.call('kfb_fuse', pa, ca, oa, len(srcs), a.code, a.flat_grads.data_ptr(), a.code,
-                       None, None, K.stream_ptr(self._stream))
-            esize = a.flat_grads.element_size()
-            coll.all_reduce(comm, a.grads_buf, b['hi'] - b['lo'], a.code, 'sum', scale=scale,
-                            byte_offset=b['lo'] * esize, stream=self._stream,
-                            blocks=min(comm.default_blocks, 16))
+        k = b['slot']
+        ss_l = self._ss_local[k:k + 1] if self.monitor_norms else None
+        ss_g = self._ss_global[k:k + 1] if self.monitor_norms else None
+        a.fuse_grads(sumsq_out=ss_l, stream=self._stream, idx=b['idx'], scratch=self._fuse_scratch)
+        esize = a.flat_grads.element_size()
+        coll.all_reduce(comm, a.grads_buf, b['hi'] - b['lo'], a.code, 'sum', scale=scale,
+                        byte_offset=b['lo'] * esize, stream=self._stream, sumsq_out=ss_g,
+                        blocks=comm.channel_blocks(2, 16), channel=2)
         b['launched'] = True
 
     def _finish_overlap(self, average):
-        self._average = average
+        if bool(average) != self._average:
+            raise RuntimeError('GradSync(overlap=True) was built with average=%s; the buckets of this step '
+                               'were already reduced with that scale' % self._average)
         self._launch_ready(force=True)
         torch.cuda.current_stream().wait_stream(self._stream)
         for a in self._arenas:
@@ -214,6 +208,13 @@ class GradSync(object):
             b['pending'] = len(b['idx'])
             b['launched'] = False
         self._next_bucket = 0
+        if self.monitor_norms:
+            from ...ops import _cuda as K
+            n = len(self._buckets)
+            K.call('kfb_sum_slots', self._ss_local.data_ptr(), n, self._ss_out.data_ptr(), K.stream_ptr())
+            K.call('kfb_sum_slots', self._ss_global.data_ptr(), n, self._ss_out.data_ptr() + 4, K.stream_ptr())
+            self.sumsq_local = self._ss_out[0]
+            self.sumsq_global = self._ss_out[1]
 
     def arenas(self):
         self._ensure()

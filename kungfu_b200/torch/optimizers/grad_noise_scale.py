@@ -52,9 +52,11 @@ def _gns_step(self, closure=None):
 
 
 def MonitorGradientNoiseScaleOptimizer(optimizer, named_parameters=None, device_batch_size=1,
-                                       monitor_interval=1, alpha=0.9, op=None):
+                                       monitor_interval=1, alpha=0.9, op=None, overlap=False):
     """S-SGD whose ``noise_scale`` attribute (a device scalar) tracks the
-    gradient noise scale; read it with ``float(opt.noise_scale)``."""
+    gradient noise scale; read it with ``float(opt.noise_scale)``. ``overlap``
+    as in SynchronousSGDOptimizer: the two norms then come out of the
+    per-bucket kernels (fixed slots, summed in order)."""
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]
     else:
@@ -62,6 +64,6 @@ def MonitorGradientNoiseScaleOptimizer(optimizer, named_parameters=None, device_
     mixin = type('_GNS', (object, ), {k: v for k, v in _SynchronousSGD.__dict__.items() if k not in ('__dict__', '__weakref__')})
     mixin._kf_setup = _gns_setup
     mixin.step = torch.no_grad()(_gns_step)
-    return core.wrap(optimizer, mixin, _kf_named=named, _kf_average=True, _kf_overlap=False,
+    return core.wrap(optimizer, mixin, _kf_named=named, _kf_average=True, _kf_overlap=bool(overlap),
                      _kf_device_batch=device_batch_size, _kf_interval=max(1, int(monitor_interval)),
                      _kf_gns_alpha=float(alpha))

@@ -17,6 +17,7 @@ from .sync_sgd import _SynchronousSGD
 def _var_setup(self):
     self._kf_sync = core.GradSync(self._kf_named, overlap=False)
     self._kf_var_step = 0
+    self._kf_var_bufs = {}
     self.variance = None
 
 
@@ -34,14 +35,19 @@ def _variance_of(self):
                 continue
             ends = a.segment_ends()
             nseg = ends.numel()
-            seg = comm.alloc(max(nseg * 4, 16))
+            bufs = self._kf_var_bufs.get((id(comm), id(a)))
+            if bufs is None:
+                # symmetric allocations are collective and never shrink: made once, reused every step
+                bufs = (comm.alloc(max(nseg * 4, 16)), comm.alloc(max(nseg * 4, 16)) if comm.np > 1 else None,
+                        torch.zeros(K.VAR_WORK_WORDS * comm.n_local_ranks, dtype=torch.float32, device=comm.device))
+                self._kf_var_bufs[(id(comm), id(a))] = bufs
+            seg, out, work = bufs
             sv = seg.view(torch.float32)
             sv[:nseg].zero_()
             ga, _k = a.grads_buf.ptr_array()
             K.call('kfb_grad_variance', comm.cstruct, ga, a.code, a.count, ends.data_ptr(), nseg,
-                   sv.data_ptr(), comm.default_blocks, comm.default_threads, K.stream_ptr())
+                   sv.data_ptr(), work.data_ptr(), comm.default_blocks, comm.default_threads, K.stream_ptr())
             if comm.np > 1:
-                out = comm.alloc(max(nseg * 4, 16))
                 coll.all_reduce(comm, seg, (nseg + 3) // 4 * 4, K.F32, 'sum', algo=K.ALGO_ONESHOT, out=out)
                 sv = out.view(torch.float32)
             v = sv[:nseg].sqrt().sum()

@@ -13,13 +13,23 @@ from . import core
 
 class _SynchronousSGD(object):
     def _kf_setup(self):
-        self._kf_sync = None if core.is_fused(self) else core.GradSync(
-            self._kf_named, overlap=self._kf_overlap)
+        if core.is_fused(self):
+            self._kf_sync = None
+            if self._kf_overlap:
+                # bucketed fused steps launched from autograd hooks while backward runs
+                self.enable_overlap(sync=True, average=self._kf_average)
+            self.rebind_overlap()
+        else:
+            self._kf_sync = core.GradSync(self._kf_named, overlap=self._kf_overlap, average=self._kf_average)
 
     def sync_gradients(self):
         """All-reduce (average) every gradient in place; no parameter update."""
         if self._kf_sync is None:
-            self._kf_sync = core.GradSync(self._kf_named, overlap=False)
+            if core.is_fused(self) and self._ov is not None:
+                raise RuntimeError('sync_gradients() is not available while the fused step overlaps backward '
+                                   '(the exchange and the update are one kernel); build the optimizer with '
+                                   'overlap=False')
+            self._kf_sync = core.GradSync(self._kf_named, overlap=False, average=self._kf_average)
         self._kf_sync.sync(average=self._kf_average)
 
     @torch.no_grad()
@@ -42,8 +52,10 @@ def SynchronousSGDOptimizer(optimizer, named_parameters=None, op=None, overlap=F
     """Wrap `optimizer` so that step() first synchronises gradients.
 
     op: None|'mean'|'average' -> average (default), 'sum' -> plain sum.
-    overlap: launch bucket all-reduces from autograd hooks while backward runs
-             (generic optimizers; the FusedSGD path is a single fused kernel).
+    overlap: launch the buckets from autograd hooks while backward runs: for
+             the fused optimizers each bucket is one gather + one fused
+             exchange-and-update kernel, for other optimizers one gather + one
+             all-reduce (one backward pass per step() is assumed).
     """
     if named_parameters is None:
         named = [('p%d' % i, p) for i, p in enumerate(q for g in optimizer.param_groups for q in g['params'])]

@@ -199,8 +199,16 @@ def test_grad_variance_and_gns(np_):
     ends = torch.tensor([800, 4000, n], dtype=torch.int64, device='cuda')
     seg = torch.zeros(np_ * 3, device='cuda')
     ga, _1 = grads.ptr_array()
-    K.call('kfb_grad_variance', comm.cstruct, ga, K.F32, n, ends.data_ptr(), 3, seg.data_ptr(),
+    work = torch.zeros(K.VAR_WORK_WORDS * np_, device='cuda')
+    K.call('kfb_grad_variance', comm.cstruct, ga, K.F32, n, ends.data_ptr(), 3, seg.data_ptr(), work.data_ptr(),
            comm.default_blocks, 256, K.stream_ptr())
+    torch.cuda.synchronize()
+    first = seg.clone()
+    seg.zero_()
+    K.call('kfb_grad_variance', comm.cstruct, ga, K.F32, n, ends.data_ptr(), 3, seg.data_ptr(), work.data_ptr(),
+           comm.default_blocks, 256, K.stream_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(first, seg), 'the variance sums are formed in a fixed order: bit-identical run to run'
     torch.cuda.synchronize()
     st = torch.stack(gs)
     v = (st * st).mean(0) - st.mean(0) ** 2

@@ -34,6 +34,8 @@ def check_allreduce():
         es = torch.empty(0, dtype=dtype).element_size()
         buf = comm.alloc(n * es, multicast=True)
         out = comm.alloc(n * es, multicast=True)
+        if pc.require_nvls() and np_ > 1:
+            assert buf.mc_ptr and out.mc_ptr, 'KUNGFU_REQUIRE_NVLS=1: the buffers must have a multicast alias'
         these = list(algos) + ([K.ALGO_NVLS] if buf.mc_ptr else [])
         xs = inputs(n, dtype, 1)
         ref = torch.stack([x.float() for x in xs]).sum(0) / np_
@@ -93,7 +95,7 @@ def check_movers():
 
 
 def check_fused_optimizers():
-    from kungfu_b200.optim import FusedSGD
+    from kungfu_b200.optim import FusedAdamW, FusedSGD
     torch.manual_seed(0)
 
     def make():
@@ -105,12 +107,19 @@ def check_fused_optimizers():
         return torch.randn(32, 64, generator=g).to(dev), torch.randint(0, 16, (32, ), generator=g).to(dev)
 
     # S-SGD fused == single process on the concatenated batch (P2P kernel, then the NVLS kernel)
-    def fused_ssgd_matches_oracle(nvls_min):
+    def fused_ssgd_matches_oracle(nvls_min, overlap=False, adam=False):
         m = make()
-        opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.1, momentum=0.9), m.named_parameters())
+        if adam:
+            inner = FusedAdamW(m.parameters(), lr=1e-2, weight_decay=0.05, bucket_bytes=8000)
+        else:
+            inner = FusedSGD(m.parameters(), lr=0.1, momentum=0.9, bucket_bytes=8000)
+        opt = kf.optimizers.SynchronousSGDOptimizer(inner, m.named_parameters(), overlap=overlap)
         opt.nvls_min_bytes = nvls_min
         ref = make()
-        ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+        if adam:
+            ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.05)
+        else:
+            ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
         for step in range(4):
             x, y = batch(rank, step)
             opt.zero_grad(set_to_none=True)
@@ -121,14 +130,68 @@ def check_fused_optimizers():
             torch.nn.functional.cross_entropy(ref(torch.cat(xs)), torch.cat(ys)).backward()
             ropt.step()
         torch.cuda.synchronize()
+        if overlap and np_ > 1:
+            assert len(opt._ov['buckets']) > 1, 'the test model must span several buckets'
+        want = 'nvls' if (nvls_min == 0 and comm.multicast_ok) else ('p2p' if np_ > 1 else 'local')
+        assert opt.last_algo == want, (opt.last_algo, want)
+        if nvls_min == 0 and pc.require_nvls() and np_ > 1:
+            assert opt.last_algo == 'nvls'
+        tol = dict(rtol=2e-3, atol=2e-4) if adam else dict(rtol=1e-4, atol=1e-5)
         for p, q in zip(m.parameters(), ref.parameters()):
-            assert torch.allclose(p, q, rtol=1e-4, atol=1e-5), (nvls_min, (p - q).abs().max())
-        opt.consolidate()
+            assert torch.allclose(p, q, **tol), (nvls_min, overlap, adam, (p - q).abs().max())
+        # the sharded fp32 state, made whole, equals the single-process optimizer's
+        sd = opt.state_dict()
+        for i, q in enumerate(ref.parameters()):
+            assert torch.allclose(sd['state'][i]['master'], q, **tol), (i, 'master')
+            rs = ropt.state[q]
+            if adam:
+                assert torch.allclose(sd['state'][i]['exp_avg'], rs['exp_avg'], rtol=2e-3, atol=1e-5)
+                assert torch.allclose(sd['state'][i]['exp_avg_sq'], rs['exp_avg_sq'], rtol=2e-3, atol=1e-7)
+            else:
+                assert torch.allclose(sd['state'][i]['momentum_buffer'], rs['momentum_buffer'], rtol=1e-4, atol=1e-5)
+        return [p.detach().clone() for p in m.parameters()]
 
-    fused_ssgd_matches_oracle(1 << 40)  # peer load/store kernel
-    fused_ssgd_matches_oracle(0)        # NVLS kernel (when multicast is available)
+    for adam in (False, True):
+        a = fused_ssgd_matches_oracle(1 << 40, adam=adam)  # peer load/store kernel
+        b = fused_ssgd_matches_oracle(0, adam=adam)        # NVLS kernel (when multicast is available)
+        c = fused_ssgd_matches_oracle(1 << 40, overlap=True, adam=adam)  # buckets launched from autograd hooks
+        d = fused_ssgd_matches_oracle(0, overlap=True, adam=adam)
+        # cutting the arena into buckets changes no element's arithmetic
+        for x, y in zip(a, c):
+            assert torch.equal(x, y), 'bucketed p2p step differs from the single launch'
+        for x, y in zip(b, d):
+            assert torch.equal(x, y), 'bucketed NVLS step differs from the single launch'
     if rank == 0:
-        print('fused S-SGD ok (p2p + nvls)', flush=True)
+        print('fused S-SGD / AdamW ok (p2p + nvls, single launch + overlapped buckets)', flush=True)
+
+    # save -> new objects -> load -> continue == uninterrupted run
+    def run_ckpt(split):
+        m = make()
+        opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.1, momentum=0.9), m.named_parameters())
+        for step in range(6):
+            if step == split:
+                import io
+                f = io.BytesIO()
+                torch.save({'model': m.state_dict(), 'opt': opt.state_dict()}, f)
+                f.seek(0)
+                ck = torch.load(f)
+                m = make()
+                for p in m.parameters():
+                    p.data.zero_()
+                opt = kf.optimizers.SynchronousSGDOptimizer(FusedSGD(m.parameters(), lr=0.5, momentum=0.1), m.named_parameters())
+                m.load_state_dict(ck['model'])
+                opt.load_state_dict(ck['opt'])
+            x, y = batch(rank, step)
+            opt.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+        torch.cuda.synchronize()
+        return [p.detach().clone() for p in m.parameters()]
+
+    for x, y in zip(run_ckpt(-1), run_ckpt(3)):
+        assert torch.allclose(x, y, rtol=1e-6, atol=1e-7), (x - y).abs().max()
+    if rank == 0:
+        print('checkpoint round trip ok', flush=True)
 
     # generic optimizer (Adam) through GradSync, plain and overlapped
     for overlap in (False, True):
@@ -166,6 +229,77 @@ def check_fused_optimizers():
     torch.cuda.synchronize()
     if np_ > 1:
         assert float((w1[0] - w1[-1]).abs().max()) < 0.2 * float((w0[0] - w0[-1]).abs().max())
+    # SMA: fused (average on the switch, started by zero_grad under forward/backward), fused AdamW and a
+    # plain torch optimizer on the device path all follow the same recurrence as a host-side oracle
+    def sma_oracle(alpha, lr, steps, adam):
+        ms = [make() for _ in range(np_)]
+        for r, mm in enumerate(ms):
+            for p in mm.parameters():
+                p.data += 0.1 * r
+        mk = (lambda ps: torch.optim.AdamW(ps, lr=lr, weight_decay=0.0)) if adam else (lambda ps: torch.optim.SGD(ps, lr=lr))
+        opts = [mk(mm.parameters()) for mm in ms]
+        for step in range(steps):
+            for r, (mm, oo) in enumerate(zip(ms, opts)):
+                x, y = batch(r, step)
+                oo.zero_grad()
+                torch.nn.functional.cross_entropy(mm(x), y).backward()
+            with torch.no_grad():
+                for ps in zip(*[list(mm.parameters()) for mm in ms]):
+                    avg = torch.stack([p.data for p in ps]).mean(0)
+                    for p in ps:
+                        p.data.add_(avg - p.data, alpha=alpha)
+            for oo in opts:
+                oo.step()
+        return [p.detach().clone() for p in ms[rank].parameters()]
+
+    for kind in ('fused-sgd', 'fused-adamw', 'torch-sgd', 'torch-adamw'):
+        adam = kind.endswith('adamw')
+        m = make()
+        for p in m.parameters():
+            p.data += 0.1 * rank
+        if kind == 'fused-sgd':
+            inner = FusedSGD(m.parameters(), lr=0.05)
+        elif kind == 'fused-adamw':
+            inner = FusedAdamW(m.parameters(), lr=0.01, weight_decay=0.0)
+        elif kind == 'torch-sgd':
+            inner = torch.optim.SGD(m.parameters(), lr=0.05)
+        else:
+            inner = torch.optim.AdamW(m.parameters(), lr=0.01, weight_decay=0.0)
+        opt = kf.optimizers.SynchronousAveragingOptimizer(inner, m.named_parameters(), alpha=0.5)
+        for step in range(4):
+            x, y = batch(rank, step)
+            opt.zero_grad(set_to_none=True)
+            torch.nn.functional.cross_entropy(m(x), y).backward()
+            opt.step()
+        torch.cuda.synchronize()
+        want = sma_oracle(0.5, 0.01 if adam else 0.05, 4, adam)
+        for p, q in zip(m.parameters(), want):
+            assert torch.allclose(p, q, rtol=2e-3, atol=2e-4), (kind, (p - q).abs().max())
+    if rank == 0:
+        print('SMA ok: fused SGD / fused AdamW / torch SGD / torch AdamW vs oracle', flush=True)
+    # PairAveraging around a plain torch optimizer stays on the device (pull + blend kernel, publish kernel);
+    # lr = 0 makes it pure gossip: replicas contract
+    if np_ > 1:
+        for mixed in (False, True):
+            m = make()
+            if mixed:
+                m[2] = m[2].to(torch.bfloat16)  # two dtypes -> two arenas, one snapshot
+            for p in m.parameters():
+                p.data += 0.1 * rank
+            opt = kf.optimizers.PairAveragingOptimizer(torch.optim.SGD(m.parameters(), lr=0.0), m.named_parameters())
+            first = next(m.parameters())
+            w0 = kf.ops.all_gather(first.data.clone())
+            for step in range(12):
+                opt.step()
+            torch.cuda.synchronize()
+            kf.run_barrier()
+            assert opt._kf_gen is not None, 'the device path must have been taken'
+            w1 = kf.ops.all_gather(first.data.clone())
+            spread0 = float((w0.max(0).values - w0.min(0).values).max())
+            spread1 = float((w1.max(0).values - w1.min(0).values).max())
+            assert spread1 < 0.5 * spread0, (mixed, spread0, spread1)
+        if rank == 0:
+            print('PairAveraging (torch optimizer, device path) ok', flush=True)
     # PairAveraging fused: one-sided pulls, no barrier
     m = make()
     opt = kf.optimizers.PairAveragingOptimizer(FusedSGD(m.parameters(), lr=0.05), m.named_parameters())
@@ -177,8 +311,9 @@ def check_fused_optimizers():
     torch.cuda.synchronize()
     assert all(torch.isfinite(p).all() for p in m.parameters())
     kf.run_barrier()
+    torn = kf.ops.all_reduce_fn(opt.torn_reads.to(torch.int64).cpu(), 'sum')
     if rank == 0:
-        print('SMA / PairAveraging ok; torn reads', int(opt.torn_reads), flush=True)
+        print('PairAveraging fused ok; torn reads (all ranks)', int(torn), flush=True)
     # PairAveraging with the peer drawn ON THE DEVICE: the whole step (forward, backward, pull + blend +
     # update + publish) is one CUDA graph; lr = 0 makes it pure gossip averaging, so replicas must contract
     if np_ > 1:
@@ -212,7 +347,7 @@ def check_fused_optimizers():
             graph.replay()
         torch.cuda.synchronize()
         kf.run_barrier()
-        assert int(opt._kf_step_t) == 3 + 8, int(opt._kf_step_t)
+        assert int(opt._step_t) == 3 + 8, int(opt._step_t)
         w1 = kf.ops.all_gather(first.data.clone())
         spread0 = float((w0.max(0).values - w0.min(0).values).max())
         spread1 = float((w1.max(0).values - w1.min(0).values).max())
@@ -231,6 +366,25 @@ def check_fused_optimizers():
         opt.step()
     if np_ > 1:
         assert opt.noise_scale is not None and torch.isfinite(opt.noise_scale)
+        plain = float(opt.noise_scale)
+        # the same monitor on the overlapped (bucketed) step: norms come from per-bucket slots
+        for inner_kind in ('fused', 'torch'):
+            m = make()
+            if inner_kind == 'fused':
+                inner = FusedSGD(m.parameters(), lr=0.05, bucket_bytes=8000)
+            else:
+                inner = torch.optim.SGD(m.parameters(), lr=0.05)
+            opt = kf.optimizers.MonitorGradientNoiseScaleOptimizer(inner, m.named_parameters(), device_batch_size=32,
+                                                                   overlap=True)
+            if inner_kind == 'torch':
+                opt._kf_sync.bucket_bytes = 8000
+            for step in range(3):
+                x, y = batch(rank, step)
+                opt.zero_grad(set_to_none=True)
+                torch.nn.functional.cross_entropy(m(x), y).backward()
+                opt.step()
+            got = float(opt.noise_scale)
+            assert abs(got - plain) <= 1e-4 * abs(plain), (inner_kind, got, plain)
     m = make()
     opt = kf.optimizers.MonitorGradientVarianceOptimizer(torch.optim.SGD(m.parameters(), lr=0.05), m.named_parameters())
     x, y = batch(rank, 0)
