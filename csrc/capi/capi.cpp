@@ -193,6 +193,16 @@ int64_t kf_broadcast_async(kf_peer *p, const void *send, void *recv, int64_t cou
 
 int kf_wait_handle(kf_peer *p, int64_t handle) { return done(p, p->peer->wait(handle)); }
 
+int kf_submit(kf_peer *p, int (*fn)(void *), void *arg, void (*on_done)(void *, int))
+{
+    if (!p || !fn) return fail("kf_submit: null argument");
+    p->peer->submit_detached([fn, arg, on_done] {
+        const int rc = fn(arg);
+        if (on_done) on_done(arg, rc);
+    });
+    return 0;
+}
+
 int kf_save(kf_peer *p, const char *version, const char *name, const void *data, int64_t nbytes)
 {
     p->peer->save(version ? version : "", name, data, (size_t)nbytes);

@@ -7,6 +7,7 @@
 #include <unistd.h>
 
 #include "core/log.hpp"
+#include "core/platforms.hpp"
 
 namespace kf {
 
@@ -24,6 +25,22 @@ bool PeerConfig::from_env(PeerConfig *out, std::string *err)
     }
     const std::string self = getenv_str(env::kSelfSpec);
     if (self.empty()) {
+        // a hosting platform may describe the cluster instead of kungfu-run
+        PeerList platform_peers;
+        int task        = 0;
+        std::string perr;
+        const int found = modelarts_cluster(&platform_peers, &task, &perr);
+        if (found < 0) {
+            if (err) *err = "ModelArts environment: " + perr;
+            return false;
+        }
+        if (found > 0 && platform_peers.size() > 1) {
+            c.single     = false;
+            c.init_peers = platform_peers;
+            c.self       = platform_peers[task];
+            *out         = c;
+            return true;
+        }
         // not launched by kungfu-run: one process, rank 0 of 1
         c.single = true;
         parse_peer_id("127.0.0.1:0", &c.self);
@@ -374,6 +391,7 @@ void Peer::async_loop()
             async_q_.pop_front();
         }
         const bool ok = job.second();
+        if (job.first == 0) continue;  // fire-and-forget job: its own completion callback reports
         {
             std::lock_guard<std::mutex> lk(async_mu_);
             async_done_[job.first] = ok;
@@ -389,6 +407,16 @@ int64_t Peer::submit(std::function<bool()> op)
     async_q_.emplace_back(h, std::move(op));
     async_cv_.notify_all();
     return h;
+}
+
+void Peer::submit_detached(std::function<void()> op)
+{
+    std::lock_guard<std::mutex> lk(async_mu_);
+    async_q_.emplace_back(0, [op] {
+        op();
+        return true;
+    });
+    async_cv_.notify_all();
 }
 
 bool Peer::wait(int64_t handle)

@@ -113,6 +113,9 @@ class Peer
     // async: returns a handle; wait() reports the op's success
     int64_t submit(std::function<bool()> op);
     bool wait(int64_t handle);
+    // runs op on the same worker pool; nothing is recorded (the op reports its own completion).
+    // Jobs queued before close() are still run: the destructor drains the queue, then joins.
+    void submit_detached(std::function<void()> op);
 
     std::vector<float> egress_rates();
 };

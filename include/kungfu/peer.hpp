@@ -6,10 +6,11 @@
 // apply f there, broadcast the result (/root/reference/srcs/cpp/src/session.cpp:162-181).
 #pragma once
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <functional>
 #include <stdexcept>
 #include <string>
-#include <thread>
 #include <vector>
 
 #include "../kungfu_host.h"
@@ -31,12 +32,42 @@ class Peer
         if (rc != 0) throw std::runtime_error(std::string(what) + ": " + kf_last_error());
     }
 
-    template <typename F> void async(F f, DoneCallback done)
+    // Callback overloads run on the runtime's own worker threads (kf_submit): the op's return code is
+    // checked there, and ~Peer() (kf_peer_close) runs what is still queued and joins those threads, so
+    // no operation can outlive the object it captured. A failed asynchronous operation is handed to the
+    // error handler; the default prints the runtime's message and exits, which is what the reference
+    // did for any failed op (/root/reference/srcs/go/libkungfu-comm/main.go:163-187).
+    struct Job {
+        std::function<int()> op;
+        DoneCallback done;
+        const char *what;
+        Peer *self;
+    };
+    std::function<void(int, const char *)> on_error_;
+
+    static int run_job(void *arg) { return static_cast<Job *>(arg)->op(); }
+    static void end_job(void *arg, int rc)
     {
-        std::thread([f, done] {
-            f();
-            if (done) done();
-        }).detach();
+        Job *j = static_cast<Job *>(arg);
+        if (rc != 0) j->self->fail_async(rc, j->what);
+        else if (j->done) j->done();
+        delete j;
+    }
+    void fail_async(int rc, const char *what)
+    {
+        if (on_error_) {
+            on_error_(rc, what);
+            return;
+        }
+        std::fprintf(stderr, "[kungfu] asynchronous %s failed (%d): %s\n", what, rc, kf_last_error());
+        std::exit(1);
+    }
+    template <typename F> int async(const char *what, F f, DoneCallback done)
+    {
+        Job *j = new Job{std::function<int()>(f), std::move(done), what, this};
+        const int rc = kf_submit(p_, &Peer::run_job, j, &Peer::end_job);
+        if (rc != 0) delete j;
+        return rc;
     }
 
   public:
@@ -57,7 +88,12 @@ class Peer
     bool Detached() const { return kf_detached(p_) != 0; }
 
     int Barrier() { return kf_barrier(p_); }
-    int Barrier(DoneCallback done) { async([this] { kf_barrier(p_); }, done); return 0; }
+    int Barrier(DoneCallback done)
+    {
+        return async("Barrier", [this] { return kf_barrier(p_); }, done);
+    }
+    // what to do when a callback-style operation fails (default: print and exit(1))
+    void SetAsyncErrorHandler(std::function<void(int, const char *)> h) { on_error_ = std::move(h); }
 
     int AllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
     {
@@ -66,8 +102,7 @@ class Peer
     int AllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const char *name, DoneCallback done)
     {
         std::string n(name);
-        async([=] { kf_all_reduce(p_, send, recv, count, dtype, op, n.c_str()); }, done);
-        return 0;
+        return async("AllReduce", [=] { return kf_all_reduce(p_, send, recv, count, dtype, op, n.c_str()); }, done);
     }
     // all-reduce along `tree` (father array of Size() entries, nullptr = active strategy) that also feeds the
     // per-strategy throughput statistics CheckInterference() votes on
@@ -81,15 +116,14 @@ class Peer
     {
         std::string n(name);
         std::vector<int32_t> t(tree ? tree : nullptr, tree ? tree + Size() : nullptr);
-        async([=] { kf_monitored_all_reduce(p_, send, recv, count, dtype, op, t.empty() ? nullptr : t.data(), (int)t.size(), n.c_str()); },
-              done);
-        return 0;
+        return async("MonitoredAllReduce", [=] {
+            return kf_monitored_all_reduce(p_, send, recv, count, dtype, op, t.empty() ? nullptr : t.data(), (int)t.size(), n.c_str());
+        }, done);
     }
     // runs `done` on the runtime's callback path without doing any communication (ordering / wake-up hook)
     int Noop(DoneCallback done)
     {
-        async([] {}, done);
-        return 0;
+        return async("Noop", [] { return 0; }, done);
     }
     int CrossAllReduce(const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
     {
@@ -106,8 +140,7 @@ class Peer
     int Broadcast(const void *send, void *recv, int64_t count, int dtype, const char *name, DoneCallback done)
     {
         std::string n(name);
-        async([=] { kf_broadcast(p_, send, recv, count, dtype, n.c_str()); }, done);
-        return 0;
+        return async("Broadcast", [=] { return kf_broadcast(p_, send, recv, count, dtype, n.c_str()); }, done);
     }
     int LocalReduce(const void *send, void *recv, int64_t count, int dtype, int op, const char *name)
     {
@@ -158,8 +191,7 @@ class Peer
     int Request(int rank, const char *name, void *buf, int64_t nbytes, DoneCallback done)
     {
         std::string n(name);
-        async([=] { kf_request(p_, rank, nullptr, n.c_str(), buf, nbytes); }, done);
-        return 0;
+        return async("Request", [=] { return kf_request(p_, rank, nullptr, n.c_str(), buf, nbytes); }, done);
     }
 
     // control / adaptation / monitoring

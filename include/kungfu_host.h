@@ -53,6 +53,11 @@ int kf_consensus(kf_peer *p, const void *data, int64_t nbytes, const char *name,
 int64_t kf_all_reduce_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, int op, const char *name);
 int64_t kf_broadcast_async(kf_peer *p, const void *send, void *recv, int64_t count, int dtype, const char *name);
 int kf_wait_handle(kf_peer *p, int64_t handle);
+/* Run fn(arg) on the runtime's worker threads, then on_done(arg, rc) on the same thread (may be NULL).
+ * This is the path behind the callback overloads of kungfu::Peer (the reference ran them on the Go
+ * runtime's goroutines, srcs/go/libkungfu-comm/main.go:163-187). kf_peer_close() runs every job
+ * that was queued before it and joins the workers, so no job outlives the peer. */
+int kf_submit(kf_peer *p, int (*fn)(void *), void *arg, void (*on_done)(void *, int));
 
 /* p2p model store; version may be NULL (unversioned). kf_request returns 0 iff found. */
 int kf_save(kf_peer *p, const char *version, const char *name, const void *data, int64_t nbytes);

@@ -35,6 +35,12 @@ from ..parallel.flat import build_arenas
 OVERLAP_CHANNEL = 2
 
 
+def _record_step(comm, algo, nbytes, stream):
+    st = getattr(comm, 'stats', None)
+    if st is not None:
+        st.record(algo, nbytes, stream)
+
+
 class _Bucket(object):
     __slots__ = ('group', 'arena', 'idx', 'lo', 'hi', 'slot', 'pending')
 
@@ -65,12 +71,19 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.use_nvls = os.environ.get('KUNGFU_FUSED_NVLS', '1') != '0'
         self.nvls_min_bytes = int(os.environ.get('KUNGFU_FUSED_NVLS_MIN_BYTES', str(256 << 10)))
         self.last_algo = None  # 'nvls' | 'p2p' | 'local': what the last sync step ran
+        self.step_algos = []
+        self._algos = set()
         # overlapped (bucketed) synchronous step
         self.overlap = bool(overlap)
         self.bucket_bytes = int(bucket_bytes or os.environ.get('KUNGFU_BUCKET_BYTES', self.BUCKET_BYTES))
         self._ov_average = True
         self._ov_sync = False
         self._ov = None
+        # CTAs of a bucket kernel that runs UNDER backward. They may sit at the entry barrier for as
+        # long as the ranks are skewed, and every resident CTA takes a slot away from the one-wave
+        # grids of the model kernels, so hidden buckets get few CTAs (they only have to finish
+        # before backward does); the last bucket, whose time is exposed, gets the full set.
+        self.hidden_blocks = int(os.environ.get('KUNGFU_OVERLAP_BLOCKS', '8'))
 
     # -- arenas -------------------------------------------------------------------------
     @property
@@ -169,7 +182,8 @@ class FusedOptimizer(torch.optim.Optimizer):
         return C.byref(self._local)
 
     # -- one fused launch over [lo, hi) of an arena ----------------------------------------
-    def _launch_range(self, g, a, lo, hi, sync, grad_scale, ss_g, cstruct, blocks, threads, stream):
+    def _launch_range(self, g, a, lo, hi, sync, grad_scale, ss_g, cstruct, blocks, threads, stream,
+                      local_blocks=None):
         comm = self.comm
         a.ensure_master(slots=self._n_slots())
         h = self._hyper(g, a, lo)
@@ -184,26 +198,28 @@ class FusedOptimizer(torch.optim.Optimizer):
             raise K.KungFuCudaError('KUNGFU_REQUIRE_NVLS=1 but the fused step has no multicast alias to run on')
         if use_nvls:
             # the switch reduces the gradient shard and multicasts the new parameters
-            self.last_algo = 'nvls'
+            self._algos.add('nvls')
             K.call('kfb_ssgd_fused_step_nvls', cstruct, a.grads_buf.mc_ptr + go, a.code,
                    a.params_buf.mc_ptr + go, a.code, a.master.data_ptr() + mo, a.mom.data_ptr() + mo, count,
                    float(grad_scale), C.byref(h), ssp, min(blocks, 32), threads, K.stream_ptr(stream))
+            _record_step(comm, K.ALGO_NVLS, count * esz, stream)
             return
         if multi:
-            self.last_algo = 'p2p'
+            self._algos.add('p2p')
+            _record_step(comm, K.ALGO_TWOSHOT, count * esz, stream)
             ga, _k1 = a.grads_buf.ptr_array(go)
             pa, _k2 = a.params_buf.ptr_array(go)
             cs = cstruct
             step_blocks = blocks
         else:
-            self.last_algo = 'local'
+            self._algos.add('local')
             me = max(comm.rank, 0)
             ga, _k1 = K.ptr_array([a.grads_buf.ptrs[me] + go])
             pa, _k2 = K.ptr_array([a.params_buf.ptrs[me] + go])
             cs = self._local_struct()
             # a purely local update is HBM-bound, not NVLink-bound: it needs every SM it can
             # get (the comm default of 32 CTAs reaches ~1.7 TB/s; 128 is the flag-slot limit)
-            step_blocks = self.local_blocks
+            step_blocks = local_blocks or self.local_blocks
         if comm.emulated and (lo != 0 or hi != a.count):
             raise K.KungFuCudaError('bucketed steps are not available under single-GPU rank emulation')
         K.call('kfb_ssgd_fused_step', cs, ga, a.code, pa, a.code, a.master.data_ptr() + mo,
@@ -242,6 +258,13 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.sumsq_global = self._ss_out[1]
 
     def _after_step(self):
+        # the most capable path any launch of this step took
+        for name in ('nvls', 'p2p', 'local'):
+            if name in self._algos:
+                self.last_algo = name
+                break
+        self.step_algos = sorted(self._algos)
+        self._algos = set()
         self._steps += 1
         self._step_t.add_(1)
 
@@ -383,9 +406,12 @@ class FusedOptimizer(torch.optim.Optimizer):
         n = comm.np
         scale = (1.0 / n) if (sync and self._ov_average) else 1.0
         blocks = comm.channel_blocks(OVERLAP_CHANNEL, self._blocks)
+        last = b.slot == len(ov['buckets']) - 1
+        if not last:
+            blocks = min(blocks, self.hidden_blocks)
         threads = self._threads or comm.default_threads
         self._launch_range(b.group, a, b.lo, b.hi, sync, scale, ss_g, comm.channel(OVERLAP_CHANNEL), blocks,
-                           threads, side)
+                           threads, side, local_blocks=None if last else self.hidden_blocks * 4)
 
     def _finish_overlap(self):
         ov = self._ov

@@ -158,8 +158,10 @@ class _CommBase(object):
         if self.np > 1:
             K.call('kfb_barrier', self.cstruct, K.stream_ptr(stream))
 
-    def close(self):
-        pass
+    def close(self, collective=True):
+        self.closed = True
+        self._keep = []
+        self._channels = {}
 
 
 class LocalComm(_CommBase):

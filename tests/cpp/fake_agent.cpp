@@ -110,6 +110,28 @@ int main()
         CHECK(z[500] == y[0]);
         peer.CalcStats();
     }
+    // a callback-style operation that fails reports through the error handler (not silently, not by a
+    // dangling thread): ask for a blob nobody saved
+    if (np > 1) {
+        kungfu::Latch failed(1);
+        int seen_rc = 0;
+        peer.SetAsyncErrorHandler([&](int rc, const char *) {
+            seen_rc = rc;
+            failed.done();
+        });
+        float buf4[4];
+        bool called = false;
+        CHECK(peer.Request((rank + 1) % np, "nobody-saved-this", buf4, sizeof(buf4), [&] { called = true; }) == 0);
+        failed.wait();
+        CHECK(seen_rc != 0 && !called);
+        peer.SetAsyncErrorHandler(nullptr);
+    }
+    // operations still queued when the Peer goes away are run and joined by its destructor
+    {
+        static int32_t late_one = 1, late_sum = 0;
+        peer.Barrier();
+        peer.AllReduce(&late_one, &late_sum, 1, kungfu::I32, kungfu::SUM, "late-async", [] {});
+    }
     peer.Barrier();
     printf("OK fake-agent rank %d/%d\n", rank, np);
     return 0;

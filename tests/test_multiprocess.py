@@ -166,3 +166,35 @@ def test_workers_survive_garbage_and_hostile_headers_on_their_ports(tmp_path):
             run.kill()
     assert run.returncode == 0, log[-3000:]
     assert log.count('OK survived') == 2
+
+
+def test_modelarts_environment_describes_the_cluster():
+    import sys
+    """No kungfu-run: two tasks find each other through the ModelArts variables
+    (DLS_TASK_INDEX / DLS_TASK_NUMBER / BATCH_CUSTOM<i>_HOSTS), one of them by host name
+    (reference: srcs/go/platforms/modelarts/modelarts.go:25-115)."""
+    import subprocess
+    base = 21000 + (os.getpid() * 13) % 9000
+    code = ('import torch, kungfu_b200.torch as kf\n'
+            'x = kf.ops.all_reduce_fn(torch.tensor([float(kf.current_rank() + 1)]))\n'
+            'assert kf.current_cluster_size() == 2 and float(x) == 3.0, (kf.current_cluster_size(), x)\n'
+            'kf.run_barrier()\n'
+            'print("OK modelarts rank", kf.current_rank())\n')
+    procs = []
+    for t in range(2):
+        env = dict(os.environ, PYTHONPATH=ROOT, DLS_TASK_INDEX=str(t), DLS_TASK_NUMBER='2',
+                   BATCH_CUSTOM0_HOSTS='127.0.0.1:%d' % base, BATCH_CUSTOM1_HOSTS='localhost:%d' % (base + 1))
+        for k in [k for k in env if k.startswith('KUNGFU_')]:
+            del env[k]
+        procs.append(subprocess.Popen([sys.executable, '-c', code], stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                                      text=True, env=env))
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), '\n'.join(outs)
+    assert sorted(o.strip().splitlines()[-1] for o in outs) == ['OK modelarts rank 0', 'OK modelarts rank 1']
+    # unusable variables are an error, not a silent single-process run
+    env = dict(os.environ, PYTHONPATH=ROOT, DLS_TASK_INDEX='0', DLS_TASK_NUMBER='2', BATCH_CUSTOM0_HOSTS='127.0.0.1:%d' % base)
+    for k in [k for k in env if k.startswith('KUNGFU_')]:
+        del env[k]
+    r = subprocess.run([sys.executable, '-c', code], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env,
+                       timeout=60)
+    assert r.returncode != 0 and 'BATCH_CUSTOM1_HOSTS' in r.stdout, r.stdout
