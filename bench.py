@@ -58,6 +58,9 @@ def parse_args():
                     help='after the timed region, also time stock PyTorch (torchvision-style ResNet-50, torch BN, '
                          'torch.optim.SGD, DistributedDataParallel over NCCL) with the same protocol')
     ap.add_argument('--baseline-steps', type=int, default=10)
+    ap.add_argument('--trace', action='store_true',
+                    help='after the measurement, replay 4 steps under torch.profiler and print where the communication '
+                         'kernels sit on the timeline of rank 0 (diagnostic; never part of a reported number)')
     return ap.parse_args()
 
 
@@ -156,6 +159,41 @@ def correctness_check(kf, K, opt, dev, rank, np_):
     out['fused_step_max_err'] = float((w.detach().float() - want).abs().max())
     out['fused_step_algo'] = chk.last_algo
     return out
+
+
+def trace_steps(run_step, rank, kf):
+    import tempfile
+
+    import torch
+    kf.run_barrier()
+    with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) as prof:
+        for _ in range(4):
+            run_step()
+        torch.cuda.synchronize()
+    kf.run_barrier()
+    path = os.path.join(tempfile.gettempdir(), 'kf_trace_%d.json' % rank)
+    prof.export_chrome_trace(path)
+    ev = [e for e in json.load(open(path))['traceEvents'] if e.get('cat') == 'kernel']
+    ev.sort(key=lambda e: e['ts'])
+    if rank != 0 or not ev:
+        return
+    # steps are separated by the stem convolution's first kernel; use the fused-step kernels as anchors instead:
+    # report, per occurrence of each of our communication / optimizer kernels, start offset and duration
+    ours = [e for e in ev if 'ssgd_fused' in e['name'] or 'k_fuse' in e['name'] or 'k_sum_slots' in e['name']]
+    t0 = ev[0]['ts']
+    span = ev[-1]['ts'] + ev[-1]['dur'] - t0
+    busy = sum(e['dur'] for e in ev)
+    print('[trace] 4 steps: span %.3f ms/step, sum of kernel durations %.3f ms/step, %d kernels/step' %
+          (span / 4e3, busy / 4e3, len(ev) // 4), file=sys.stderr)
+    last_model = None
+    for e in ev:
+        if e in ours:
+            name = e['name'].split('<')[0].split('(')[0][-28:]
+            gap = (e['ts'] - (last_model['ts'] + last_model['dur'])) if last_model else 0.0
+            print('[trace] %-28s start %9.3f ms  dur %8.1f us  (%.1f us after the previous model kernel ended)' %
+                  (name, (e['ts'] - t0) / 1e3, e['dur'], gap), file=sys.stderr)
+        else:
+            last_model = e
 
 
 def ddp_baseline(args, kf, dev, rank, np_, local_rank):
@@ -352,6 +390,8 @@ def main():
                'd2h_bytes_per_step': loss_host.element_size(), 'ms_per_step': e2e_ms / args.steps,
                'loss': float(loss_host)}
 
+    if args.trace:
+        trace_steps(run_step, rank, kf)
     check = correctness_check(kf, K, opt, dev, rank, np_)
     baseline = None
     if args.same_box_baseline == 'ddp':

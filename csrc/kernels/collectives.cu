@@ -565,6 +565,66 @@ __global__ void __launch_bounds__(512)
         st_stream16(dst + i, ld_stream16(src + i));
 }
 
+// ---- a whole strategy walk in ONE launch --------------------------------------------
+// The reference walks (reduce graph, broadcast graph) per chunk on the host,
+// receiving from `prevs` and sending to `nexts`
+// (/root/reference/srcs/go/kungfu/session/session.go:218-286). Here the graphs
+// are compiled (parallel/planner.py) into rounds of incoming edges per rank:
+// in round r a rank pulls from the sources of its round-r edges, reducing onto
+// (reduce phase) or overwriting (broadcast phase) its own chunk; a peer
+// barrier separates rounds, because a source's chunk is final only once the
+// source finished its own earlier rounds. CTA b of every rank always handles
+// the same grid-stride slice of every chunk, so the per-CTA barrier of
+// common.cuh is all the ordering the walk needs.
+#define KFB_GRAPH_MAX_ROUNDS 64
+#define KFB_GRAPH_MAX_EDGES 320
+#define KFB_GRAPH_MAX_PLANS 16
+struct GraphArgs {
+    PeerPads pads;
+    uint32_t *local_epoch;
+    void *bufs[KFB_MAX_RANKS];
+    int rank, np;
+    int n_rounds, n_reduce_rounds;
+    int round_begin[KFB_GRAPH_MAX_ROUNDS + 1];  // edges of round r: [round_begin[r], round_begin[r+1])
+    unsigned char edge_plan[KFB_GRAPH_MAX_EDGES];
+    unsigned char edge_src[KFB_GRAPH_MAX_EDGES];
+    long long chunk_lo[KFB_GRAPH_MAX_PLANS];  // in 16-byte vectors
+    long long chunk_n[KFB_GRAPH_MAX_PLANS];
+};
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(512)
+    k_graph_allreduce(const __grid_constant__ GraphArgs a)
+{
+    using P                = Pack<T>;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long first  = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    uint4 *mine            = reinterpret_cast<uint4 *>(a.bufs[a.rank]);
+    for (int r = 0; r < a.n_rounds; ++r) {
+        peer_barrier(a.pads, a.local_epoch, a.rank, a.np, blockIdx.x);
+        for (int e = a.round_begin[r]; e < a.round_begin[r + 1]; ++e) {
+            const int pl       = a.edge_plan[e];
+            const uint4 *src   = reinterpret_cast<const uint4 *>(a.bufs[a.edge_src[e]]) + a.chunk_lo[pl];
+            uint4 *dst         = mine + a.chunk_lo[pl];
+            const long long nv = a.chunk_n[pl];
+            if (r < a.n_reduce_rounds) {
+                for (long long i = first; i < nv; i += stride) {
+                    typename P::acc_t x[P::N], y[P::N];
+                    P::unpack(ld_stream16(dst + i), x);
+                    P::unpack(ld_stream16(src + i), y);
+#pragma unroll
+                    for (int k = 0; k < P::N; ++k) x[k] = apply_op<OP>(x[k], y[k]);
+                    st_stream16(dst + i, P::pack(x));
+                }
+            } else {
+                for (long long i = first; i < nv; i += stride) st_stream16(dst + i, ld_stream16(src + i));
+            }
+        }
+    }
+    // nobody may overwrite its buffer while a child still pulls from it
+    peer_barrier(a.pads, a.local_epoch, a.rank, a.np, blockIdx.x);
+}
+
 // ---- host side ------------------------------------------------------------------
 static size_t dtype_size(int dt)
 {
@@ -898,6 +958,78 @@ extern "C" int kfb_consensus(const kfb_comm *comm, void *const *in,
     KFB_CUDA_OK(cudaGetLastError());
     return launch(comm, k_consensus, blocks, threads,
                   reinterpret_cast<cudaStream_t>(stream), m, agree_out);
+}
+
+extern "C" int kfb_graph_allreduce(const kfb_comm *comm, void *const *bufs, int dtype, int op, int n_plans,
+                                   const int64_t *chunk_lo_bytes, const int64_t *chunk_bytes, int n_rounds,
+                                   int n_reduce_rounds, const int32_t *round_begin, const int32_t *edge_plan,
+                                   const int32_t *edge_src, int blocks, int threads, void *stream)
+{
+    int rc = check_comm(comm, blocks, threads);
+    if (rc) return rc;
+    if (comm->rank < 0) {
+        set_last_error("kfb_graph_allreduce: needs real ranks (the edge tables are per rank)");
+        return KFB_ERR_ARG;
+    }
+    if (n_plans < 1 || n_plans > KFB_GRAPH_MAX_PLANS || n_rounds < 0 || n_rounds > KFB_GRAPH_MAX_ROUNDS ||
+        n_reduce_rounds < 0 || n_reduce_rounds > n_rounds || round_begin[n_rounds] > KFB_GRAPH_MAX_EDGES) {
+        set_last_error("kfb_graph_allreduce: graph too large (plans %d/%d rounds %d/%d edges %d/%d)", n_plans,
+                       KFB_GRAPH_MAX_PLANS, n_rounds, KFB_GRAPH_MAX_ROUNDS, n_rounds >= 0 ? round_begin[n_rounds] : -1,
+                       KFB_GRAPH_MAX_EDGES);
+        return KFB_ERR_ARG;
+    }
+    if (!dtype_size(dtype)) {
+        set_last_error("unsupported dtype %d", dtype);
+        return KFB_ERR_ARG;
+    }
+    GraphArgs a;
+    memset(&a, 0, sizeof(a));
+    fill_pads(a.pads, comm);
+    a.local_epoch = reinterpret_cast<uint32_t *>(comm->local_epoch);
+    for (int r = 0; r < comm->np; ++r) a.bufs[r] = bufs[r];
+    a.rank            = comm->rank;
+    a.np              = comm->np;
+    a.n_rounds        = n_rounds;
+    a.n_reduce_rounds = n_reduce_rounds;
+    for (int r = 0; r <= n_rounds; ++r) a.round_begin[r] = round_begin[r];
+    for (int e = 0; e < round_begin[n_rounds]; ++e) {
+        if (edge_plan[e] < 0 || edge_plan[e] >= n_plans || edge_src[e] < 0 || edge_src[e] >= comm->np) {
+            set_last_error("kfb_graph_allreduce: edge %d out of range", e);
+            return KFB_ERR_ARG;
+        }
+        a.edge_plan[e] = (unsigned char)edge_plan[e];
+        a.edge_src[e]  = (unsigned char)edge_src[e];
+    }
+    for (int i = 0; i < n_plans; ++i) {
+        if (chunk_lo_bytes[i] % 16) {
+            set_last_error("kfb_graph_allreduce: chunks must start on 16-byte boundaries");
+            return KFB_ERR_ARG;
+        }
+        a.chunk_lo[i] = chunk_lo_bytes[i] / 16;
+        a.chunk_n[i]  = (chunk_bytes[i] + 15) / 16;
+    }
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define KFB_GRAPH(T)                                                           \
+    switch (op) {                                                              \
+    case KFB_OP_SUM: k_graph_allreduce<T, KFB_OP_SUM><<<blocks, threads, 0, s>>>(a); break;   \
+    case KFB_OP_MIN: k_graph_allreduce<T, KFB_OP_MIN><<<blocks, threads, 0, s>>>(a); break;   \
+    case KFB_OP_MAX: k_graph_allreduce<T, KFB_OP_MAX><<<blocks, threads, 0, s>>>(a); break;   \
+    case KFB_OP_PROD: k_graph_allreduce<T, KFB_OP_PROD><<<blocks, threads, 0, s>>>(a); break; \
+    default: set_last_error("bad op %d", op); return KFB_ERR_ARG;              \
+    }                                                                          \
+    break;
+    switch (dtype) {
+    case KFB_F32: KFB_GRAPH(float)
+    case KFB_BF16: KFB_GRAPH(__nv_bfloat16)
+    case KFB_F16: KFB_GRAPH(__half)
+    case KFB_I32: KFB_GRAPH(int32_t)
+    case KFB_F64: KFB_GRAPH(double)
+    case KFB_I64: KFB_GRAPH(int64_t)
+    case KFB_U8: KFB_GRAPH(uint8_t)
+    }
+#undef KFB_GRAPH
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
 }
 
 extern "C" int kfb_edge_reduce(void *dst, const void *src, int64_t count,

@@ -127,6 +127,22 @@ int kfb_edge_reduce(void *dst, const void *src, int64_t count, int dtype,
 int kfb_edge_copy(void *dst, const void *src, int64_t bytes, int blocks,
                   int threads, void *stream);
 
+/* A whole strategy walk (reduce graph then broadcast graph, several graph pairs
+ * over chunks of the buffer) in ONE launch: in round r this rank pulls from
+ * edge_src[e] for e in [round_begin[r], round_begin[r+1]) into chunk
+ * edge_plan[e] of its own buffer, reducing onto it while r < n_reduce_rounds
+ * and overwriting it afterwards; peer barriers separate the rounds. bufs[r]:
+ * rank r's buffer as mapped here; chunk i covers chunk_bytes[i] bytes at
+ * chunk_lo_bytes[i] (16-byte aligned). The tables are this rank's view,
+ * compiled by parallel/planner.py from the strategy's graphs.
+ * (srcs/go/kungfu/session/session.go:218-313) */
+int kfb_graph_allreduce(const kfb_comm *comm, void *const *bufs, int dtype,
+                        int op, int n_plans, const int64_t *chunk_lo_bytes,
+                        const int64_t *chunk_bytes, int n_rounds,
+                        int n_reduce_rounds, const int32_t *round_begin,
+                        const int32_t *edge_plan, const int32_t *edge_src,
+                        int blocks, int threads, void *stream);
+
 /* ---- multi-tensor helpers (replace K13 fuse/defuse + K17 local norm) ----- */
 
 /* Copy+cast n tensors into one flat buffer (the symmetric bucket) and

@@ -92,6 +92,9 @@ _SIGS = {
     'kfb_gather': (C.c_int, [C.POINTER(KfbComm), C.c_int, _PTRS, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
     'kfb_barrier': (C.c_int, [C.POINTER(KfbComm), C.c_void_p]),
     'kfb_consensus': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int64, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_graph_allreduce': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, C.c_int, C.c_int, _I64S, _I64S, C.c_int, C.c_int,
+                                      C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_int,
+                                      C.c_void_p]),
     'kfb_edge_reduce': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     'kfb_edge_copy': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p]),
     'kfb_fuse': (C.c_int, [_PTRS, _I64S, _I64S, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -203,6 +206,11 @@ def ptr_array(ptrs):
 def i64_array(vals):
     arr = (C.c_int64 * len(vals))(*[int(v) for v in vals])
     return C.cast(arr, _I64S), arr
+
+
+def i32_array(vals):
+    arr = (C.c_int32 * max(1, len(vals)))(*[int(v) for v in vals])
+    return C.cast(arr, C.POINTER(C.c_int32)), arr
 
 
 def dtype_code(dt):

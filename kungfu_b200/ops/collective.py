@@ -21,12 +21,15 @@ ONESHOT_MAX_BYTES = 256 << 10
 # large-message variant installed by parallel.planner.VariantChooser (None = built-in preference)
 PREFERRED_LARGE = None
 
+# Fault injection for the interference vote (tests, examples/adapt_strategy.py): the variant with
+# this code runs on a single CTA, i.e. at a fraction of its bandwidth, until it is set back to None.
+SLOW_VARIANT = None
 
-def _record(comm, algo, nbytes, stream):
-    """Feed the device traffic statistics (parallel/devstats.py)."""
-    st = getattr(comm, 'stats', None)
-    if st is not None:
-        st.record(algo, nbytes, stream)
+
+def variant_blocks(comm, algo, channel=0, blocks=None):
+    if SLOW_VARIANT is not None and algo == SLOW_VARIANT:
+        return 1
+    return comm.channel_blocks(channel, blocks)
 
 
 def choose_algo(comm, nbytes, buf=None, op=K.OP_SUM, dtype=K.F32):
@@ -67,12 +70,15 @@ def all_reduce(comm, buf, count, dtype, op='sum', scale=1.0, algo=None, out=None
     out_arr, _k2 = out.ptr_array(out_byte_offset)
     mc_in = (buf.mc_ptr + byte_offset) if buf.mc_ptr else None
     mc_out = (out.mc_ptr + out_byte_offset) if out.mc_ptr else None
+    st = getattr(comm, 'stats', None)
+    ev0 = st.begin(stream) if st is not None else None
     K.call('kfb_allreduce', comm.channel(channel), algo, in_arr, out_arr, mc_in, mc_out,
            count, code, opc, float(scale),
            sumsq_out.data_ptr() if sumsq_out is not None else None,
-           comm.channel_blocks(channel, blocks), threads or comm.default_threads,
+           variant_blocks(comm, algo, channel, blocks), threads or comm.default_threads,
            K.stream_ptr(stream))
-    _record(comm, algo, nbytes, stream)
+    if st is not None:
+        st.end(ev0, algo, nbytes, stream)
     return out
 
 

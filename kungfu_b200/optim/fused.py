@@ -35,10 +35,17 @@ from ..parallel.flat import build_arenas
 OVERLAP_CHANNEL = 2
 
 
-def _record_step(comm, algo, nbytes, stream):
+def _record_step(comm, algo, nbytes, stream, ev0=None):
+    """Feed the device traffic statistics (parallel/devstats.py): a fused step moves the same bytes
+    over NVLink as the all-reduce variant it is built on."""
     st = getattr(comm, 'stats', None)
     if st is not None:
-        st.record(algo, nbytes, stream)
+        st.end(ev0, algo, nbytes, stream)
+
+
+def _begin_step(comm, stream):
+    st = getattr(comm, 'stats', None)
+    return st.begin(stream) if st is not None else None
 
 
 class _Bucket(object):
@@ -192,25 +199,29 @@ class FusedOptimizer(torch.optim.Optimizer):
         go, mo = lo * esz, lo * 4
         ssp = ss_g.data_ptr() if ss_g is not None else None
         multi = sync and comm.np > 1 and not comm.cross
+        from ..ops import collective as coll
         use_nvls = (multi and a.grads_buf.mc_ptr and a.params_buf.mc_ptr and self.use_nvls
-                    and count * esz >= self.nvls_min_bytes)
-        if multi and _comm.require_nvls() and not use_nvls and count * esz >= self.nvls_min_bytes:
+                    and count * esz >= self.nvls_min_bytes
+                    and coll.PREFERRED_LARGE in (None, K.ALGO_NVLS))  # the planner may have voted NVLS out
+        if (multi and _comm.require_nvls() and count * esz >= self.nvls_min_bytes and self.use_nvls
+                and not (a.grads_buf.mc_ptr and a.params_buf.mc_ptr)):
             raise K.KungFuCudaError('KUNGFU_REQUIRE_NVLS=1 but the fused step has no multicast alias to run on')
         if use_nvls:
             # the switch reduces the gradient shard and multicasts the new parameters
             self._algos.add('nvls')
+            ev0 = _begin_step(comm, stream)
             K.call('kfb_ssgd_fused_step_nvls', cstruct, a.grads_buf.mc_ptr + go, a.code,
                    a.params_buf.mc_ptr + go, a.code, a.master.data_ptr() + mo, a.mom.data_ptr() + mo, count,
-                   float(grad_scale), C.byref(h), ssp, min(blocks, 32), threads, K.stream_ptr(stream))
-            _record_step(comm, K.ALGO_NVLS, count * esz, stream)
+                   float(grad_scale), C.byref(h), ssp, 1 if coll.SLOW_VARIANT == K.ALGO_NVLS else min(blocks, 32),
+                   threads, K.stream_ptr(stream))
+            _record_step(comm, K.ALGO_NVLS, count * esz, stream, ev0)
             return
         if multi:
             self._algos.add('p2p')
-            _record_step(comm, K.ALGO_TWOSHOT, count * esz, stream)
             ga, _k1 = a.grads_buf.ptr_array(go)
             pa, _k2 = a.params_buf.ptr_array(go)
             cs = cstruct
-            step_blocks = blocks
+            step_blocks = 1 if coll.SLOW_VARIANT == K.ALGO_TWOSHOT else blocks
         else:
             self._algos.add('local')
             me = max(comm.rank, 0)
@@ -222,9 +233,12 @@ class FusedOptimizer(torch.optim.Optimizer):
             step_blocks = local_blocks or self.local_blocks
         if comm.emulated and (lo != 0 or hi != a.count):
             raise K.KungFuCudaError('bucketed steps are not available under single-GPU rank emulation')
+        ev0 = _begin_step(comm, stream) if multi else None
         K.call('kfb_ssgd_fused_step', cs, ga, a.code, pa, a.code, a.master.data_ptr() + mo,
                a.mom.data_ptr() + mo, count, float(grad_scale), C.byref(h), ssp, step_blocks, threads,
                K.stream_ptr(stream))
+        if multi:
+            _record_step(comm, K.ALGO_TWOSHOT, count * esz, stream, ev0)
 
     # -- monolithic step ------------------------------------------------------------------
     def _run(self, sync, grad_scale):

@@ -94,6 +94,9 @@ class _CommBase(object):
         self._keep = []
         self._channels = {}
         self.closed = False
+        from .devstats import DeviceStats
+        self.stats = DeviceStats(self)  # bytes / device time per kernel variant (calc_stats, egress_rates, ...)
+        self.planner = None             # parallel.planner.DevicePlanner, attached on first use
         self.default_blocks = min(64, int(os.environ.get('KUNGFU_COMM_BLOCKS', '32')))
         self.default_threads = int(os.environ.get('KUNGFU_COMM_THREADS', '512'))
 
@@ -381,6 +384,11 @@ def default_comm():
             _default.is_local_root = lx.rank == 0
         else:
             _default = PeerComm(kfpy.control_exchange(), dev)
+        if isinstance(_default, PeerComm) and not _default.cross:
+            # measured bus bandwidth decides which all-reduce variant serves which size; the probe is
+            # collective, and creating the communicator is a point every rank passes
+            from .planner import planner_for
+            planner_for(_default).probe()
     return _default
 
 

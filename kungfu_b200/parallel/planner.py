@@ -50,11 +50,23 @@ def _depths(n, edges):
 
 
 class GraphExecutor(object):
-    def __init__(self, comm, strategies=None):
+    """Runs the active (reduce, broadcast) graph pairs on the device.
+
+    The graphs are compiled once into this rank's edge table: for every round,
+    which chunk to pull from which rank (see kfb_graph_allreduce in
+    include/kungfu_b200.h). On a real communicator the whole walk is ONE kernel
+    launch; the same table can be walked from Python with one kernel per edge
+    (`launcher='python'`), which is what the host simulation in
+    tests/test_planner_cpu.py drives with threads and numpy."""
+
+    def __init__(self, comm, strategies=None, launcher=None):
         self.comm = comm
         self.strategies = strategies if strategies is not None else kfpy.peer().strategies()
         self.stats = []  # (seconds, bytes) of monitored runs
         self._plans = [self._compile(s) for s in self.strategies]
+        self.launcher = launcher or ('device' if hasattr(comm, 'cstruct') and not getattr(comm, 'emulated', False)
+                                     else 'python')
+        self.table = self._table()
 
     def _compile(self, s):
         n = self.comm.np
@@ -69,6 +81,23 @@ class GraphExecutor(object):
             'my_bdepth': bdepth[rank], 'my_bprev': bprev[rank],
         }
 
+    def _table(self):
+        """This rank's edges per round: reduce rounds first, then broadcast rounds."""
+        max_r = max(p['reduce_rounds'] for p in self._plans)
+        max_b = max(p['bcast_rounds'] for p in self._plans)
+        rounds = []
+        for rnd in range(1, max_r + 1):
+            rounds.append([(i, src) for i, p in enumerate(self._plans) if p['my_rdepth'] == rnd for src in p['my_rprev']])
+        for rnd in range(1, max_b + 1):
+            rounds.append([(i, src) for i, p in enumerate(self._plans) if p['my_bdepth'] == rnd for src in p['my_bprev']])
+        begin, plan, src = [0], [], []
+        for edges in rounds:
+            for i, s_ in edges:
+                plan.append(i)
+                src.append(s_)
+            begin.append(len(plan))
+        return {'rounds': rounds, 'n_reduce': max_r, 'begin': begin, 'plan': plan, 'src': src}
+
     def all_reduce(self, buf, count, dtype, op='sum', byte_offset=0, monitored=False, stream=None):
         """In-place all-reduce of buf[byte_offset : +count] following the active graphs."""
         comm = self.comm
@@ -79,38 +108,54 @@ class GraphExecutor(object):
         k = len(self._plans)
         # chunk i -> strategy i (aligned to 16 bytes)
         per = ((count + k - 1) // k * es + 15) // 16 * 16 // es
+        chunks = []
+        for i in range(k):
+            lo = i * per
+            chunks.append((byte_offset + lo * es, max(0, min(per, count - lo))))
         ev0 = ev1 = None
         if monitored:
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record(stream)
-        max_r = max(p['reduce_rounds'] for p in self._plans)
-        max_b = max(p['bcast_rounds'] for p in self._plans)
-        me = comm.rank
-        for rnd in range(1, max_r + 1):
-            comm.barrier(stream)  # inputs of this round are final on every rank
-            for i, p in enumerate(self._plans):
-                lo = i * per
-                n = min(per, count - lo)
-                if n <= 0 or p['my_rdepth'] != rnd:
-                    continue
-                off = byte_offset + lo * es
-                for src in p['my_rprev']:
-                    coll.edge_reduce(buf.ptrs[me] + off, buf.ptrs[src] + off, n, code, op, stream=stream)
-        for rnd in range(1, max_b + 1):
-            comm.barrier(stream)
-            for i, p in enumerate(self._plans):
-                lo = i * per
-                n = min(per, count - lo)
-                if n <= 0 or p['my_bdepth'] != rnd:
-                    continue
-                off = byte_offset + lo * es
-                for src in p['my_bprev']:
-                    coll.edge_copy(buf.ptrs[me] + off, buf.ptrs[src] + off, n * es, stream=stream)
-        comm.barrier(stream)  # nobody overwrites its buffer while a child still pulls
+        if self.launcher == 'device':
+            self._walk_device(buf, chunks, code, es, op, stream)
+        else:
+            self._walk_python(buf, chunks, code, es, op, stream)
         if monitored:
             ev1.record(stream)
+        st = getattr(comm, 'stats', None)
+        if st is not None:
+            from .devstats import ALGO_GRAPH
+            st.record(ALGO_GRAPH, count * es, stream, events=(ev0, ev1) if monitored else None)
+        if monitored:
             ev1.synchronize()
             self.stats.append((ev0.elapsed_time(ev1) / 1e3, count * es))
+
+    def _walk_device(self, buf, chunks, code, es, op, stream):
+        comm, t = self.comm, self.table
+        bufs, _k0 = buf.ptr_array()
+        lo, _k1 = K.i64_array([c[0] for c in chunks])
+        nb, _k2 = K.i64_array([c[1] * es for c in chunks])
+        begin, _k3 = K.i32_array(t['begin'])
+        plan, _k4 = K.i32_array(t['plan'])
+        src, _k5 = K.i32_array(t['src'])
+        K.call('kfb_graph_allreduce', comm.cstruct, bufs, code, op if isinstance(op, int) else K.OPS[op],
+               len(chunks), lo, nb, len(t['rounds']), t['n_reduce'], begin, plan, src,
+               comm.default_blocks, comm.default_threads, K.stream_ptr(stream))
+
+    def _walk_python(self, buf, chunks, code, es, op, stream):
+        comm, t = self.comm, self.table
+        me = comm.rank
+        for r, edges in enumerate(t['rounds']):
+            comm.barrier(stream)  # inputs of this round are final on every rank
+            for i, src in edges:
+                off, n = chunks[i]
+                if n <= 0:
+                    continue
+                if r < t['n_reduce']:
+                    coll.edge_reduce(buf.ptrs[me] + off, buf.ptrs[src] + off, n, code, op, stream=stream)
+                else:
+                    coll.edge_copy(buf.ptrs[me] + off, buf.ptrs[src] + off, n * es, stream=stream)
+        comm.barrier(stream)  # nobody overwrites its buffer while a child still pulls
 
     def throughput(self):
         """bytes/s over the monitored runs since the last call (the reference's StrategyStat window)."""
@@ -134,6 +179,8 @@ class VariantChooser(object):
         self.best = {}       # size -> algo
         self.reference = {}  # algo -> busbw at the largest probe size
         self.disabled = set()
+        self._bufs = None    # probe buffers (symmetric allocations are collective: made once)
+        self.switches = 0
 
     def _time(self, fn, iters=8):
         for _ in range(3):
@@ -154,9 +201,10 @@ class VariantChooser(object):
             return
         sizes = sizes or self.PROBE_SIZES
         es = torch.empty(0, dtype=self.dtype).element_size()
-        cap = max(sizes)
-        buf = comm.alloc(cap, multicast=True)
-        out = comm.alloc(cap, multicast=True)
+        cap = max(max(sizes), max(self.PROBE_SIZES))
+        if self._bufs is None or self._bufs[0].nbytes < cap:
+            self._bufs = (comm.alloc(cap, multicast=True), comm.alloc(cap, multicast=True))
+        buf, out = self._bufs
         code = K.dtype_code(self.dtype)
         algos = [K.ALGO_ONESHOT, K.ALGO_TWOSHOT] + ([K.ALGO_NVLS] if buf.mc_ptr else [])
         for nbytes in sizes:
@@ -218,3 +266,79 @@ class VariantChooser(object):
             self.probe(sizes=(big, ))
             return True
         return False
+
+
+class DevicePlanner(object):
+    """What `-strategy`, set_tree, monitored_all_reduce, calc_stats and
+    check_interference mean for CUDA tensors. One per communicator
+    (``planner_for(comm)``); created together with the communicator so that
+    the variant probe, which is collective, runs at a point every rank reaches.
+
+    Two adaptive mechanisms, both with the reference's rule (a window under 80 %
+    of the best window seen is a vote; a majority of votes switches,
+    /root/reference/srcs/go/kungfu/session/adaptiveStrategies.go:61-121):
+
+    * kernel variants {one-shot, two-shot, NVLS}: chosen per size from the probe,
+      re-voted from the device-timed windows of the TRAINING collectives
+      (DeviceStats), switched by disabling the slow variant and re-probing;
+    * strategy graphs: the executor follows whatever set_tree / set_strategy
+      installed in the runtime (digest-checked there), so the reference's
+      "switch to a star rooted at rank 1" demo works unchanged on GPU tensors.
+    """
+
+    def __init__(self, comm):
+        self.comm = comm
+        self.chooser = VariantChooser(comm)
+        self._executor = None
+        self._digest = None
+
+    def probe(self):
+        import os
+        if self.comm.np > 1 and not self.comm.emulated and os.environ.get('KUNGFU_PROBE_VARIANTS', '1') != '0':
+            self.chooser.probe(sizes=(64 << 10, 1 << 20, 16 << 20))
+
+    def executor(self):
+        """Graph executor for the strategies currently active in the runtime."""
+        strategies = kfpy.peer().strategies()
+        digest = repr(strategies)
+        if self._executor is None or digest != self._digest:
+            self._executor = GraphExecutor(self.comm, strategies)
+            self._digest = digest
+        return self._executor
+
+    def monitored_all_reduce(self, buf, count, dtype, op='sum', stream=None):
+        self.comm.stats.timing = True
+        self.executor().all_reduce(buf, count, dtype, op, monitored=True, stream=stream)
+
+    def calc_stats(self):
+        self.comm.stats.calc()
+
+    def check_interference(self):
+        """Vote on the active kernel variant from the windows calc_stats() closed;
+        a majority switches to the next-best variant. Returns True on a switch."""
+        comm = self.comm
+        if comm.np <= 1:
+            return False
+        from ..torch.ops import collective as tops
+        vote = 1 if comm.stats.below_reference(VariantChooser.THRESHOLD) else 0
+        total = int(tops.all_reduce_fn(torch.tensor([vote], dtype=torch.int32), 'sum')[0])
+        if total * 2 <= comm.np:
+            return False
+        active = comm.stats.active
+        if active in (K.ALGO_ONESHOT, K.ALGO_TWOSHOT, K.ALGO_NVLS):
+            self.chooser.disabled.add(active)
+            if len(self.chooser.disabled) >= 3:
+                self.chooser.disabled = {active}
+            self.chooser.probe(sizes=(1 << 20, 16 << 20))
+            self.chooser.switches += 1
+            # the new variant starts a fresh reference window
+            for st in comm.stats.by_variant.values():
+                st.reference = 0.0
+            return True
+        return False
+
+
+def planner_for(comm):
+    if comm.planner is None:
+        comm.planner = DevicePlanner(comm)
+    return comm.planner

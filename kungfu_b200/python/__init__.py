@@ -119,25 +119,56 @@ def _on_membership_change(detached=False):
         pass
 
 
+def _device_planner():
+    """The device data plane's planner, if this process has created a device communicator."""
+    try:
+        from ..parallel import comm as pc
+        if pc._default is None:
+            return None
+        from ..parallel.planner import planner_for
+        return planner_for(pc._default)
+    except Exception:
+        return None
+
+
 def check_interference():
     """Majority vote over the workers: has the active strategy dropped well below its reference throughput?
-    (reference: session/adaptiveStrategies.go:18-127)"""
-    return _p().check_interference()
+    (reference: session/adaptiveStrategies.go:18-127). Two data planes are voted on: the host runtime's
+    strategy graphs (CPU tensors) and, when GPU collectives are in use, the device kernel variants fed by
+    the training all-reduces; on a device vote the slow variant is replaced by the next best one. The
+    return value keeps the reference's meaning for the caller: True = the workers agreed that the
+    active strategy is being interfered with."""
+    host = _p().check_interference()
+    dp = _device_planner()
+    dev = dp.check_interference() if dp is not None else False
+    return bool(host) or bool(dev)
 
 
 def calc_stats():
-    """Fold the traffic counters since the last call into the per-strategy throughput statistics."""
+    """Fold the traffic counters since the last call into the per-strategy throughput statistics
+    (host strategies and device kernel variants)."""
     _p().calc_stats()
+    dp = _device_planner()
+    if dp is not None:
+        dp.calc_stats()
 
 
 def log_stats():
     """Log the per-strategy throughput statistics."""
     _p().log_stats()
+    dp = _device_planner()
+    if dp is not None:
+        for line in dp.comm.stats.lines():
+            print('[kungfu] rank %d %s' % (current_rank(), line), flush=True)
 
 
 def print_strategy_stats():
     """Print the per-strategy throughput statistics of this worker."""
     _p().print_strategy_stats()
+    dp = _device_planner()
+    if dp is not None:
+        for line in dp.comm.stats.lines():
+            print(line, flush=True)
 
 
 def set_tree(forest):
@@ -158,8 +189,14 @@ def get_peer_latencies():
 
 
 def egress_rates():
-    """Bytes per second sent to every peer over the last monitoring period (KUNGFU_CONFIG_ENABLE_MONITORING)."""
-    return _p().egress_rates()
+    """Bytes per second sent to every peer: the control plane's sockets over the last monitoring period
+    (KUNGFU_CONFIG_ENABLE_MONITORING) plus, when GPU collectives are in use, the NVLink bytes the device
+    kernels moved since the previous call (per-variant byte model, parallel/devstats.py)."""
+    rates = list(_p().egress_rates())
+    dp = _device_planner()
+    if dp is not None and dp.comm.np == len(rates) and not dp.comm.cross:
+        rates = [a + b for a, b in zip(rates, dp.comm.stats.egress_rates())]
+    return rates
 
 
 def _get_cuda_index():

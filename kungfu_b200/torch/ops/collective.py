@@ -315,22 +315,68 @@ def barrier():
     kfpy.run_barrier()
 
 
+def _cuda_consensus(x):
+    from ...ops import collective as coll
+    comm = _comm()
+    if comm.np == 1:
+        return True
+    xc = x.detach().contiguous()
+    nbytes = xc.numel() * xc.element_size()
+    pad = (nbytes + 15) // 16 * 16
+    src = _stage(comm, 'in', pad)
+    src.local[:pad].zero_()
+    src.local[:nbytes].copy_(xc.view(-1).view(torch.uint8))
+    agree = torch.zeros(1, dtype=torch.int32, device=x.device)
+    coll.consensus(comm, src, pad, agree)
+    return bool(int(agree))
+
+
 def consensus(x, name=None):
-    """True iff every worker holds identical bytes in x."""
-    xc = x.detach().contiguous().cpu()
+    """True iff every worker holds identical bytes in x (CUDA tensors on one NVLink domain: one
+    device kernel compares them in place, nothing is copied to the host)."""
+    if x.is_cuda and not _comm().cross:
+        # shapes first (control plane, a few bytes), then the bytes on the device
+        meta = torch.tensor(list(x.shape) + [x.element_size(), x.dim()], dtype=torch.int64)
+        if not consensus(meta, name=(name or 'kungfu::consensus') + '::shape'):
+            return False
+        return _cuda_consensus(x)
+    xc = to_host(x.detach().contiguous())
     agree = C.c_int(0)
     _check(H.lib().kf_consensus(kfpy.peer()._h, xc.data_ptr(), xc.numel() * xc.element_size(),
                                 _name(name, 'consensus'), C.byref(agree)), 'consensus')
     return bool(agree.value)
 
 
+def _cuda_monitored_all_reduce(x, tree, op):
+    """The strategy walk on the device: the graphs active in the runtime (set by -strategy, set_tree or
+    the `tree` argument) are walked by ONE kernel over peer memory, timed with CUDA events, and the
+    bytes / device time land in the same statistics calc_stats() and check_interference() read."""
+    from ...parallel.planner import planner_for
+    comm = _comm()
+    if tree is not None and len(tree) > 0:
+        kfpy.set_tree([int(t) for t in tree])
+    if comm.np == 1:
+        return x.clone()
+    from ...ops import _cuda as K
+    xc = x.contiguous()
+    nbytes = xc.numel() * xc.element_size()
+    pad = (nbytes + 15) // 16 * 16
+    buf = _stage(comm, 'in', pad)
+    buf.local[:nbytes].copy_(xc.view(-1).view(torch.uint8))
+    planner_for(comm).monitored_all_reduce(buf, xc.numel(), K.dtype_code(x.dtype), op)
+    return buf.local[:nbytes].view(x.dtype).view(xc.shape).clone()
+
+
 def monitored_all_reduce(x, tree=None, op=None, name=None):
-    """All-reduce of a CPU tensor that feeds the strategy throughput stats;
+    """All-reduce that feeds the strategy throughput stats (CPU tensors: host runtime; CUDA tensors:
+    device graph executor);
     `tree` (father array) installs a new tree first
     (/root/reference/srcs/python/kungfu/tensorflow/ops/collective.py:40-60)."""
     if op is None:
         op = 'sum'
-    xc = x.contiguous().cpu()
+    if x.is_cuda and not _comm().cross:
+        return _cuda_monitored_all_reduce(x, tree, op)
+    xc = to_host(x.contiguous())
     y = torch.empty_like(xc)
     arr, n = None, 0
     if tree is not None and len(tree) > 0:
@@ -356,6 +402,8 @@ def save_variable(x, name, version=None):
 
 def request_variable(target, name, like, version=None):
     """Fetch `name` from worker `target`'s store; returns (ok, tensor)."""
+    # (the store is a host object, like the reference's; models that live on GPUs exchange snapshots
+    # through PairAveragingOptimizer's device path instead)
     out = torch.empty(like.shape, dtype=like.dtype)
     ok = kfpy.peer().request(int(target), name, out.data_ptr(), out.numel() * out.element_size(),
                              None if version is None else str(version))

@@ -28,6 +28,7 @@ def global_noise_scale(batch_small, batch_big, tensor, avg_tensor, alpha=0.6, _s
 
 
 def egress_rates():
-    """float32[np] bytes/s sent to each peer over the control plane (needs
-    KUNGFU_CONFIG_ENABLE_MONITORING=true)."""
+    """float32[np] bytes/s sent to each peer: control-plane sockets (with
+    KUNGFU_CONFIG_ENABLE_MONITORING=true) plus the NVLink bytes of the device kernels since the previous call
+    (reference: /root/reference/srcs/python/kungfu/tensorflow/ops/monitor.py:20-27)."""
     return torch.tensor(kfpy.egress_rates(), dtype=torch.float32)

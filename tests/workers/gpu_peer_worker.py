@@ -426,6 +426,65 @@ def check_planner():
     torch.cuda.synchronize()
     assert torch.equal(buf.view(torch.float32)[:n].cpu(), torch.stack(xs).max(0).values)
     kfpy.set_strategy('AUTO')
+    # ---- the same through the PUBLIC ops on CUDA tensors (nothing is staged through the host) ----
+    x = torch.arange(100003, device=dev, dtype=torch.float32) * 1e-3 + rank
+    want = sum(torch.arange(100003, dtype=torch.float32) * 1e-3 + r for r in range(np_))
+    for s in ('STAR', 'RING', 'BINARY_TREE_STAR'):
+        kfpy.set_strategy(s)
+        y = kf.ops.monitored_all_reduce(x)
+        assert y.is_cuda and torch.allclose(y.cpu(), want, rtol=1e-5, atol=1e-4), (s, (y.cpu() - want).abs().max())
+    star = [np_ - 1] * np_
+    y = kf.ops.monitored_all_reduce(x, tree=star, op='max')
+    assert torch.equal(y.cpu(), torch.arange(100003, dtype=torch.float32) * 1e-3 + (np_ - 1))
+    kfpy.set_strategy('AUTO')
+    assert kf.ops.consensus(torch.full((1000, ), 7.0, device=dev))
+    assert kf.ops.consensus(torch.full((1000, ), float(rank), device=dev)) == (np_ == 1)
+    # ---- device traffic in the monitoring API, and the interference vote on the TRAINING all-reduce ----
+    from kungfu_b200.parallel.planner import planner_for
+    dp = planner_for(comm)
+    big = comm.alloc(16 << 20, multicast=True)
+    kf.ops.calc_stats()          # opens the first window (and switches device timing on)
+    kf.ops.egress_rates()
+
+    def window(k=12):
+        for _ in range(k):
+            coll.all_reduce(comm, big, (16 << 20) // 2, torch.bfloat16, 'sum', scale=1.0 / np_)
+        torch.cuda.synchronize()
+        kf.ops.calc_stats()
+
+    if np_ > 1:
+        window()
+        rates = kf.ops.egress_rates()
+        assert len(rates) == np_ and float(rates.sum()) > 1e6 and float(rates[rank]) == 0.0, rates
+        active = comm.stats.active
+        fast = comm.stats.by_variant[active].throughput
+        assert fast > 0 and not kf.ops.check_interference()
+        # slow the active variant down on a majority of ranks (one CTA instead of 32): the window collapses,
+        # the workers vote, the planner installs another variant
+        if rank <= np_ // 2:
+            coll.SLOW_VARIANT = active
+        window()
+        slow = comm.stats.by_variant[active].throughput
+        assert slow < 0.8 * fast, (slow, fast)
+        assert kf.ops.check_interference(), 'a majority saw the active variant under 80 % of its reference'
+        coll.SLOW_VARIANT = None
+        assert coll.choose_algo(comm, 16 << 20, big, K.OP_SUM, K.BF16) != active
+        window()
+        assert comm.stats.active != active
+        xs16 = inputs((16 << 20) // 2, torch.bfloat16, 5)
+        big.view(torch.bfloat16)[:(16 << 20) // 2].copy_(xs16[rank])
+        coll.all_reduce(comm, big, (16 << 20) // 2, torch.bfloat16, 'sum')
+        torch.cuda.synchronize()
+        ref16 = torch.stack([t.float() for t in xs16]).sum(0)
+        got16 = big.view(torch.bfloat16)[:(16 << 20) // 2].float().cpu()
+        assert torch.allclose(got16, ref16, rtol=2e-2, atol=2e-2)
+        if rank == 0:
+            from kungfu_b200.parallel.devstats import VARIANTS
+            print('adaptive switch ok: %s %.1f GB/s -> slowed to %.1f GB/s -> %s' %
+                  (VARIANTS[active], fast / 1e9, slow / 1e9, VARIANTS[comm.stats.active]), flush=True)
+            kf.ops.print_strategy_stats()
+        dp.chooser.disabled.clear()
+        dp.probe()
     ch = VariantChooser(comm)
     ch.probe(sizes=(64 << 10, 4 << 20))
     assert ch.choose(4 << 20) in (K.ALGO_TWOSHOT, K.ALGO_NVLS, K.ALGO_ONESHOT)
