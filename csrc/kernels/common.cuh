@@ -318,4 +318,49 @@ peer_barrier(const PeerPads &pads, uint32_t *local_epoch, int rank, int np,
     // behind the leading __syncthreads() of the next peer_barrier call.
 }
 
+// Split-phase form of the same barrier, for kernels that overlap other work:
+// waiting inside a resident CTA takes an SM slot away from whatever else is
+// running, so the arrival is sent early by a tiny launch of its own
+// (peer_arrive_rows: "my inputs of the next collective are final") and the
+// collective kernel, launched later, only checks that every peer's arrival is
+// there (peer_wait_row), which by then it normally is.
+__device__ __forceinline__ void
+peer_arrive_rows(const PeerPads &pads, uint32_t *local_epoch, int rank, int np, int nrows)
+{
+    // one CTA; thread t handles (row, peer) = (t / np, t % np)
+    for (int t = threadIdx.x; t < nrows * np; t += blockDim.x) {
+        const int row = t / np, peer = t % np;
+        const uint32_t e = local_epoch[row] + 1;
+        __threadfence_system();
+        st_release_sys(pad_flag(pads.pad[peer], row, rank), e);
+    }
+    __syncthreads();
+    for (int row = threadIdx.x; row < nrows; row += blockDim.x) local_epoch[row] += 1;
+}
+
+__device__ __forceinline__ void
+peer_wait_row(const PeerPads &pads, const uint32_t *local_epoch, int rank, int np, int block)
+{
+    if (threadIdx.x < np) {
+        const uint32_t e     = local_epoch[block];  // already advanced by this rank's arrival
+        const uint32_t *mine = pad_flag(pads.pad[rank], block, threadIdx.x);
+        unsigned long long t0 = 0;
+        unsigned spins        = 0;
+        while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+            __nanosleep(20);
+            if ((++spins & 0x3fffu) == 0) {
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > KFB_BARRIER_TIMEOUT_NS) {
+                    printf("kungfu_b200: rank %d gave up waiting for rank %d's arrival (block %d, epoch %u)\n",
+                           rank, (int)threadIdx.x, block, e);
+                    __trap();
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
 }  // namespace kfb

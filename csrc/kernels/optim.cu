@@ -292,6 +292,10 @@ struct StepArgs {
     SgdH h;
     int rank, np;
     float *sumsq_out;
+    // KFB_STEP_PRESIGNALED: the arrival of the entry barrier was sent by kfb_peer_signal, only wait.
+    // KFB_STEP_NO_EXIT_BARRIER: do not meet the peers again on the way out (a later launch does);
+    // sumsq_out then only receives THIS rank's shard partial.
+    int flags;
 };
 
 template <typename G, typename P, int NP, bool NORM>
@@ -309,8 +313,12 @@ __global__ void __launch_bounds__(512)
     float *mom2   = a.h.v ? a.h.v + (a.rank < 0 ? (long long)rank * a.npk * 8 : 0) : nullptr;
     const Bias bias = opt_bias(a.h);
     __shared__ float red[32];
+    const bool exit_barrier = !(a.flags & KFB_STEP_NO_EXIT_BARRIER);
 
-    if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+    if (np > 1) {
+        if (a.flags & KFB_STEP_PRESIGNALED) peer_wait_row(a.pads, epoch, rank, np, blockIdx.x);
+        else peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+    }
     const long long per    = (a.npk + np - 1) / np;
     const long long lo     = (long long)rank * per;
     const long long hi     = min(lo + per, a.npk);
@@ -351,25 +359,29 @@ __global__ void __launch_bounds__(512)
         slots_store(a.h, mom, mom2, i, m, v);
         for (int k = 0; k < np; ++k) Pk8<P>::store(a.params[(rank + k) % np], i, p);
     }
+    __shared__ float s_part;
     if (NORM) {
         const float part = block_sum(ss, red);
-        __shared__ float s_part;
         if (threadIdx.x == 0) s_part = part;
         __syncthreads();
-        if (threadIdx.x < np)
+        if (exit_barrier && threadIdx.x < np)
             st_relaxed_sys_f32(
                 pad_scalar(a.pads.pad[threadIdx.x], blockIdx.x, rank), s_part);
     }
     if (np > 1 || NORM) {
-        if (np > 1) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
+        if (np > 1 && exit_barrier) peer_barrier(a.pads, epoch, rank, np, blockIdx.x);
         else __syncthreads();
     }
     if (NORM) {
         __shared__ bool is_last;
         if (threadIdx.x == 0) {
             float t = 0.f;
-            for (int r = 0; r < np; ++r)
-                t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            if (exit_barrier && !(a.flags & KFB_STEP_PARTIAL_NORM)) {
+                for (int r = 0; r < np; ++r)
+                    t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            } else {
+                t = s_part;
+            }
             scratch[blockIdx.x] = t;
             __threadfence();
             unsigned int *ticket =
@@ -436,7 +448,9 @@ __global__ void __launch_bounds__(512)
     const int rank = a.rank, np = a.np;
     const Bias bias = opt_bias(a.h);
     __shared__ float red[32];
-    peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    const bool exit_barrier = !(a.flags & KFB_STEP_NO_EXIT_BARRIER);
+    if (a.flags & KFB_STEP_PRESIGNALED) peer_wait_row(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    else peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
     const long long per    = (a.npk + np - 1) / np;
     const long long lo     = (long long)rank * per;
     const long long hi     = min(lo + per, a.npk);
@@ -459,21 +473,31 @@ __global__ void __launch_bounds__(512)
         slots_store(a.h, a.mom, a.h.v, i, m, v);
         Mc8<P>::st(mc_p, i, p);
     }
+    __shared__ float s_part;
     if (NORM) {
         const float part = block_sum(ss, red);
-        __shared__ float s_part;
         if (threadIdx.x == 0) s_part = part;
         __syncthreads();
-        if (threadIdx.x < np)
+        if (exit_barrier && threadIdx.x < np)
             st_relaxed_sys_f32(pad_scalar(a.pads.pad[threadIdx.x], blockIdx.x, rank), s_part);
     }
-    peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    if (exit_barrier) peer_barrier(a.pads, a.local_epoch, rank, np, blockIdx.x);
+    else {
+        // the parameters this rank multicast must be visible before a LATER launch's barrier lets
+        // anybody read them: that barrier's release covers this kernel's stores (same stream)
+        __threadfence_system();
+        __syncthreads();
+    }
     if (NORM) {
         __shared__ bool is_last;
         if (threadIdx.x == 0) {
             float t = 0.f;
-            for (int r = 0; r < np; ++r)
-                t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            if (exit_barrier && !(a.flags & KFB_STEP_PARTIAL_NORM)) {
+                for (int r = 0; r < np; ++r)
+                    t += ld_relaxed_sys_f32(pad_scalar(a.pads.pad[rank], blockIdx.x, r));
+            } else {
+                t = s_part;
+            }
             a.scratch[blockIdx.x] = t;
             __threadfence();
             unsigned int *ticket = reinterpret_cast<unsigned int *>(a.scratch + KFB_MAX_BLOCKS);
@@ -488,6 +512,14 @@ __global__ void __launch_bounds__(512)
             *reinterpret_cast<unsigned int *>(a.scratch + KFB_MAX_BLOCKS) = 0u;
         }
     }
+}
+
+// Arrival of the next collective's entry barrier, sent ahead of the collective
+// (see peer_arrive_rows in common.cuh). One CTA.
+__global__ void __launch_bounds__(512)
+    k_peer_signal(PeerPads pads, uint32_t *local_epoch, int rank, int np, int nrows)
+{
+    peer_arrive_rows(pads, local_epoch, rank, np, nrows);
 }
 
 // Plain local flat SGD on a reduced gradient (any-rank, no peers).
@@ -1178,6 +1210,24 @@ static int fill_step(StepArgs &a, const kfb_comm *c, int64_t count)
     return KFB_OK;
 }
 
+extern "C" int kfb_peer_signal(const kfb_comm *comm, int rows, void *stream)
+{
+    if (!comm || comm->rank < 0 || comm->np < 1 || comm->np > KFB_MAX_RANKS || rows < 1 || rows > KFB_MAX_BLOCKS) {
+        set_last_error("kfb_peer_signal: needs a real rank and 1..%d rows", KFB_MAX_BLOCKS);
+        return KFB_ERR_ARG;
+    }
+    if (comm->np == 1) return KFB_OK;
+    PeerPads pads;
+    fill_pads(pads, comm);
+    k_peer_signal<<<1, 512, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        pads, reinterpret_cast<uint32_t *>(comm->local_epoch), comm->rank, comm->np, rows);
+    KFB_CUDA_OK(cudaGetLastError());
+    return KFB_OK;
+}
+
+static thread_local int g_step_flags = 0;
+extern "C" void kfb_set_step_flags(int flags) { g_step_flags = flags; }
+
 extern "C" int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
                                    int grad_dtype, void *const *params,
                                    int param_dtype, float *master, float *mom,
@@ -1190,6 +1240,8 @@ extern "C" int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
     StepArgs a;
     rc = fill_step(a, comm, count);
     if (rc) return rc;
+    a.flags      = comm->rank < 0 ? 0 : g_step_flags;
+    g_step_flags = 0;
     for (int r = 0; r < comm->np; ++r) {
         a.grads[r]  = grads[r];
         a.params[r] = params[r];
@@ -1233,6 +1285,8 @@ extern "C" int kfb_ssgd_fused_step_nvls(const kfb_comm *comm, void *mc_grads, in
     StepArgs a;
     rc = fill_step(a, comm, count);
     if (rc) return rc;
+    a.flags      = g_step_flags;
+    g_step_flags = 0;
     a.stage[0]   = mc_grads;
     a.stage[1]   = mc_params;
     a.master     = master;

@@ -220,6 +220,23 @@ int kfb_ssgd_fused_step(const kfb_comm *comm, void *const *grads,
                         float *sumsq_out, int blocks, int threads,
                         void *stream);
 
+/* Split-phase entry barrier for steps that run UNDER other work (bucketed,
+ * overlapped S-SGD). kfb_peer_signal (one tiny CTA) sends this rank's arrival
+ * for `rows` CTA rows of the communicator ("my gradients of the next bucket
+ * are final"); the step launched later with KFB_STEP_PRESIGNALED only checks
+ * that every peer's arrival is there instead of arriving and spinning itself.
+ * KFB_STEP_NO_EXIT_BARRIER drops the barrier on the way out; the caller must
+ * end the sequence with a launch that keeps it (the last bucket) before
+ * anything reads the parameters. kfb_set_step_flags applies to the NEXT
+ * kfb_ssgd_fused_step[_nvls] call of the calling thread only. With
+ * NO_EXIT_BARRIER sumsq_out receives this rank's shard partial (sum them
+ * over the ranks afterwards). `rows` must equal the step's `blocks`. */
+#define KFB_STEP_PRESIGNALED 1
+#define KFB_STEP_NO_EXIT_BARRIER 2
+#define KFB_STEP_PARTIAL_NORM 4 /* sumsq_out := this rank's shard partial even when the exit barrier is kept */
+int kfb_peer_signal(const kfb_comm *comm, int rows, void *stream);
+void kfb_set_step_flags(int flags);
+
 /* NVLS variant: the switch sums the gradient shard (multimem.ld_reduce) and
  * multicasts the updated parameters (multimem.st). mc_grads / mc_params are
  * the multicast aliases of the flat gradient / parameter buffers. np >= 2. */

@@ -26,6 +26,7 @@ VAR_WORK_WORDS = 4 * MAX_BLOCKS + 8
 F32, BF16, F16, I32, F64, I64, U8 = range(7)
 OP_SUM, OP_MIN, OP_MAX, OP_PROD = range(4)
 ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = range(3)
+STEP_PRESIGNALED, STEP_NO_EXIT_BARRIER, STEP_PARTIAL_NORM = 1, 2, 4
 
 DTYPES = {
     torch.float32: F32,
@@ -102,6 +103,8 @@ _SIGS = {
     'kfb_defuse': (C.c_int, [C.c_void_p, C.c_int, _PTRS, _I64S, _I64S, C.c_int, C.c_int, C.c_void_p]),
     'kfb_ssgd_fused_step': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     'kfb_ssgd_fused_step_nvls': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    'kfb_peer_signal': (C.c_int, [C.POINTER(KfbComm), C.c_int, C.c_void_p]),
+    'kfb_set_step_flags': (None, [C.c_int]),
     'kfb_sgd_flat': (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_void_p]),
     'kfb_sma_fused_step': (C.c_int, [C.POINTER(KfbComm), _PTRS, C.c_int, _PTRS, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float, C.POINTER(SgdHyper), C.c_int, C.c_int, C.c_void_p]),
     'kfb_pair_avg_step_dev': (C.c_int, [C.POINTER(KfbComm), C.c_void_p, C.c_int64, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.POINTER(SgdHyper), C.c_void_p, C.c_void_p, C.c_ulonglong, C.c_int, C.c_int, C.c_void_p]),

@@ -91,6 +91,8 @@ class FusedOptimizer(torch.optim.Optimizer):
         # grids of the model kernels, so hidden buckets get few CTAs (they only have to finish
         # before backward does); the last bucket, whose time is exposed, gets the full set.
         self.hidden_blocks = int(os.environ.get('KUNGFU_OVERLAP_BLOCKS', '8'))
+        # how many autograd hooks after a bucket's arrival signal its exchange kernel is launched
+        self.defer_hooks = int(os.environ.get('KUNGFU_OVERLAP_DEFER_HOOKS', '6'))
 
     # -- arenas -------------------------------------------------------------------------
     @property
@@ -348,6 +350,8 @@ class FusedOptimizer(torch.optim.Optimizer):
             h.remove()
         for a in self._all_arenas() if self._arenas is not None else []:
             a.segments = [(0, a.count)]
+        if self._arenas is not None:
+            self._size_norm_slots(sum(len(a) for _, a in self._arenas))
         self._ov = None
 
     def _setup_overlap(self):
@@ -385,58 +389,112 @@ class FusedOptimizer(torch.optim.Optimizer):
             for j in b.idx:
                 hooks.append(b.arena.params[j].register_post_accumulate_grad_hook(self._on_grad))
         stream = torch.cuda.Stream(device=comm.device, priority=-1)
-        self._ov = {'buckets': buckets, 'where': where, 'hooks': hooks, 'stream': stream, 'next': 0,
-                    'armed': True, 'joined': True,
+        self._ov = {'buckets': buckets, 'where': where, 'hooks': hooks, 'stream': stream, 'fused': 0, 'stepped': 0,
+                    'since': 0, 'armed': True,
                     'fuse_scratch': torch.zeros(K.FUSE_SCRATCH_FLOATS, dtype=torch.float32, device=comm.device)}
         self._size_norm_slots(len(buckets))
+        if comm.np > 1:
+            # per-bucket norm partials of this rank's shards, summed over the ranks once per step
+            nb4 = (len(buckets) + 3) // 4 * 4
+            self._ov['norm_in'] = comm.alloc(nb4 * 4)
+            self._ov['norm_out'] = comm.alloc(nb4 * 4)
+            self._ss_partial = self._ov['norm_in'].view(torch.float32)[:nb4]
+            self._ss_global_parts = self._ov['norm_out'].view(torch.float32)[:nb4]
+        else:
+            self._ss_partial = self._ss_global_parts
 
     def _on_grad(self, p):
         ov = self._ov
         if ov is None or not ov['armed']:
             return
         ov['where'][id(p)].pending -= 1
-        self._launch_ready()
+        ov['since'] += 1
+        self._progress()
 
-    def _launch_ready(self, force=False):
+    def _progress(self, force=False):
+        """Buckets go through two launches, in bucket order, on the side stream:
+        (1) gather + arrival signal as soon as all gradients of the bucket exist;
+        (2) the fused exchange + update a few autograd hooks later (or when the
+        next bucket is complete), ordered behind the main stream at that point.
+        By then every peer's arrival is normally in, so the kernel does not sit
+        on SMs waiting for a slower rank while backward needs them."""
         ov = self._ov
-        while ov['next'] < len(ov['buckets']):
-            b = ov['buckets'][ov['next']]
-            if b.pending > 0 and not force:
+        bks = ov['buckets']
+        nb = len(bks)
+        while True:
+            if ov['stepped'] < ov['fused']:
+                nxt_ready = ov['fused'] < nb and bks[ov['fused']].pending <= 0
+                if force or nxt_ready or ov['since'] >= self.defer_hooks:
+                    self._step_bucket(bks[ov['stepped']])
+                    ov['stepped'] += 1
+                    continue
                 return
-            self._launch_bucket(b)
-            ov['next'] += 1
+            if ov['fused'] < nb and (bks[ov['fused']].pending <= 0 or force):
+                self._fuse_bucket(bks[ov['fused']])
+                ov['fused'] += 1
+                ov['since'] = 0
+                continue
+            return
 
-    def _launch_bucket(self, b):
+    def _bucket_blocks(self, b):
+        comm, ov = self.comm, self._ov
+        blocks = min(comm.channel_blocks(OVERLAP_CHANNEL, self._blocks), 32)
+        if b.slot != len(ov['buckets']) - 1:
+            blocks = min(blocks, self.hidden_blocks)
+        return blocks
+
+    def _multi(self):
+        comm = self.comm
+        return self._ov_sync and comm.np > 1 and not comm.cross
+
+    def _fuse_bucket(self, b):
         comm, ov = self.comm, self._ov
         side = ov['stream']
         # everything this bucket reads was produced on the stream that is current now
         side.wait_stream(torch.cuda.current_stream())
-        ov['joined'] = False
-        a = b.arena
         ss_l = self._ss_local_parts[b.slot:b.slot + 1] if self.monitor_norms else None
-        ss_g = self._ss_global_parts[b.slot:b.slot + 1] if self.monitor_norms else None
-        a.fuse_grads(sumsq_out=ss_l, stream=side, idx=b.idx, scratch=ov['fuse_scratch'])
+        b.arena.fuse_grads(sumsq_out=ss_l, stream=side, idx=b.idx, scratch=ov['fuse_scratch'])
+        if self._multi():
+            K.call('kfb_peer_signal', comm.channel(OVERLAP_CHANNEL), self._bucket_blocks(b), K.stream_ptr(side))
+
+    def _step_bucket(self, b):
+        comm, ov = self.comm, self._ov
+        side = ov['stream']
+        # ordered behind the main stream as of NOW: this is what keeps the kernel from starting
+        # (and spinning) right behind its own signal
+        side.wait_stream(torch.cuda.current_stream())
+        a = b.arena
+        ss_g = self._ss_partial[b.slot:b.slot + 1] if self.monitor_norms else None
         sync = self._ov_sync
-        n = comm.np
-        scale = (1.0 / n) if (sync and self._ov_average) else 1.0
-        blocks = comm.channel_blocks(OVERLAP_CHANNEL, self._blocks)
+        scale = (1.0 / comm.np) if (sync and self._ov_average) else 1.0
         last = b.slot == len(ov['buckets']) - 1
-        if not last:
-            blocks = min(blocks, self.hidden_blocks)
+        blocks = self._bucket_blocks(b)
         threads = self._threads or comm.default_threads
+        if self._multi():
+            flags = K.STEP_PRESIGNALED | K.STEP_PARTIAL_NORM
+            if not last:
+                flags |= K.STEP_NO_EXIT_BARRIER
+            K.lib().kfb_set_step_flags(flags)
         self._launch_range(b.group, a, b.lo, b.hi, sync, scale, ss_g, comm.channel(OVERLAP_CHANNEL), blocks,
                            threads, side, local_blocks=None if last else self.hidden_blocks * 4)
 
     def _finish_overlap(self):
         ov = self._ov
-        self._launch_ready(force=True)
+        self._progress(force=True)
         torch.cuda.current_stream().wait_stream(ov['stream'])
-        ov['joined'] = True
         for b in ov['buckets']:
             b.pending = len(b.idx)
-        ov['next'] = 0
+        ov['fused'] = ov['stepped'] = ov['since'] = 0
         if self.monitor_norms:
-            self._sum_norm_slots(len(ov['buckets']))
+            n = len(ov['buckets'])
+            if self._multi():
+                # every slot holds this rank's shard partial: add the ranks up (rank order: identical everywhere)
+                from ..ops import collective as coll
+                coll.all_reduce(self.comm, ov['norm_in'], (n + 3) // 4 * 4, K.F32, 'sum', algo=K.ALGO_ONESHOT,
+                                out=ov['norm_out'])
+            elif self._ss_partial is not self._ss_global_parts:
+                self._ss_global_parts.copy_(self._ss_partial)
+            self._sum_norm_slots(n)
         self._after_step()
 
     # -- state ------------------------------------------------------------------------------

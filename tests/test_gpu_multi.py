@@ -19,7 +19,7 @@ def test_peer_memory_path(np_):
         pytest.skip('needs %d GPUs' % np_)
     # KUNGFU_REQUIRE_NVLS: a box whose multicast set-up fails must fail here, not pass on the fall-back kernels
     res = run_workers(np_, os.path.join(ROOT, 'tests', 'workers', 'gpu_peer_worker.py'), timeout=600,
-                      extra_flags=['-allow-nvlink'], env={'KUNGFU_REQUIRE_NVLS': '1'})
+                      extra_flags=['-allow-nvlink'], env={'KUNGFU_REQUIRE_NVLS': '1', 'KUNGFU_PROBE_VARIANTS': '0'})
     assert res.returncode == 0, res.stdout[-6000:]
     assert res.stdout.count('OK rank') == np_, res.stdout[-6000:]
     assert 'multicast=True' in res.stdout, res.stdout[-2000:]
