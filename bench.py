@@ -58,6 +58,7 @@ def parse_args():
                     help='after the timed region, also time stock PyTorch (torchvision-style ResNet-50, torch BN, '
                          'torch.optim.SGD, DistributedDataParallel over NCCL) with the same protocol')
     ap.add_argument('--baseline-steps', type=int, default=10)
+    ap.add_argument('--clock-interval-ms', type=int, default=100)
     ap.add_argument('--trace', action='store_true',
                     help='after the measurement, replay 4 steps under torch.profiler and print where the communication '
                          'kernels sit on the timeline of rank 0 (diagnostic; never part of a reported number)')
@@ -65,53 +66,66 @@ def parse_args():
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks / throttle reasons during the timed region."""
-    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
-         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
-         'clocks_event_reasons.sw_power_cap')
+    """SM clock and throttle reasons of ONE device during the timed region, read
+    through NVML in this process (a thread, one device handle). The earlier
+    `nvidia-smi -lms 100` child enumerated every GPU of the box ten times a
+    second; with several ranks that is N x 10 whole-box queries per second next
+    to a measurement that waits for the slowest GPU every step."""
+    REASONS = (('hw_slowdown', 0x8), ('hw_thermal_slowdown', 0x40), ('sw_thermal_slowdown', 0x20),
+               ('sw_power_cap', 0x4))
 
-    def __init__(self, index):
+    def __init__(self, index, interval_s=0.1):
         self.index = index
+        self.interval = interval_s
         self.rows = []
-        self.proc = None
+        self.th = None
+        self._stop = threading.Event()
+        self.err = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(
-                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '100'],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.th = threading.Thread(target=self._read, daemon=True)
-            self.th.start()
-        except Exception:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            idx = self.index
+            if vis:
+                try:
+                    idx = int(vis.split(',')[self.index])
+                except ValueError:
+                    idx = self.index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:
+            self.err = '%s: %s' % (type(e).__name__, e)
+            return
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(',')])
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                self.rows.append((mhz, mask))
+            except Exception as e:
+                self.err = '%s: %s' % (type(e).__name__, e)
+                return
+            self._stop.wait(self.interval)
 
     def stop(self):
-        if self.proc is None:
-            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-            except Exception:
-                continue
-            for n, v in zip(names, r[3:7]):
-                if v.lower().startswith('active'):
-                    reasons.add(n)
-        # "under load": drop idle samples taken before the first kernel landed
-        load = [s for s in sm if s > 0]
-        return {'sm_mhz': statistics.median(load) if load else None,
-                'sm_max_mhz': max(mx) if mx else None, 'reasons': sorted(reasons), 'samples': len(sm)}
+        if self.th is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['NVML unavailable: %s' % self.err]}
+        self._stop.set()
+        self.th.join(timeout=5)
+        sm = [r[0] for r in self.rows if r[0] > 0]
+        reasons = sorted({name for _, mask in self.rows for name, bit in self.REASONS if mask & bit})
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': self.max_mhz, 'reasons': reasons,
+                'samples': len(self.rows), 'how': 'NVML in-process, every %d ms' % int(self.interval * 1e3)}
 
 
 def reference_arm(args):
@@ -185,6 +199,14 @@ def trace_steps(run_step, rank, kf):
     busy = sum(e['dur'] for e in ev)
     print('[trace] 4 steps: span %.3f ms/step, sum of kernel durations %.3f ms/step, %d kernels/step' %
           (span / 4e3, busy / 4e3, len(ev) // 4), file=sys.stderr)
+    agg = {}
+    for e in ev:
+        k = e['name'][:120]
+        t = agg.setdefault(k, [0.0, 0])
+        t[0] += e['dur']
+        t[1] += 1
+    for name, (dur, cnt) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:int(os.environ.get('KUNGFU_TRACE_TOP', '0'))]:
+        print('[trace-top] %8.3f ms/step %5d x  %s' % (dur / 4e3, cnt // 4, name), file=sys.stderr)
     last_model = None
     for e in ev:
         if e in ours:
@@ -338,7 +360,7 @@ def main():
         mx = kf.ops.all_reduce_fn(torch.tensor([ms], dtype=torch.float64), 'max')
         return float(mx[0]), K.launch_count - before
 
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, args.clock_interval_ms / 1e3)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)

@@ -36,17 +36,23 @@ def test_optimizers(kind, np_):
 
 
 def test_mnist_slp_np_invariance(tmp_path):
-    outs = []
-    for np_ in (1, 2, 4):
-        out = str(tmp_path / ('slp%d.pt' % np_))
-        _ok(run_workers(np_, os.path.join(W, 'mnist_slp_worker.py'), args=['48', '40', out]), np_)
-        outs.append(torch.load(out))
-    for o in outs[1:]:
-        # same mathematics, different fp32 summation order across the splits
-        assert torch.allclose(o['w'], outs[0]['w'], atol=2e-4)
-        assert torch.allclose(o['b'], outs[0]['b'], atol=2e-4)
-        assert abs(o['acc'] - outs[0]['acc']) <= 1e-3
-    assert outs[0]['acc'] > 0.3
+    """S-SGD with np workers == one worker on the global batch, np in {1, 2, 3, 4}
+    (/root/reference/tests/python/integration/test_mnist_slp.py:153-176 demands the same accuracy to 1e-6).
+    In float64 the only difference between the splits is the order of a few additions: the weights agree
+    to 1e-12 and the accuracy exactly. In float32 (the reference's precision) that reordering is visible
+    in the last bits of every gradient sum; over 40 steps it reaches a few 1e-5 (bound used: 1e-4) and the accuracy, a count
+    over 2000 samples, is still identical."""
+    for dt, tol in (('f64', 1e-12), ('f32', 1e-4)):
+        outs = []
+        for np_ in (1, 2, 3, 4):
+            out = str(tmp_path / ('slp%d%s.pt' % (np_, dt)))
+            _ok(run_workers(np_, os.path.join(W, 'mnist_slp_worker.py'), args=['48', '40', out, dt]), np_)
+            outs.append(torch.load(out))
+        for o in outs[1:]:
+            assert torch.allclose(o['w'], outs[0]['w'], atol=tol, rtol=0), (dt, (o['w'] - outs[0]['w']).abs().max())
+            assert torch.allclose(o['b'], outs[0]['b'], atol=tol, rtol=0), (dt, (o['b'] - outs[0]['b']).abs().max())
+            assert abs(o['acc'] - outs[0]['acc']) <= 1e-6, (dt, o['acc'], outs[0]['acc'])
+        assert outs[0]['acc'] > 0.3
 
 
 def test_bad_worker_tears_down_job(tmp_path):

@@ -12,15 +12,16 @@ import kungfu_b200.torch as kf
 rank, np_ = kf.current_rank(), kf.current_cluster_size()
 global_batch, steps = int(sys.argv[1]), int(sys.argv[2])
 out_path = sys.argv[3]
+dtype = torch.float64 if (len(sys.argv) > 4 and sys.argv[4] == 'f64') else torch.float32
 assert global_batch % np_ == 0
 local = global_batch // np_
 
 g = torch.Generator().manual_seed(2020)
-X = torch.rand(steps * global_batch, 784, generator=g)
-W_true = torch.randn(784, 10, generator=g)
+X = torch.rand(steps * global_batch, 784, generator=g).to(dtype)
+W_true = torch.randn(784, 10, generator=g).to(dtype)
 Y = (X @ W_true).argmax(1)
 
-model = torch.nn.Linear(784, 10)
+model = torch.nn.Linear(784, 10).to(dtype)
 torch.nn.init.zeros_(model.weight)
 torch.nn.init.zeros_(model.bias)
 opt = torch.optim.SGD(model.parameters(), lr=0.1)
