@@ -223,6 +223,14 @@ int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached)
     return done(p, ok);
 }
 
+int kf_peek_cluster_change(kf_peer *p, int *differs)
+{
+    bool d        = false;
+    const bool ok = p->peer->peek_cluster_change(&d);
+    if (differs) *differs = d ? 1 : 0;
+    return done(p, ok);
+}
+
 int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached)
 {
     bool c = false, d = false;

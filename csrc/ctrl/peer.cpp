@@ -248,10 +248,8 @@ bool Peer::propose(const Cluster &next, bool *changed, bool *detached)
     return true;
 }
 
-bool Peer::resize_cluster_from_url(bool *changed, bool *detached)
+bool Peer::fetch_agreed_cluster(Cluster *out)
 {
-    *changed = *detached = false;
-    if (cfg_.single) return true;
     Cluster next;
     for (int attempt = 0;; ++attempt) {
         next = cluster();
@@ -276,8 +274,28 @@ bool Peer::resize_cluster_from_url(bool *changed, bool *detached)
         if (attempt % 20 == 0) KF_WARN("diverged cluster proposals, retrying");
         std::this_thread::sleep_for(std::chrono::milliseconds(50));
     }
+    *out = next;
+    return true;
+}
+
+bool Peer::resize_cluster_from_url(bool *changed, bool *detached)
+{
+    *changed = *detached = false;
+    if (cfg_.single) return true;
+    Cluster next;
+    if (!fetch_agreed_cluster(&next)) return false;
     if (!propose(next, changed, detached)) return false;
     if (*changed && !*detached) return update_to(next.workers);
+    return true;
+}
+
+bool Peer::peek_cluster_change(bool *differs)
+{
+    *differs = false;
+    if (cfg_.single) return true;
+    Cluster next;
+    if (!fetch_agreed_cluster(&next)) return false;
+    *differs = next.bytes() != cluster().bytes();
     return true;
 }
 

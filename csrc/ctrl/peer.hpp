@@ -76,6 +76,7 @@ class Peer
     int64_t next_handle_ = 1;
     bool async_stop_     = false;
     void async_loop();
+    bool fetch_agreed_cluster(Cluster *out);
 
     bool update_to(const PeerList &workers);
     bool propose(const Cluster &next, bool *changed, bool *detached);
@@ -100,6 +101,10 @@ class Peer
     // elastic
     bool resize_cluster(int new_size, bool *changed, bool *detached);
     bool resize_cluster_from_url(bool *changed, bool *detached);
+    // Does the config server publish a cluster other than the current one? Same fetch + byte
+    // consensus as resize_cluster_from_url (every rank gets the same answer), nothing is changed:
+    // lets a caller prepare (e.g. make sharded optimizer state whole) only when a resize is coming.
+    bool peek_cluster_change(bool *differs);
     bool propose_new_size(int new_size);
 
     // p2p model store

@@ -21,7 +21,7 @@ import torch.nn.functional as F
 import kungfu_b200.torch as kf
 from kungfu_b200 import models
 from kungfu_b200.optim import FusedSGD
-from kungfu_b200.torch.elastic import ElasticState
+from kungfu_b200.torch.elastic import ElasticState, warm_up
 from kungfu_b200.torch.policy import NoiseScaleElasticPolicy
 
 ap = argparse.ArgumentParser()
@@ -31,19 +31,24 @@ ap.add_argument('--steps', type=int, default=120)
 ap.add_argument('--max-size', type=int, default=8)
 ap.add_argument('--check-every', type=int, default=10)
 ap.add_argument('--image-size', type=int, default=224)
+ap.add_argument('--report-every', type=int, default=20)
 args = ap.parse_args()
 
 torch.cuda.set_device(kf.get_cuda_index())
 dev = torch.device('cuda', torch.cuda.current_device())
 torch.backends.cudnn.benchmark = True
 model = models.to_b200_layout(getattr(models, args.model)(fused_bn=True).to(dev))
+x = torch.randn(args.batch_size, 3, args.image_size, args.image_size, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+y = torch.randint(0, 1000, (args.batch_size, ), device=dev)
+# Nothing above has touched the control plane yet (the device index comes from the launcher's environment):
+# a worker that joins a running job finishes cuDNN's algorithm search on its own first, so that the first
+# steps of the grown cluster do not run at the speed of its autotuning.
+warm_up(model, lambda: (x, y), lambda out, tgt: F.cross_entropy(out.float(), tgt), steps=3)
 opt = kf.optimizers.MonitorGradientNoiseScaleOptimizer(
     FusedSGD(model.parameters(), lr=0.01, momentum=0.9), model.named_parameters(), device_batch_size=args.batch_size)
 state = ElasticState(model, opt, max_step=args.steps)
 policy = NoiseScaleElasticPolicy(opt, args.batch_size, max_size=args.max_size, check_every=args.check_every,
                                  min_steps_between=2 * args.check_every)
-x = torch.randn(args.batch_size, 3, args.image_size, args.image_size, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
-y = torch.randint(0, 1000, (args.batch_size, ), device=dev)
 t0, n0 = time.time(), state.trained_samples
 while not state.should_stop():
     opt.zero_grad(set_to_none=True)
@@ -55,7 +60,7 @@ while not state.should_stop():
     policy.after_step(state)
     if state.stopped:
         break
-    if kf.current_cluster_size() != np_before or state.step % 20 == 0:
+    if kf.current_cluster_size() != np_before or state.step % args.report_every == 0:
         torch.cuda.synchronize()
         dt = time.time() - t0
         if kf.current_rank() == 0:

@@ -66,6 +66,9 @@ int kf_request(kf_peer *p, int target_rank, const char *version, const char *nam
 /* elastic control */
 int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached);
 int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached);
+/* *differs = 1 if the config server publishes a cluster other than the current one (same fetch +
+ * consensus as above, nothing is changed). Collective. */
+int kf_peek_cluster_change(kf_peer *p, int *differs);
 int kf_propose_new_size(kf_peer *p, int new_size);
 
 /* adaptation / monitoring */

@@ -84,6 +84,7 @@ def _declare(l):
     f('kf_request', C.c_int, _VP, C.c_int, C.c_char_p, C.c_char_p, _VP, C.c_int64)
     f('kf_resize_cluster', C.c_int, _VP, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int))
     f('kf_resize_cluster_from_url', C.c_int, _VP, C.POINTER(C.c_int), C.POINTER(C.c_int))
+    f('kf_peek_cluster_change', C.c_int, _VP, C.POINTER(C.c_int))
     f('kf_propose_new_size', C.c_int, _VP, C.c_int)
     f('kf_set_tree', C.c_int, _VP, C.POINTER(C.c_int32), C.c_int)
     f('kf_set_strategy', C.c_int, _VP, C.c_char_p)
@@ -230,6 +231,11 @@ class Peer(object):
         ch, det = C.c_int(0), C.c_int(0)
         _check(lib().kf_resize_cluster(self._h, n, C.byref(ch), C.byref(det)), 'resize_cluster')
         return bool(ch.value), bool(det.value)
+
+    def peek_cluster_change(self):
+        d = C.c_int(0)
+        _check(lib().kf_peek_cluster_change(self._h, C.byref(d)), 'peek_cluster_change')
+        return bool(d.value)
 
     def resize_cluster_from_url(self):
         ch, det = C.c_int(0), C.c_int(0)

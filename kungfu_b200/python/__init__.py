@@ -104,6 +104,13 @@ def resize_cluster_from_url():
     return changed, det
 
 
+def cluster_change_pending():
+    """True if the config server publishes a cluster other than the current one, i.e. the next
+    resize_cluster_from_url() will change the membership. Collective (every worker gets the same
+    answer); nothing is changed. Lets a training loop prepare for a resize only when one is coming."""
+    return _p().peek_cluster_change()
+
+
 def _on_membership_change(detached=False):
     try:
         from ..torch.ops import collective as tops

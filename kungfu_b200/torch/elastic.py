@@ -16,18 +16,50 @@ from .ops import collective as tops
 
 
 class ResizeProfiler(object):
+    """Durations of resizes as a survivor sees them, in two parts: waiting for the
+    new membership (consensus, runners spawning joiners, joiners starting: nothing
+    a survivor can speed up) and the state hand-over (re-mapping peer memory,
+    re-creating arenas, broadcasting model and optimizer state)."""
+
     def __init__(self):
         self.records = []
+        self.phases = []  # (old, new, membership_s, handover_s)
         self._t0 = None
+        self._t1 = None
 
     def begin(self):
         self._t0 = time.time()
+        self._t1 = None
+
+    def membership_done(self):
+        self._t1 = time.time()
 
     def end(self, old, new):
-        self.records.append((old, new, time.time() - self._t0))
+        now = time.time()
+        self.records.append((old, new, now - self._t0))
+        t1 = self._t1 if self._t1 is not None else self._t0
+        self.phases.append((old, new, t1 - self._t0, now - t1))
 
     def report(self):
-        return ['resize %d -> %d took %.3fs' % r for r in self.records]
+        return ['resize %d -> %d took %.3fs (membership %.3fs, state hand-over %.3fs)' % (r + p[2:])
+                for r, p in zip(self.records, self.phases)]
+
+
+def warm_up(model, make_batch, loss_fn, steps=2):
+    """Run a few LOCAL forward/backward passes (no optimizer, no communication)
+    and drop the gradients: cuDNN's algorithm search, the allocator's first
+    growth and lazy module loading then happen before this worker talks to the
+    cluster. A worker that joins a running job should call this BEFORE its first
+    kungfu call (the control plane starts on first use): the survivors wait for
+    a joiner at the membership barrier either way, but the first steps of the new
+    cluster then run at full speed instead of waiting for the joiner's autotune."""
+    for _ in range(steps):
+        x, y = make_batch()
+        loss_fn(model(x), y).backward()
+    for p in model.parameters():
+        p.grad = None
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
 
 
 class ElasticState(object):
@@ -80,6 +112,7 @@ class ElasticState(object):
             self.optimizer.consolidate()
         self.last_resize_step = self.step
         changed, detached = kfpy.resize_cluster(new_size)
+        self.profiler.membership_done()
         if detached:
             self.stopped = True
             return False
@@ -128,11 +161,14 @@ class ElasticHook(object):
     def after_step(self):
         self.state.end_step(self.local_batch_size)
         changed = False
-        if self._poll:
+        if self._poll and kfpy.cluster_change_pending():
             self.state.profiler.begin()
             if hasattr(self.state.optimizer, 'consolidate'):
+                # sharded fp32 optimizer state is made whole only when a resize is really coming
+                # (it used to be gathered after every single step)
                 self.state.optimizer.consolidate()
             changed, detached = kfpy.resize_cluster_from_url()
+            self.state.profiler.membership_done()
             if detached:
                 self.exit_reason = 'change cluster'
                 return False
