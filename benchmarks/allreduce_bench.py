@@ -82,7 +82,10 @@ blocks_list = [int(x) for x in args.blocks.split(',')]
 rows = []
 if rank == 0:
     print('# np=%d dtype=%s multicast=%s' % (np_, args.dtype, bool(buf.mc_ptr)))
-    print('%-16s %-9s %7s %10s %10s %10s %9s' % ('size', 'algo', 'blocks', 'us', 'algBW GB/s', 'busBW GB/s', 'of 900'))
+    print('# busBW = 2(n-1)/n * bytes/time (nccl-tests convention, comparable across algorithms and with NCCL);')
+    print('# link GB/s = bytes one GPU really sends per direction / time, by the byte model of SURVEY.md 7.5.8:')
+    print('#   one-shot (n-1) S, two-shot 2(n-1)/n S, NVLS S (1 + 1/n); "of 900" is that figure over the nominal link rate')
+    print('%-16s %-9s %7s %10s %10s %10s %10s %9s' % ('size', 'algo', 'blocks', 'us', 'algBW GB/s', 'busBW GB/s', 'link GB/s', 'of 900'))
 for label, nbytes in [(str(s), s) for s in sizes] + named:
     count = nbytes // es
     best = {}
@@ -110,10 +113,14 @@ for label, nbytes in [(str(s), s) for s in sizes] + named:
     for name, (ms, blocks) in best.items():
         alg = nbytes / ms / 1e6
         bus = alg * 2 * (np_ - 1) / max(np_, 1)
+        wire = {'oneshot': float(np_ - 1), 'twoshot': 2.0 * (np_ - 1) / max(np_, 1), 'nvls': 1.0 + 1.0 / max(np_, 1)}.get(name)
+        link = alg * wire if wire is not None else float('nan')
         rows.append({'size': label, 'bytes': nbytes, 'algo': name, 'blocks': blocks, 'us': ms * 1e3,
-                     'algbw_gbs': alg, 'busbw_gbs': bus, 'kungfu_rate_gbs': 4 * (np_ - 1) * nbytes / ms / 1e6})
+                     'algbw_gbs': alg, 'busbw_gbs': bus, 'link_gbs': link, 'link_of_900': link / 900.0,
+                     'kungfu_rate_gbs': 4 * (np_ - 1) * nbytes / ms / 1e6})
         if rank == 0:
-            print('%-16s %-9s %7d %10.1f %10.1f %10.1f %8.1f%%' % (label, name, blocks, ms * 1e3, alg, bus, 100 * bus / 900.0))
+            print('%-16s %-9s %7d %10.1f %10.1f %10.1f %10.1f %8.1f%%' % (label, name, blocks, ms * 1e3, alg, bus, link,
+                                                                     100 * link / 900.0))
 if rank == 0 and args.json:
     with open(args.json, 'w') as f:
         json.dump({'np': np_, 'dtype': args.dtype, 'multicast': bool(buf.mc_ptr), 'rows': rows}, f, indent=1)

@@ -22,12 +22,12 @@ import torch.nn.functional as F
 
 import kungfu_b200.torch as kf
 from kungfu_b200 import models
-from kungfu_b200.optim import FusedSGD
+from kungfu_b200.optim import FusedAdamW, FusedSGD
 
 ap = argparse.ArgumentParser()
 ap.add_argument('--model', default='resnet50')
 ap.add_argument('--optimizer', default='ssgd', choices=['ssgd', 'sma', 'pair', 'gns', 'variance', 'ada', 'none'])
-ap.add_argument('--base', default='fused', choices=['fused', 'sgd', 'adam'])
+ap.add_argument('--base', default='fused', choices=['fused', 'fused-adamw', 'sgd', 'adam', 'adamw'])
 ap.add_argument('--overlap', action='store_true')
 ap.add_argument('--batch-size', type=int, default=256)
 ap.add_argument('--seq-len', type=int, default=128)
@@ -87,8 +87,12 @@ model.train()
 params = list(model.parameters())
 if args.base == 'fused':
     base = FusedSGD(params, lr=0.01, momentum=args.momentum)
+elif args.base == 'fused-adamw':
+    base = FusedAdamW(params, lr=1e-4, weight_decay=0.01)
 elif args.base == 'sgd':
     base = torch.optim.SGD(params, lr=0.01, momentum=args.momentum)
+elif args.base == 'adamw':
+    base = torch.optim.AdamW(params, lr=1e-4, weight_decay=0.01)
 else:
     base = torch.optim.Adam(params, lr=1e-4)
 named = list(model.named_parameters())
