@@ -2,6 +2,7 @@
 # One 8-GPU session: correctness at np=8, overlap A/B, box effects, kernel tables, baselines, other models, elastic growth.
 # Everything is written under gpurun_out/n8/.
 O=gpurun_out/n8; mkdir -p $O
+export KUNGFU_BN_COOP=0   # the cooperative BN launch is validated separately on one GPU
 RUN="kungfu_b200/bin/kungfu-run -q -allow-nvlink -H 127.0.0.1:8"
 tr8() { python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port $((29800 + RANDOM % 100)) "$@"; }
 echo "== [1] multi-GPU correctness at np=8 (NVLS required)"; date +%T
@@ -20,7 +21,6 @@ for m in ref-nccl-fused ref-nccl-unfused; do $RUN -np 8 python benchmarks/baseli
 echo "== [7] other models N=8"; date +%T
 $RUN -np 8 python benchmarks/train_bench.py --model densenet121 --optimizer sma --batch-size 128 --steps 30 2>&1 | grep RESULT | tee -a $O/models8.txt
 $RUN -np 8 python benchmarks/train_bench.py --model bert_base --optimizer pair --base fused-adamw --batch-size 32 --graph --pair-device-select 1 --fused-ln 1 --fused-grads 1 --fused-linear 1 --pad-vocab 8 --mlm-positions 20 --steps 40 2>&1 | grep RESULT | tee -a $O/models8.txt
-$RUN -np 8 python benchmarks/train_bench.py --model vgg16 --optimizer ssgd --batch-size 128 --steps 20 2>&1 | grep RESULT | tee -a $O/models8.txt
 echo "== [8] elastic ResNet-50, noise-scale driven growth 1 -> 2 -> 4 -> 8"; date +%T
 kungfu_b200/bin/kungfu-run -q -w -builtin-config-port 9100 -np 1 -H 127.0.0.1:8 -allow-nvlink -timeout 300s python examples/elastic_resnet_gns.py --steps 160 --batch-size 128 --check-every 10 --report-every 5 > $O/elastic_1_2_4_8.txt 2>&1; grep -E "^step|resize|finished" $O/elastic_1_2_4_8.txt | cut -c1-260 | tail -45
 date +%T
