@@ -170,7 +170,11 @@ int kfb_fuse(void *const *srcs, const int64_t *counts, const int64_t *dst_offs,
  *    ordered on one stream are fine. Nothing in it needs clearing: every slot
  *    that is read was written by the same call.
  * Inputs, outputs and semantics are those of kfb_fuse; the norm is summed in
- * one fixed order (equal to kfb_fuse within fp32 rounding). */
+ * one fixed order (equal to kfb_fuse within fp32 rounding). Unlike kfb_fuse it
+ * does not cut a very large tensor into pieces first (that needs a host-side
+ * list whose length depends on the sizes): every tensor is streamed by 16 CTAs,
+ * so a single gradient of tens of millions of elements is copied well below
+ * HBM speed; hand such tensors to kfb_fuse, or split them in the caller. */
 #define KFB_FUSE_NOALLOC_MAX_TENSORS 1024
 int kfb_fuse_noalloc(void *const *srcs, const int64_t *counts,
                      const int64_t *dst_offs, int n, int src_dtype, void *dst,
