@@ -51,8 +51,9 @@ def parse_args():
                     help='evaluate the 7x7/2 stem as a 4x4 conv over a space-to-depth input (same maths)')
     ap.add_argument('--momentum', type=float, default=0.0)
     ap.add_argument('--skip-e2e', action='store_true')
-    ap.add_argument('--overlap', type=int, default=int(os.environ.get('KUNGFU_BENCH_OVERLAP', '1')),
-                    help='launch the fused exchange+update bucket by bucket from autograd hooks, under backward')
+    ap.add_argument('--overlap', type=int, default=int(os.environ.get('KUNGFU_BENCH_OVERLAP', '0')),
+                    help='launch the fused exchange+update bucket by bucket from autograd hooks, under backward '
+                         '(measured on 2 and 8 B200: within +-0.3 %% of the single launch, see profiles/overlap_ab_b200.txt)')
     ap.add_argument('--same-box-baseline', default=os.environ.get('KUNGFU_BENCH_BASELINE', 'ddp'),
                     choices=['ddp', 'none'],
                     help='after the timed region, also time stock PyTorch (torchvision-style ResNet-50, torch BN, '

@@ -12,8 +12,8 @@ step 4, on consensus set_tree([1]*np) = star rooted at rank 1).
 On GPUs the gradients never touch the host runtime: the statistics come from
 the device kernels of the TRAINING step (bytes and CUDA-event time per kernel
 variant), and what the vote replaces is the kernel variant (one-shot /
-two-shot / NVLS). --inject-slow makes the active variant run on a single CTA on
-a majority of the workers from step 6 on, which the vote then detects."""
+two-shot / NVLS). --inject-slow makes the active variant run on a single CTA
+from step 6 on, which the vote then detects."""
 import os
 import sys
 
@@ -45,7 +45,8 @@ if '--cuda' in sys.argv:
         F.cross_entropy(model(x).float(), y).backward()
         opt.step()
         kfpy.calc_stats()
-        if step == 6 and '--inject-slow' in sys.argv and kf.current_rank() <= np_ // 2:
+        if step == 6 and '--inject-slow' in sys.argv:
+            # (job-wide: a collective kernel needs the same grid on every rank)
             coll.SLOW_VARIANT = opt.comm.stats.active
         if step > 4 and step % 2 == 1 and kfpy.check_interference():
             coll.SLOW_VARIANT = None

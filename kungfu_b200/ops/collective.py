@@ -23,6 +23,8 @@ PREFERRED_LARGE = None
 
 # Fault injection for the interference vote (tests, examples/adapt_strategy.py): the variant with
 # this code runs on a single CTA, i.e. at a fraction of its bandwidth, until it is set back to None.
+# Set it on EVERY rank at the same point: a collective kernel needs the same grid everywhere (CTA b of
+# one rank meets CTA b of the others).
 SLOW_VARIANT = None
 
 
@@ -83,7 +85,7 @@ def all_reduce(comm, buf, count, dtype, op='sum', scale=1.0, algo=None, out=None
 
 
 def broadcast(comm, buf, nbytes, root=0, byte_offset=0, use_multicast=True,
-              blocks=None, threads=None, stream=None):
+              blocks=None, threads=None, stream=None, channel=0):
     """Every rank's buf[byte_offset : +nbytes] := root's (in place)."""
     out_arr, _k = buf.ptr_array(byte_offset)
     if comm.emulated:
@@ -91,8 +93,8 @@ def broadcast(comm, buf, nbytes, root=0, byte_offset=0, use_multicast=True,
     else:
         src = buf.ptrs[comm.rank] + byte_offset
     mc = (buf.mc_ptr + byte_offset) if (buf.mc_ptr and use_multicast) else None
-    K.call('kfb_broadcast', comm.cstruct, root, src, out_arr, mc, nbytes,
-           blocks or comm.default_blocks, threads or comm.default_threads,
+    K.call('kfb_broadcast', comm.channel(channel), root, src, out_arr, mc, nbytes,
+           comm.channel_blocks(channel, blocks), threads or comm.default_threads,
            K.stream_ptr(stream))
 
 

@@ -92,11 +92,15 @@ def drop_staging(comm):
     _comm_stream.pop(id(comm), None)
 
 
-def _cuda_all_reduce(x, y, op):
+ASYNC_CHANNEL = 1  # the asynchronous ops run on a side stream: their own CTA rows, epochs and staging buffers
+
+
+def _cuda_all_reduce(x, y, op, channel=0):
     from ...ops import _cuda as K
     from ...ops import collective as coll
     comm = _comm()
     opc = K.OPS[op]
+    tag = '' if channel == 0 else str(channel)
     if comm.cross:
         # job spans hosts: NVLink inside the host, control plane between host masters
         xc = x.contiguous()
@@ -113,23 +117,24 @@ def _cuda_all_reduce(x, y, op):
     xc = x.contiguous()
     nbytes = xc.numel() * xc.element_size()
     pad = (nbytes + 15) // 16 * 16
-    src = _stage(comm, 'in', pad)
+    src = _stage(comm, 'in' + tag, pad)
     src.local[:nbytes].copy_(xc.view(-1).view(torch.uint8))
     code = K.dtype_code(x.dtype)
     algo = coll.choose_algo(comm, nbytes, src, opc, code)
     if algo == K.ALGO_ONESHOT:
-        dst = _stage(comm, 'out', pad)
-        coll.all_reduce(comm, src, xc.numel(), code, opc, algo=algo, out=dst)
+        dst = _stage(comm, 'out' + tag, pad)
+        coll.all_reduce(comm, src, xc.numel(), code, opc, algo=algo, out=dst, channel=channel)
     else:
         dst = src
-        coll.all_reduce(comm, src, xc.numel(), code, opc, algo=algo)
+        coll.all_reduce(comm, src, xc.numel(), code, opc, algo=algo, channel=channel)
     out = dst.local[:nbytes].view(x.dtype).view(xc.shape)
     y.copy_(out)
 
 
-def _cuda_broadcast(x):
+def _cuda_broadcast(x, channel=0):
     from ...ops import collective as coll
     comm = _comm()
+    tag = '' if channel == 0 else str(channel)
     if comm.cross:
         # rare, latency-insensitive op: stage through the host control plane
         h = x.detach().contiguous().cpu().view(-1)
@@ -141,10 +146,10 @@ def _cuda_broadcast(x):
         return
     xc = x.contiguous()
     nbytes = xc.numel() * xc.element_size()
-    buf = _stage(comm, 'in', (nbytes + 15) // 16 * 16)
+    buf = _stage(comm, 'in' + tag, (nbytes + 15) // 16 * 16)
     if comm.rank == 0:
         buf.local[:nbytes].copy_(xc.view(-1).view(torch.uint8))
-    coll.broadcast(comm, buf, (nbytes + 15) // 16 * 16, root=0)
+    coll.broadcast(comm, buf, (nbytes + 15) // 16 * 16, root=0, channel=channel)
     x.copy_(buf.local[:nbytes].view(x.dtype).view(xc.shape))
 
 
@@ -225,7 +230,7 @@ def inplace_all_reduce_async_op(x, name=None, op=None):
         s = _stream_for(comm)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
-            _cuda_all_reduce(x, x, op)
+            _cuda_all_reduce(x, x, op, channel=ASYNC_CHANNEL)
             ev = torch.cuda.Event()
             ev.record(s)
         x.record_stream(s)
@@ -246,7 +251,7 @@ def inplace_broadcast_async_op(x, name=None):
         s = _stream_for(comm)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
-            _cuda_broadcast(x)
+            _cuda_broadcast(x, channel=ASYNC_CHANNEL)
             ev = torch.cuda.Event()
             ev.record(s)
         x.record_stream(s)
