@@ -397,110 +397,6 @@ __global__ void __launch_bounds__(BN_THREADS, RES ? 3 : KFB_BN_BWD_OCC)
     bn_bwd_apply_body<T, RELU, RES>(dy, x, mask, weight, mean, invstd, sums, dx, dres, rows, C);
 }
 
-// ---- one cooperative launch per direction -------------------------------------------------
-// statistics -> grid barrier -> finalize (spread over all CTAs: one warp per channel, lanes over
-// the per-CTA partials in a fixed order) -> grid barrier -> apply. Against three launches this
-// saves two launch gaps and a finalize kernel that runs on C/32 CTAs, which is most of the time of
-// the layers with few rows (14x14 and 7x7 feature maps); and when the tensor fits in the 126 MB L2
-// the apply phase re-reads it from there (it walks the rows from the end, the part the statistics
-// phase touched last).
-__device__ __forceinline__ void
-coop_reduce_partials(const float *partial, int nblocks, int C, int c, double *s_out, double *q_out)
-{
-    // one warp: lane l adds partials l, l+32, ... then a fixed shuffle tree (deterministic)
-    const int lane = threadIdx.x & 31;
-    double s = 0.0, q = 0.0;
-    for (int b = lane; b < nblocks; b += 32) {
-        s += (double)__ldcg(partial + (size_t)b * 2 * C + c);
-        q += (double)__ldcg(partial + (size_t)b * 2 * C + C + c);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s += __shfl_xor_sync(0xffffffffu, s, o);
-        q += __shfl_xor_sync(0xffffffffu, q, o);
-    }
-    *s_out = s;
-    *q_out = q;
-}
-
-}  // namespace kfb
-#include <cooperative_groups.h>
-namespace kfb {
-namespace cg = cooperative_groups;
-
-template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(BN_THREADS, (RELU && RES) ? 3 : 4)
-    k_bn_fwd_coop(const uint4 *__restrict__ x, const uint4 *__restrict__ res, uint4 *__restrict__ y,
-                  const float *__restrict__ weight, const float *__restrict__ bias, float *running_mean,
-                  float *running_var, float *save_mean, float *save_invstd, long long rows, int C, float eps,
-                  float momentum, uint8_t *__restrict__ mask, float *partial)
-{
-    extern __shared__ float smem[];
-    cg::grid_group grid = cg::this_grid();
-    bn_stats_body<T>(x, rows, C, partial, smem);
-    __threadfence();
-    grid.sync();
-    const int warps = BN_THREADS / 32, wid = threadIdx.x >> 5;
-    for (int c = blockIdx.x * warps + wid; c < C; c += gridDim.x * warps) {
-        double s, q;
-        coop_reduce_partials(partial, gridDim.x, C, c, &s, &q);
-        if ((threadIdx.x & 31) == 0) {
-            const double mean = s / (double)rows;
-            double var        = q / (double)rows - mean * mean;
-            if (var < 0.0) var = 0.0;
-            save_mean[c]   = (float)mean;
-            save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
-            if (running_mean) {
-                const double unbiased = rows > 1 ? var * (double)rows / (double)(rows - 1) : var;
-                running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
-                running_var[c]  = (float)((1.0 - momentum) * running_var[c] + momentum * unbiased);
-            }
-        }
-    }
-    __threadfence();
-    grid.sync();
-    bn_apply_body<T, RELU, RES>(x, res, y, weight, bias, save_mean, save_invstd, rows, C, mask);
-}
-
-template <typename T, bool RELU, bool RES>
-__global__ void __launch_bounds__(BN_THREADS, RES ? 3 : KFB_BN_BWD_OCC)
-    k_bn_bwd_coop(const uint4 *__restrict__ dy, const uint4 *__restrict__ x, const uint8_t *__restrict__ mask,
-                  const float *__restrict__ weight, const float *__restrict__ mean, const float *__restrict__ invstd,
-                  uint4 *__restrict__ dx, uint4 *__restrict__ dres, float *dweight, float *dbias, long long rows, int C,
-                  float *partial, float *sums)
-{
-    extern __shared__ float smem[];
-    cg::grid_group grid = cg::this_grid();
-    bn_bwd_stats_body<T, RELU>(dy, x, mask, mean, invstd, rows, C, partial, smem);
-    __threadfence();
-    grid.sync();
-    const int warps = BN_THREADS / 32, wid = threadIdx.x >> 5;
-    for (int c = blockIdx.x * warps + wid; c < C; c += gridDim.x * warps) {
-        double s, q;
-        coop_reduce_partials(partial, gridDim.x, C, c, &s, &q);
-        if ((threadIdx.x & 31) == 0) {
-            sums[c]     = (float)s;
-            sums[C + c] = (float)q;
-            if (dbias) dbias[c] = (float)s;
-            if (dweight) dweight[c] = (float)q;
-        }
-    }
-    __threadfence();
-    grid.sync();
-    bn_bwd_apply_body<T, RELU, RES>(dy, x, mask, weight, mean, invstd, sums, dx, dres, rows, C);
-}
-
-// 0 = three launches per direction, 1 = one cooperative launch (default)
-static int bn_coop_mode()
-{
-    static int mode = -1;
-    if (mode < 0) {
-        const char *e = getenv("KUNGFU_BN_COOP");
-        mode          = (e && e[0] == '0') ? 0 : 1;
-    }
-    return mode;
-}
-
 static int bn_grid(long long rows, int C)
 {
     const int RY      = BN_THREADS / (C >> 3);
@@ -559,24 +455,6 @@ static int bn_fwd_t(const void *x, const void *residual, void *y, const float *w
 {
     const int grid = bn_grid(rows, C);
     const int RY   = BN_THREADS / (C >> 3);
-    if (training && bn_coop_mode()) {
-        const size_t smem = (size_t)RY * C * sizeof(float);
-        const uint4 *xp = reinterpret_cast<const uint4 *>(x), *rp = reinterpret_cast<const uint4 *>(residual);
-        uint4 *yp       = reinterpret_cast<uint4 *>(y);
-        void *argv[]    = {(void *)&xp, (void *)&rp, (void *)&yp, (void *)&weight, (void *)&bias, (void *)&running_mean,
-                           (void *)&running_var, (void *)&save_mean, (void *)&save_invstd, (void *)&rows, (void *)&C,
-                           (void *)&eps, (void *)&momentum, (void *)&mask, (void *)&scratch};
-#define KFB_BN_COOP(R, S)                                                                                   \
-    KFB_CUDA_OK(cudaLaunchCooperativeKernel((const void *)k_bn_fwd_coop<T, R, S>,                           \
-                                            dim3(std::min(grid, one_wave(k_bn_fwd_coop<T, R, S>, smem))),   \
-                                            dim3(BN_THREADS), argv, smem, s))
-        if (relu && residual) KFB_BN_COOP(true, true);
-        else if (relu) KFB_BN_COOP(true, false);
-        else if (residual) KFB_BN_COOP(false, true);
-        else KFB_BN_COOP(false, false);
-#undef KFB_BN_COOP
-        return KFB_OK;
-    }
     if (training) {
         const size_t smem = (size_t)RY * C * sizeof(float);
         const int gs      = std::min(grid, one_wave(k_bn_stats<T>, smem));
@@ -632,22 +510,6 @@ static int bn_bwd_t(const void *dy, const void *x, const void *mask, const float
     const uint4 *gp = reinterpret_cast<const uint4 *>(dy), *xp = reinterpret_cast<const uint4 *>(x)
                 ;
     const uint8_t *yp = reinterpret_cast<const uint8_t *>(mask);
-    if (bn_coop_mode()) {
-        uint4 *dxp0 = reinterpret_cast<uint4 *>(dx), *drp0 = reinterpret_cast<uint4 *>(dres);
-        void *argv[] = {(void *)&gp, (void *)&xp, (void *)&yp, (void *)&weight, (void *)&save_mean, (void *)&save_invstd,
-                        (void *)&dxp0, (void *)&drp0, (void *)&dweight, (void *)&dbias, (void *)&rows, (void *)&C,
-                        (void *)&scratch, (void *)&sums};
-#define KFB_BN_COOP(R, S)                                                                                   \
-    KFB_CUDA_OK(cudaLaunchCooperativeKernel((const void *)k_bn_bwd_coop<T, R, S>,                           \
-                                            dim3(std::min(grid, one_wave(k_bn_bwd_coop<T, R, S>, smem))),   \
-                                            dim3(BN_THREADS), argv, smem, s))
-        if (relu && dres) KFB_BN_COOP(true, true);
-        else if (relu) KFB_BN_COOP(true, false);
-        else if (dres) KFB_BN_COOP(false, true);
-        else KFB_BN_COOP(false, false);
-#undef KFB_BN_COOP
-        return KFB_OK;
-    }
     const int gs = std::min(grid, relu ? one_wave(k_bn_bwd_stats<T, true>, smem) : one_wave(k_bn_bwd_stats<T, false>, smem));
     if (relu)
         k_bn_bwd_stats<T, true><<<gs, BN_THREADS, smem, s>>>(gp, xp, yp, save_mean, save_invstd, rows, C, scratch);

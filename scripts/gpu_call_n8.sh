@@ -2,7 +2,6 @@
 # One 8-GPU session: correctness at np=8, overlap A/B, box effects, kernel tables, baselines, other models, elastic growth.
 # Everything is written under gpurun_out/n8/.
 O=gpurun_out/n8; mkdir -p $O
-export KUNGFU_BN_COOP=0   # the cooperative BN launch is validated separately on one GPU
 RUN="kungfu_b200/bin/kungfu-run -q -allow-nvlink -H 127.0.0.1:8"
 tr8() { python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port $((29800 + RANDOM % 100)) "$@"; }
 echo "== [1] multi-GPU correctness at np=8 (NVLS required)"; date +%T
