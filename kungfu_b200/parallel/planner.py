@@ -214,8 +214,13 @@ class VariantChooser(object):
                     continue
                 self.table[nbytes][algo] = self._time(
                     lambda: coll.all_reduce(comm, buf, nbytes // es, code, 'sum', algo=algo, out=out))
+            if not self.table[nbytes]:
+                del self.table[nbytes]  # nothing left that can serve this size
+                continue
             self.best[nbytes] = min(self.table[nbytes], key=self.table[nbytes].get)
-        big = max(sizes)
+        if not self.table:
+            return
+        big = max(self.table)
         for algo, ms in self.table[big].items():
             self.reference[algo] = big / ms / 1e6 * 2 * (comm.np - 1) / comm.np
         self._install()
@@ -325,10 +330,14 @@ class DevicePlanner(object):
         if total * 2 <= comm.np:
             return False
         active = comm.stats.active
+        large = [K.ALGO_TWOSHOT] + ([K.ALGO_NVLS] if getattr(comm, 'multicast_ok', False) else [])
+        alternatives = [a for a in large if a != active and a not in self.chooser.disabled]
+        if active in large and not alternatives:
+            # the vote passed but there is nothing to switch to (no multicast: two-shot is the only
+            # large-message variant); the caller still learns that the workers see interference
+            return True
         if active in (K.ALGO_ONESHOT, K.ALGO_TWOSHOT, K.ALGO_NVLS):
             self.chooser.disabled.add(active)
-            if len(self.chooser.disabled) >= 3:
-                self.chooser.disabled = {active}
             self.chooser.probe(sizes=(1 << 20, 16 << 20))
             self.chooser.switches += 1
             # the new variant starts a fresh reference window

@@ -33,6 +33,10 @@ while True:
     assert torch.isfinite(loss) and torch.equal(w[0], w[-1]), 'replicas diverged at step %d' % hook.state.step
     with open(log_path, 'a') as f:
         f.write('%d %d %d %d %.4f\n' % (hook.state.step, kf.current_rank(), np_, os.getpid(), float(loss)))
+    if os.environ.get('KUNGFU_TEST_MEMLOG') and kf.current_rank() == 0:
+        # device memory the driver considers free, as the surviving rank 0 sees it after this step
+        with open(os.environ['KUNGFU_TEST_MEMLOG'], 'a') as f:
+            f.write('%d %d %d\n' % (hook.state.step, np_, torch.cuda.mem_get_info()[0]))
     if not hook.after_step(8):
         break
 print('OK gpu elastic worker pid %d done at step %d np %d' % (os.getpid(), hook.state.step, kf.current_cluster_size()))
