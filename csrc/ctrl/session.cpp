@@ -101,10 +101,24 @@ bool Session::run_graphs(const Workspace &w, const std::vector<const Graph *> &g
         const auto &prevs = g->prevs(rank_);
         const auto &nexts = g->nexts(rank_);
         if (g->is_self_loop(rank_)) {
-            for (int p : prevs) {
-                if (tmp.size() < n) tmp.resize(n);
-                if (!recv_from(p, w.name, tmp.data(), n)) return false;
-                transform2(effective, tmp.data(), w.recv, w.count, w.dtype, w.op);
+            // Fan-in: the receives of all predecessors are posted together (the reference receives
+            // them in parallel, session.go:242-251), the reduction then runs in predecessor order so
+            // that the sum is formed in the same order on every run.
+            const size_t np = prevs.size();
+            if (tmp.size() < n * np) tmp.resize(n * np);
+            std::vector<char> got(np, 1);
+            if (np > 1) {
+                std::vector<std::thread> rx;
+                for (size_t i = 1; i < np; ++i)
+                    rx.emplace_back([&, i] { got[i] = recv_from(prevs[i], w.name, tmp.data() + i * n, n) ? 1 : 0; });
+                got[0] = recv_from(prevs[0], w.name, tmp.data(), n) ? 1 : 0;
+                for (auto &t : rx) t.join();
+            } else if (np == 1) {
+                got[0] = recv_from(prevs[0], w.name, tmp.data(), n) ? 1 : 0;
+            }
+            for (size_t i = 0; i < np; ++i) {
+                if (!got[i]) return false;
+                transform2(effective, tmp.data() + i * n, w.recv, w.count, w.dtype, w.op);
                 effective = w.recv;
                 ++recv_count;
             }
