@@ -178,6 +178,7 @@ class Peer(object):
     def __init__(self, handle):
         self._h = handle
         self._xchg = None
+        self._xchg_version = None
 
     @classmethod
     def from_env(cls):
@@ -222,8 +223,15 @@ class Peer(object):
         _check(lib().kf_barrier(self._h), 'barrier')
 
     def exchange(self):
-        if self._xchg is None or self._xchg.size != self.size() or self._xchg.rank != self.rank():
+        # One Exchange per MEMBERSHIP: its message names are numbered, and a joiner starts counting
+        # at 1, so a survivor must start over too. Size and rank alone do not identify a membership
+        # (1 -> 2 -> 1 -> 2 comes back to the same size and rank with a new peer): the cluster
+        # version does.
+        v = self.cluster_version()
+        if (self._xchg is None or self._xchg_version != v or self._xchg.size != self.size()
+                or self._xchg.rank != self.rank()):
             self._xchg = Exchange(self)
+            self._xchg_version = v
         return self._xchg
 
     # -- elastic ----------------------------------------------------------------------

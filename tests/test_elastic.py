@@ -92,3 +92,12 @@ def test_config_server_rest_api(tmp_path):
     finally:
         if p.poll() is None:
             p.kill()
+
+
+def test_regrow_onto_a_used_address_restarts_the_control_exchange():
+    """1 -> 2 -> 1 -> 2 -> 1 -> 2: same size, same rank, new peer each time (found on GPUs, where the second
+    grow hung in PeerComm's first all-gather because the survivor kept counting message names)."""
+    res = run_workers(1, os.path.join(W, 'regrow_worker.py'), args=['1:1,2:1,1:1,2:1,1:1,2:1,1:1', '7'], timeout=120,
+                      extra_flags=['-w', '-builtin-config-port', str(_free_port())])
+    assert res.returncode == 0, res.stdout[-4000:]
+    assert 'OK regrow worker rank 0 done at step 7' in res.stdout
