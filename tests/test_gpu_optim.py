@@ -227,3 +227,93 @@ def test_grad_variance_and_gns(np_):
         exp_s = S if exp_s is None else 0.9 * exp_s + 0.1 * S
     torch.cuda.synchronize()
     assert abs(float(state[3]) - exp_s / exp_g) < 1e-3 * abs(exp_s / exp_g)
+
+
+@pytest.mark.parametrize('np_', [1, 2, 4, 8])
+@pytest.mark.parametrize('kind', [1, 2])
+def test_ssgd_fused_step_adam_rules(np_, kind):
+    """The fused step with the AdamW (kind 1) / Adam (kind 2) update against torch.optim on the averaged
+    gradient, three consecutive steps with the step number read from device memory (what keeps a captured
+    CUDA graph valid), under single-GPU rank emulation."""
+    torch.manual_seed(10 * np_ + kind)
+    comm = EmulatedComm(np_) if np_ > 1 else LocalComm()
+    n = 8 * 2000
+    grads = comm.alloc(n * 4)
+    params = comm.alloc(n * 4)
+    R = max(np_, 1)
+    p0 = torch.randn(n, device='cuda')
+    master = p0.repeat(R).contiguous()
+    m = torch.zeros_like(master)
+    v = torch.zeros_like(master)
+    step_t = torch.zeros(1, dtype=torch.int64, device='cuda')
+    ref = torch.nn.Parameter(p0.clone())
+    cls = torch.optim.AdamW if kind == 1 else torch.optim.Adam
+    ropt = cls([ref], lr=1e-2, betas=(0.9, 0.99), eps=1e-8, weight_decay=0.05)
+    h = K.SgdHyper()
+    h.lr, h.weight_decay, h.kind = 1e-2, 0.05, kind
+    h.beta1, h.beta2, h.eps = 0.9, 0.99, 1e-8
+    h.step = step_t.data_ptr()
+    h.exp_avg_sq = v.data_ptr()
+    ga, _1 = grads.ptr_array()
+    pa, _2 = params.ptr_array()
+    npk = n // 8
+    per = (npk + R - 1) // R * 8
+    for it in range(3):
+        gs = [torch.randn(n, device='cuda') for _ in range(R)]
+        for r in range(R):
+            grads.view(torch.float32, r if np_ > 1 else None)[:n].copy_(gs[r])
+        K.call('kfb_ssgd_fused_step', comm.cstruct, ga, K.F32, pa, K.F32, master.data_ptr(), m.data_ptr(), n,
+               1.0 / R, C.byref(h), None, comm.default_blocks, 256, K.stream_ptr())
+        step_t.add_(1)
+        torch.cuda.synchronize()
+        ref.grad = torch.stack(gs).sum(0) / R
+        ropt.step()
+        for r in range(R):
+            got = params.view(torch.float32, r if np_ > 1 else None)[:n]
+            assert torch.allclose(got, ref.data, rtol=1e-5, atol=1e-6), (it, r, (got - ref.data).abs().max())
+    st = ropt.state[ref]
+    for r in range(R):
+        lo, hi = min(r * per, n), min((r + 1) * per, n)
+        assert torch.allclose(m[r * n + lo:r * n + hi], st['exp_avg'][lo:hi], rtol=1e-5, atol=1e-7)
+        assert torch.allclose(v[r * n + lo:r * n + hi], st['exp_avg_sq'][lo:hi], rtol=1e-5, atol=1e-9)
+
+
+def test_fused_adamw_optimizer_single_gpu_with_overlap_and_checkpoint():
+    """FusedAdamW through the public wrapper on one GPU: bucketed launches from autograd hooks (local update, no
+    exchange), equality with torch.optim.AdamW, and a state_dict round trip into fresh objects."""
+    from kungfu_b200.optim import FusedAdamW
+    import kungfu_b200.torch as kf
+
+    def make():
+        torch.manual_seed(3)
+        return torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 16)).cuda()
+
+    def batch(step):
+        g = torch.Generator().manual_seed(100 + step)
+        return torch.randn(32, 64, generator=g).cuda(), torch.randint(0, 16, (32, ), generator=g).cuda()
+
+    m, ref = make(), make()
+    opt = kf.optimizers.SynchronousSGDOptimizer(FusedAdamW(m.parameters(), lr=1e-2, weight_decay=0.05, bucket_bytes=8000),
+                                                m.named_parameters(), overlap=True)
+    ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.05)
+    for step in range(5):
+        if step == 3:
+            sd = {'model': m.state_dict(), 'opt': opt.state_dict()}
+            m = make()
+            for p in m.parameters():
+                p.data.zero_()
+            opt = kf.optimizers.SynchronousSGDOptimizer(FusedAdamW(m.parameters(), lr=1.0, bucket_bytes=8000),
+                                                        m.named_parameters(), overlap=True)
+            m.load_state_dict(sd['model'])
+            opt.load_state_dict(sd['opt'])
+        x, y = batch(step)
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.cross_entropy(m(x), y).backward()
+        opt.step()
+        ropt.zero_grad()
+        torch.nn.functional.cross_entropy(ref(x), y).backward()
+        ropt.step()
+    torch.cuda.synchronize()
+    assert opt._ov is not None and len(opt._ov['buckets']) > 1
+    for p, q in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, rtol=1e-4, atol=1e-5), (p - q).abs().max()
