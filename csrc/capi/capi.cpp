@@ -315,6 +315,38 @@ int kf_gen_strategy_graphs(const char *peers_csv, const char *strategy, char *ou
     return copy_out(text, out, cap);
 }
 
+static int plan_out(const StrategyList &sl, int rank, int32_t *out, int cap)
+{
+    DevicePlan p;
+    std::string err;
+    if (!compile_device_plan(sl, rank, &p, &err)) return fail(err);
+    const size_t need = 4 + p.round_begin.size() + 2 * p.edge_plan.size();
+    if ((size_t)cap < need) return fail("device plan does not fit the caller's buffer");
+    size_t k = 0;
+    out[k++] = p.n_plans;
+    out[k++] = p.n_rounds;
+    out[k++] = p.n_reduce_rounds;
+    out[k++] = (int32_t)p.edge_plan.size();
+    for (int32_t v : p.round_begin) out[k++] = v;
+    for (int32_t v : p.edge_plan) out[k++] = v;
+    for (int32_t v : p.edge_src) out[k++] = v;
+    return (int)k;
+}
+
+int kf_device_plan(kf_peer *p, int32_t *out, int cap)
+{
+    return plan_out(p->peer->session()->global_strategies(), p->peer->session()->rank(), out, cap);
+}
+
+int kf_device_plan_for(const char *peers_csv, const char *strategy, int rank, int32_t *out, int cap)
+{
+    PeerList peers;
+    Strategy s;
+    if (!parse_peer_list(peers_csv, &peers)) return fail("bad peer list");
+    if (!parse_strategy(strategy, &s)) return fail("unknown strategy");
+    return plan_out(gen_global_strategies(peers, s), rank, out, cap);
+}
+
 int kf_minimum_spanning_tree(const float *weights, int n, int32_t *edges_out)
 {
     std::vector<float> w(weights, weights + (size_t)n * n);

@@ -343,4 +343,83 @@ std::vector<int32_t> mst_to_forest(const std::vector<int32_t> &edges, int n)
     return father;
 }
 
+// ---- device plan -----------------------------------------------------------------------
+static bool graph_depths(const Graph &g, std::vector<int> *depth, std::string *err)
+{
+    const int n = g.size();
+    depth->assign(n, -1);
+    std::vector<int> state(n, 0);  // 0 new, 1 on the stack, 2 done
+    // iterative longest-path-from-a-source; a cycle is an error (self loops are not edges here)
+    for (int root = 0; root < n; ++root) {
+        if (state[root] == 2) continue;
+        std::vector<std::pair<int, size_t>> stack{{root, 0}};
+        state[root] = 1;
+        while (!stack.empty()) {
+            auto &[v, i]   = stack.back();
+            const auto &ps = g.prevs(v);
+            if (i < ps.size()) {
+                const int u = ps[i++];
+                if (state[u] == 1) {
+                    if (err) *err = "cycle in strategy graph";
+                    return false;
+                }
+                if (state[u] == 0) {
+                    state[u] = 1;
+                    stack.push_back({u, 0});
+                }
+            } else {
+                int d = 0;
+                for (int u : ps) d = std::max(d, (*depth)[u] + 1);
+                (*depth)[v] = d;
+                state[v]    = 2;
+                stack.pop_back();
+            }
+        }
+    }
+    return true;
+}
+
+bool compile_device_plan(const StrategyList &sl, int rank, DevicePlan *out, std::string *err)
+{
+    DevicePlan p;
+    p.n_plans = (int)sl.size();
+    if (sl.empty() || rank < 0 || rank >= sl[0].reduce.size()) {
+        if (err) *err = "compile_device_plan: bad rank or empty strategy list";
+        return false;
+    }
+    std::vector<std::vector<int>> rdepth(sl.size()), bdepth(sl.size());
+    int max_r = 0, max_b = 0;
+    for (size_t i = 0; i < sl.size(); ++i) {
+        if (!graph_depths(sl[i].reduce, &rdepth[i], err) || !graph_depths(sl[i].bcast, &bdepth[i], err)) return false;
+        for (int d : rdepth[i]) max_r = std::max(max_r, d);
+        for (int d : bdepth[i]) max_b = std::max(max_b, d);
+    }
+    p.n_reduce_rounds = max_r;
+    p.n_rounds        = max_r + max_b;
+    p.round_begin.push_back(0);
+    for (int rnd = 1; rnd <= max_r; ++rnd) {
+        for (size_t i = 0; i < sl.size(); ++i) {
+            // only nodes with a self loop combine what they receive (reduce graph semantics)
+            if (rdepth[i][rank] != rnd || !sl[i].reduce.is_self_loop(rank)) continue;
+            for (int src : sl[i].reduce.prevs(rank)) {
+                p.edge_plan.push_back((int32_t)i);
+                p.edge_src.push_back(src);
+            }
+        }
+        p.round_begin.push_back((int32_t)p.edge_plan.size());
+    }
+    for (int rnd = 1; rnd <= max_b; ++rnd) {
+        for (size_t i = 0; i < sl.size(); ++i) {
+            if (bdepth[i][rank] != rnd) continue;
+            for (int src : sl[i].bcast.prevs(rank)) {
+                p.edge_plan.push_back((int32_t)i);
+                p.edge_src.push_back(src);
+            }
+        }
+        p.round_begin.push_back((int32_t)p.edge_plan.size());
+    }
+    *out = p;
+    return true;
+}
+
 }  // namespace kf

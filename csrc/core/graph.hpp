@@ -72,6 +72,19 @@ StrategyList gen_cross_strategies(const PeerList &peers, Strategy s);
 StrategyList strategies_from_tree(const Graph &bcast);
 std::vector<uint8_t> digest_bytes(const StrategyList &sl);
 
+// One rank's view of a strategy list, compiled for the device executor (kfb_graph_allreduce in
+// include/kungfu_b200.h): the buffer is cut into one chunk per strategy; in round r the rank pulls
+// chunk edge_plan[e] from rank edge_src[e] for e in [round_begin[r], round_begin[r+1]), reducing
+// onto its own copy while r < n_reduce_rounds and overwriting it afterwards. A node's round is its
+// depth (longest path from a source) in the reduce graph, then in the broadcast graph, so every
+// source of an edge is final when the edge runs. (The host walks the same graphs edge by edge,
+// session.cpp:run_graphs; reference: srcs/go/kungfu/session/session.go:218-286.)
+struct DevicePlan {
+    int n_plans = 0, n_rounds = 0, n_reduce_rounds = 0;
+    std::vector<int32_t> round_begin, edge_plan, edge_src;
+};
+bool compile_device_plan(const StrategyList &sl, int rank, DevicePlan *out, std::string *err);
+
 // Prim on the symmetrised n x n weight matrix (row-major). Returns n-1 edges
 // (u, v) flattened; edges[2k] is already in the tree when edges[2k+1] joins.
 std::vector<int32_t> minimum_spanning_tree(const std::vector<float> &w, int n);

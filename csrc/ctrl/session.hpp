@@ -58,6 +58,7 @@ class Session
     Session(const PeerList &peers, const PeerID &self, Strategy strategy, Client *client, Server *server);
 
     int rank() const { return rank_; }
+    const StrategyList &global_strategies() const { return global_; }
     int size() const { return (int)peers_.size(); }
     int local_rank() const { return local_rank_; }
     int local_size() const { return local_size_; }

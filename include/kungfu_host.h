@@ -90,6 +90,12 @@ int kf_recv_fd(kf_peer *p, int src_rank, const char *tag, int *fd);
 
 /* planner utilities exposed for tests / tools */
 int kf_gen_strategy_graphs(const char *peers_csv, const char *strategy, char *out, int cap);
+/* This rank's view of the active strategies, compiled for the device executor (kfb_graph_allreduce):
+ * out = {n_plans, n_rounds, n_reduce_rounds, n_edges, round_begin[n_rounds + 1], edge_plan[n_edges],
+ * edge_src[n_edges]}; returns the number of ints written or -1. kf_device_plan_for compiles a named
+ * strategy over an explicit peer list (tests, tools). */
+int kf_device_plan(kf_peer *p, int32_t *out, int cap);
+int kf_device_plan_for(const char *peers_csv, const char *strategy, int rank, int32_t *out, int cap);
 int kf_minimum_spanning_tree(const float *weights, int n, int32_t *edges_out);
 void kf_transform2(const void *x, const void *y, void *z, int64_t n, int dtype, int op);
 int kf_cluster_resize(const char *cluster_json, int new_size, char *out, int cap);

@@ -89,6 +89,8 @@ def _declare(l):
     f('kf_set_tree', C.c_int, _VP, C.POINTER(C.c_int32), C.c_int)
     f('kf_set_strategy', C.c_int, _VP, C.c_char_p)
     f('kf_current_strategies', C.c_int, _VP, C.c_char_p, C.c_int)
+    f('kf_device_plan', C.c_int, _VP, C.POINTER(C.c_int32), C.c_int)
+    f('kf_device_plan_for', C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_int32), C.c_int)
     f('kf_current_strategy_name', C.c_int, _VP, C.c_char_p, C.c_int)
     f('kf_get_peer_latencies', C.c_int, _VP, C.POINTER(C.c_float), C.c_int)
     f('kf_egress_rates', C.c_int, _VP, C.POINTER(C.c_float), C.c_int)
@@ -125,6 +127,27 @@ def _adopt_torchrun_env():
     os.environ['KUNGFU_INIT_PEERS'] = peers
     os.environ.setdefault('KUNGFU_INIT_CLUSTER_VERSION', '0')
     os.environ.setdefault('KUNGFU_ALLREDUCE_STRATEGY', 'AUTO')
+
+
+def device_plan_table(v):
+    """Unpack {n_plans, n_rounds, n_reduce_rounds, n_edges, round_begin[], edge_plan[], edge_src[]}
+    (kf_device_plan, include/kungfu_host.h) into the table the device executor walks."""
+    n_plans, n_rounds, n_reduce, n_edges = v[:4]
+    begin = v[4:4 + n_rounds + 1]
+    plan = v[4 + n_rounds + 1:4 + n_rounds + 1 + n_edges]
+    src = v[4 + n_rounds + 1 + n_edges:4 + n_rounds + 1 + 2 * n_edges]
+    rounds = [[(plan[e], src[e]) for e in range(begin[r], begin[r + 1])] for r in range(n_rounds)]
+    return {'n_plans': n_plans, 'rounds': rounds, 'n_reduce': n_reduce, 'begin': list(begin), 'plan': list(plan),
+            'src': list(src)}
+
+
+def device_plan_for(peers_csv, strategy, rank):
+    """Compile a named strategy over an explicit peer list for `rank` (tests, tools)."""
+    buf = (C.c_int32 * 8192)()
+    n = lib().kf_device_plan_for(peers_csv.encode(), strategy.encode(), int(rank), buf, len(buf))
+    if n < 0:
+        raise KungFuHostError('device_plan_for: %s' % lib().kf_last_error().decode())
+    return device_plan_table(list(buf[:n]))
 
 
 class Exchange(object):
@@ -287,6 +310,14 @@ class Peer(object):
             out.append({'loops': set(int(a) for a in re.findall(r'\((\d+)\)', red)),
                         'reduce': edges(red), 'bcast': edges(bc)})
         return out
+
+    def device_plan(self):
+        """This rank's compiled edge table of the active strategies (see device_plan_table)."""
+        buf = (C.c_int32 * 8192)()
+        n = lib().kf_device_plan(self._h, buf, len(buf))
+        if n < 0:
+            raise KungFuHostError('device_plan: %s' % lib().kf_last_error().decode())
+        return device_plan_table(list(buf[:n]))
 
     def strategy_name(self):
         buf = C.create_string_buffer(64)

@@ -10,10 +10,10 @@ On one NVSwitch domain topology shaping buys no bandwidth, so the planner has
 two jobs here:
 
 * ``GraphExecutor``: API parity for -strategy / set_tree / monitored
-  all-reduce on CUDA tensors. A strategy's graphs are compiled into rounds
-  (nodes of equal depth); a round is a device barrier plus single-edge
-  pull kernels (csrc/kernels/collectives.cu:k_edge_reduce / k_edge_copy) on the
-  caller's stream. The buffer is cut into one chunk per active graph pair
+  all-reduce on CUDA tensors. The runtime compiles a strategy's graphs into
+  rounds (nodes of equal depth) of pull edges for this rank; one kernel walks
+  all rounds with peer barriers in between (csrc/kernels/collectives.cu:
+  k_graph_allreduce). The buffer is cut into one chunk per active graph pair
   (RING/CLIQUE/MULTI_* have several), like the reference's chunk hashing.
 * ``VariantChooser``: the B200 meaning of "adaptive strategy selection" -- it
   times the fused variants {one-shot, two-shot, NVLS} with CUDA events at a few
@@ -29,74 +29,21 @@ from ..ops import _cuda as K
 from ..ops import collective as coll
 
 
-def _depths(n, edges):
-    """depth[v] = longest path from any source to v along `edges`."""
-    prevs = {v: [] for v in range(n)}
-    for a, b in edges:
-        prevs[b].append(a)
-    depth = {}
-
-    def d(v, seen=()):
-        if v in depth:
-            return depth[v]
-        if v in seen:
-            raise ValueError('cycle in strategy graph')
-        depth[v] = 0 if not prevs[v] else 1 + max(d(u, seen + (v, )) for u in prevs[v])
-        return depth[v]
-
-    for v in range(n):
-        d(v)
-    return depth, prevs
-
-
 class GraphExecutor(object):
     """Runs the active (reduce, broadcast) graph pairs on the device.
 
-    The graphs are compiled once into this rank's edge table: for every round,
-    which chunk to pull from which rank (see kfb_graph_allreduce in
-    include/kungfu_b200.h). On a real communicator the whole walk is ONE kernel
-    launch; the same table can be walked from Python with one kernel per edge
-    (`launcher='python'`), which is what the host simulation in
-    tests/test_planner_cpu.py drives with threads and numpy."""
+    The graphs are compiled by the runtime (csrc/core/graph.cpp:compile_device_plan, `kf_device_plan`) into
+    this rank's edge table: for every round, which chunk to pull from which rank (see kfb_graph_allreduce
+    in include/kungfu_b200.h). On a real communicator the whole walk is ONE kernel launch; the same table
+    can be walked from Python with one kernel per edge (`launcher='python'`), which is what the host
+    simulation in tests/test_planner_cpu.py drives with threads and numpy."""
 
-    def __init__(self, comm, strategies=None, launcher=None):
+    def __init__(self, comm, table=None, launcher=None):
         self.comm = comm
-        self.strategies = strategies if strategies is not None else kfpy.peer().strategies()
+        self.table = table if table is not None else kfpy.peer().device_plan()
         self.stats = []  # (seconds, bytes) of monitored runs
-        self._plans = [self._compile(s) for s in self.strategies]
         self.launcher = launcher or ('device' if hasattr(comm, 'cstruct') and not getattr(comm, 'emulated', False)
                                      else 'python')
-        self.table = self._table()
-
-    def _compile(self, s):
-        n = self.comm.np
-        rank = self.comm.rank
-        rdepth, rprev = _depths(n, s['reduce'])
-        bdepth, bprev = _depths(n, s['bcast'])
-        rounds_r = max(rdepth.values()) if rdepth else 0
-        rounds_b = max(bdepth.values()) if bdepth else 0
-        return {
-            'reduce_rounds': rounds_r, 'bcast_rounds': rounds_b,
-            'my_rdepth': rdepth[rank], 'my_rprev': rprev[rank] if rank in s['loops'] else [],
-            'my_bdepth': bdepth[rank], 'my_bprev': bprev[rank],
-        }
-
-    def _table(self):
-        """This rank's edges per round: reduce rounds first, then broadcast rounds."""
-        max_r = max(p['reduce_rounds'] for p in self._plans)
-        max_b = max(p['bcast_rounds'] for p in self._plans)
-        rounds = []
-        for rnd in range(1, max_r + 1):
-            rounds.append([(i, src) for i, p in enumerate(self._plans) if p['my_rdepth'] == rnd for src in p['my_rprev']])
-        for rnd in range(1, max_b + 1):
-            rounds.append([(i, src) for i, p in enumerate(self._plans) if p['my_bdepth'] == rnd for src in p['my_bprev']])
-        begin, plan, src = [0], [], []
-        for edges in rounds:
-            for i, s_ in edges:
-                plan.append(i)
-                src.append(s_)
-            begin.append(len(plan))
-        return {'rounds': rounds, 'n_reduce': max_r, 'begin': begin, 'plan': plan, 'src': src}
 
     def all_reduce(self, buf, count, dtype, op='sum', byte_offset=0, monitored=False, stream=None):
         """In-place all-reduce of buf[byte_offset : +count] following the active graphs."""
@@ -105,7 +52,7 @@ class GraphExecutor(object):
             return
         code = dtype if isinstance(dtype, int) else K.dtype_code(dtype)
         es = coll._ESIZE[code]
-        k = len(self._plans)
+        k = self.table['n_plans']
         # chunk i -> strategy i (aligned to 16 bytes)
         per = ((count + k - 1) // k * es + 15) // 16 * 16 // es
         chunks = []
@@ -304,10 +251,10 @@ class DevicePlanner(object):
 
     def executor(self):
         """Graph executor for the strategies currently active in the runtime."""
-        strategies = kfpy.peer().strategies()
-        digest = repr(strategies)
+        table = kfpy.peer().device_plan()
+        digest = repr(table)
         if self._executor is None or digest != self._digest:
-            self._executor = GraphExecutor(self.comm, strategies)
+            self._executor = GraphExecutor(self.comm, table)
             self._digest = digest
         return self._executor
 

@@ -71,7 +71,8 @@ def _simulate(peers, strategy, count=1000):
 
     def run(rank):
         try:
-            ex = planner.GraphExecutor(_FakeComm(rank, np_, barrier), strategies)
+            # the edge table comes from the runtime's compiler, exactly what the device kernel is given
+            ex = planner.GraphExecutor(_FakeComm(rank, np_, barrier), H.device_plan_for(peers, strategy, rank))
             ex.all_reduce(buf, count, K.F32)
         except Exception as e:  # noqa: BLE001
             errors.append((rank, repr(e)))
