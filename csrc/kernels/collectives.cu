@@ -569,7 +569,7 @@ __global__ void __launch_bounds__(512)
 // The reference walks (reduce graph, broadcast graph) per chunk on the host,
 // receiving from `prevs` and sending to `nexts`
 // (/root/reference/srcs/go/kungfu/session/session.go:218-286). Here the graphs
-// are compiled (parallel/planner.py) into rounds of incoming edges per rank:
+// are compiled (csrc/core/graph.cpp:compile_device_plan) into rounds of incoming edges per rank:
 // in round r a rank pulls from the sources of its round-r edges, reducing onto
 // (reduce phase) or overwriting (broadcast phase) its own chunk; a peer
 // barrier separates rounds, because a source's chunk is final only once the

@@ -134,7 +134,8 @@ int kfb_edge_copy(void *dst, const void *src, int64_t bytes, int blocks,
  * and overwriting it afterwards; peer barriers separate the rounds. bufs[r]:
  * rank r's buffer as mapped here; chunk i covers chunk_bytes[i] bytes at
  * chunk_lo_bytes[i] (16-byte aligned). The tables are this rank's view,
- * compiled by parallel/planner.py from the strategy's graphs.
+ * compiled by the host runtime (kf_device_plan, include/kungfu_host.h) from the
+ * strategy's graphs.
  * (srcs/go/kungfu/session/session.go:218-313) */
 int kfb_graph_allreduce(const kfb_comm *comm, void *const *bufs, int dtype,
                         int op, int n_plans, const int64_t *chunk_lo_bytes,
