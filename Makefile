@@ -1,5 +1,5 @@
 # Convenience targets; the build itself is kungfu_b200/_build.py (no CMake, no Go).
-.PHONY: build test gpu-test sanitize docs clean
+.PHONY: build test gpu-test sanitize fuzz sass docs clean
 
 build:
 	python -m kungfu_b200._build
@@ -12,6 +12,12 @@ gpu-test: build
 
 sanitize: build
 	scripts/tsan-check.sh
+
+fuzz: build
+	python scripts/fuzz_cli.py -n 200
+
+sass: build
+	python scripts/dump_sass.py
 
 docs:
 	python scripts/gen-api-doc.py
