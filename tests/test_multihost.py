@@ -24,3 +24,41 @@ def test_three_hosts_on_loopback(strategy):
     outs = [p.communicate(timeout=120)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), '\n'.join(o[-1500:] for o in outs)
     assert sum(o.count('OK multihost') for o in outs) == 5
+
+
+FAKE_SSH = """#!/bin/sh
+# stands in for the system ssh: drops the options and the target, runs the command on this machine
+while [ "$1" = "-o" ]; do shift 2; done
+echo "fake-ssh target=$1" >&2
+shift
+exec sh -c "$*"
+"""
+
+
+def test_rrun_starts_one_runner_per_host_through_ssh(tmp_path):
+    """kungfu-rrun end to end (not -dry-run): the `ssh` it executes is a local
+    stand-in, so the per-host command line it builds (-H, -self, forwarded
+    flags, quoting of the program's arguments) is what starts the job.
+    Reference: /root/reference/srcs/go/cmd/kungfu-rrun/rrun.go."""
+    fake = tmp_path / 'ssh'
+    fake.write_text(FAKE_SSH)
+    fake.chmod(0o755)
+    bindir = os.path.join(ROOT, 'kungfu_b200', 'bin')
+    base = 33000 + (os.getpid() * 17) % 10000
+    env = dict(os.environ, PYTHONPATH=ROOT, PATH='%s:%s:%s' % (tmp_path, bindir, os.environ.get('PATH', '')))
+    cmd = [os.path.join(bindir, 'kungfu-rrun'), '-H', '127.0.0.1:2,127.0.0.2:1', '-u', 'nobody', '-q', '-np', '3', '-timeout', '90s',
+           '-port-range', '%d-%d' % (base, base + 16), '-port', str(base + 20), sys.executable, '-c',
+           "import kungfu_b200.torch as kf, torch; s = kf.ops.all_reduce_fn(torch.ones(3), 'sum'); "
+           "print('OK rrun %d/%d sum=%d it\\'s quoted' % (kf.current_rank(), kf.current_cluster_size(), int(s[0])))"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=150)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.count('fake-ssh target=nobody@127.0.0.') == 2, r.stdout[-3000:]
+    for rank in range(3):
+        assert "OK rrun %d/3 sum=3 it's quoted" % rank in r.stdout, r.stdout[-3000:]
+    # output is prefixed with the host it came from
+    assert '[127.0.0.1] ' in r.stdout and '[127.0.0.2] ' in r.stdout
+
+    # a failing host is reported and fails the whole call
+    r = subprocess.run([os.path.join(bindir, 'kungfu-distribute'), '-H', '127.0.0.1:1,127.0.0.2:1', 'sh', '-c', 'exit 3'],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=60)
+    assert r.returncode == 3 and r.stdout.count('exited with 3') == 2, r.stdout
