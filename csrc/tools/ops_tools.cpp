@@ -6,12 +6,16 @@
 //                                                 (starts the workers of `kungfu-run -w -np 0` runners)
 //   kungfu-config-client -server URL [-H ip:slots,...] [-port-range a-b] [-period 1s] [-ttl 10s]
 //                      [-reset | -clear | -example]           random-size cluster every period
+//                      [-shuffle] [-seed N]    -shuffle: a random SUBSET of the slots in random order (ranks move,
+//                                              hosts empty out, sometimes no worker survives), as the reference's
+//                                              client does; without it the first n slots
 //
 // Reference: /root/reference/tests/go/cmd/kungfu-test-util/kungfu-test-util.go:20-86,
 // kungfu-notify-start/kungfu-notify-start.go:25-70, kungfu-config-client-example/
 // kungfu-config-client-example.go:22-156.
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -157,9 +161,17 @@ int config_client(const Flags &f)
         return 2;
     }
     const int cap = hl.cap() > 0 ? hl.cap() : 1;
+    std::mt19937 rng(f.has("seed") ? (unsigned)atoi(f.get("seed", "0").c_str()) : (unsigned)getpid());
+    const bool shuffle = f.has("shuffle");
     auto make = [&](int n, Cluster *c) {
         c->runners = hl.gen_runner_list((uint16_t)atoi(f.get("port", "38080").c_str()));
-        return hl.gen_peer_list(n, pr, &c->workers, &err);
+        if (!shuffle) return hl.gen_peer_list(n, pr, &c->workers, &err);
+        PeerList all;
+        if (!hl.gen_peer_list(cap, pr, &all, &err)) return false;
+        std::shuffle(all.begin(), all.end(), rng);
+        all.resize((size_t)n);
+        c->workers = all;
+        return true;
     };
     if (f.has("example")) {
         Cluster c;
@@ -169,7 +181,6 @@ int config_client(const Flags &f)
     }
     const double period = parse_duration_seconds(f.get("period", "1s"), 1.0);
     const double ttl    = parse_duration_seconds(f.get("ttl", "0s"), 0.0);
-    std::mt19937 rng((unsigned)getpid());
     const auto t0 = std::chrono::steady_clock::now();
     for (int i = 0;; ++i) {
         Cluster c;
@@ -185,7 +196,7 @@ int config_client(const Flags &f)
 
 int main(int argc, char **argv)
 {
-    static const char *const bools[] = {"reset", "clear", "example", nullptr};
+    static const char *const bools[] = {"reset", "clear", "example", "shuffle", nullptr};
     const Flags f = parse(argc, argv, bools);
     if (strstr(argv[0], "notify-start")) return notify_start(f);
     if (strstr(argv[0], "config-client")) return config_client(f);

@@ -142,7 +142,8 @@ def build_host(force=False, verbose=True):
             continue
         exe = os.path.join(BIN_DIR, name)
         (obj,), ch = _compile_all(cxx, CXX_FLAGS + ['-I', os.path.join(ROOT, 'csrc')], [src], force)
-        if ch or changed or not os.path.exists(exe):
+        # several tools share one source: only the first of them sees it recompiled, so go by the object's age too
+        if ch or changed or not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(obj):
             _run([cxx, '-o', exe, obj] + objs + ['-pthread', '-ldl'])
             if verbose:
                 print('[kungfu_b200] linked', exe)

@@ -167,6 +167,31 @@ def test_random_resize_soak():
     assert 'now rank' in log or 'leaves at step' in log  # at least one membership change was observed
 
 
+def test_virtual_cluster_under_a_shuffling_config_client():
+    """Three loopback nodes x 2 slots, one kept-alive watch-mode runner per node, a stand-alone config server and a
+    client that PUTs random SUBSETS of the slots in random order (ranks move, nodes empty out and are refilled,
+    sometimes nobody survives): every worker checks every all-reduce, and after a final full cluster all six
+    slots finish. Reference: the docker-compose cluster tests (benchmarks/adaptation/gen-compose.py:60-123,
+    .github/workflows/cluster-test-1.sh, kungfu-config-client-example.go:96-116)."""
+    res = subprocess.run([sys.executable, os.path.join(ROOT, 'benchmarks', 'adaptation', 'virtual_cluster.py'), '--nodes', '3',
+                          '--cap', '2', '--np', '2', '--ttl', '6', '--period', '0.5', '--seed', str(os.getpid() % 1000),
+                          '--port-base', str(_base(9))], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=280)
+    assert res.returncode == 0, res.stdout[-4000:]
+    assert '6 of 6 workers finished' in res.stdout and 'runners exited with [0, 0, 0]' in res.stdout, res.stdout[-2000:]
+
+
+def test_config_client_shuffle_is_a_random_subset_in_random_order():
+    seen = set()
+    for seed in range(8):
+        r = subprocess.run([os.path.join(BIN, 'kungfu-config-client'), '-H', '127.0.0.1:2,127.0.0.2:2', '-port-range', '100-110',
+                            '-shuffle', '-seed', str(seed), '-example'], stdout=subprocess.PIPE, text=True, timeout=10)
+        c = json.loads(r.stdout)
+        assert sorted(c['Workers']) == ['127.0.0.1:100', '127.0.0.1:101', '127.0.0.2:100', '127.0.0.2:101']
+        assert c['Runners'] == ['127.0.0.1:38080', '127.0.0.2:38080']
+        seen.add(tuple(c['Workers']))
+    assert len(seen) > 2  # orders differ between seeds
+
+
 def test_elastic_hook_follows_config_server(tmp_path):
     """ElasticHook (reference: tensorflow/experimental/hook/elastic.py) under kungfu-run -w with a built-in config
     server: an operator PUTs 3 workers, then 1; the hook grows, shrinks (detached workers stop) and finishes."""
