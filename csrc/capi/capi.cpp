@@ -1,6 +1,11 @@
 // extern "C" surface of the host runtime (see include/kungfu_host.h).
+#include <chrono>
+#include <condition_variable>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/kungfu_host.h"
 #include "core/base.hpp"
@@ -283,6 +288,85 @@ int kf_egress_rates(kf_peer *p, float *out, int n)
     auto v = p->peer->egress_rates();
     for (int i = 0; i < n && i < (int)v.size(); ++i) out[i] = v[i];
     return 0;
+}
+
+int64_t kf_request_async(kf_peer *p, int target_rank, const char *version, const char *name, void *buf, int64_t nbytes)
+{
+    if (!p || !name || !buf || nbytes < 0) return fail("kf_request_async: bad argument");
+    Peer *peer = p->peer.get();
+    const std::string v = version ? version : "", n = name;
+    return peer->submit([peer, target_rank, v, n, buf, nbytes] { return peer->request(target_rank, v, n, buf, (size_t)nbytes); });
+}
+
+struct kf_prefetch_state {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<uint8_t> model, incoming;
+    bool have = false, requesting = false;
+    int64_t fresh = 0;
+};
+
+struct kf_prefetch {
+    kf_peer *peer;
+    std::string name;
+    std::shared_ptr<kf_prefetch_state> st;
+};
+
+kf_prefetch *kf_prefetch_new(kf_peer *p, const char *name, int64_t nbytes)
+{
+    if (!p || !name || nbytes <= 0) {
+        fail("kf_prefetch_new: bad argument");
+        return nullptr;
+    }
+    auto *pf = new kf_prefetch{p, name, std::make_shared<kf_prefetch_state>()};
+    pf->st->model.resize((size_t)nbytes);
+    pf->st->incoming.resize((size_t)nbytes);
+    return pf;
+}
+
+int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh)
+{
+    if (!pf || !out) return fail("kf_prefetch_next: null argument");
+    auto st    = pf->st;
+    Peer *peer = pf->peer->peer.get();
+    const size_t n = st->model.size();
+    if (!st->have) {
+        if (!peer->request(target_rank, "", pf->name, st->model.data(), n)) return done(pf->peer, false);
+        st->have = true;
+    }
+    bool start = false;
+    {
+        std::lock_guard<std::mutex> lk(st->mu);
+        if (!st->requesting) st->requesting = start = true;
+    }
+    if (start) {
+        const std::string name = pf->name;
+        // the job owns a reference to the buffers: kf_prefetch_free may run before it does
+        peer->submit_detached([peer, st, name, target_rank, n] {
+            const bool ok = peer->request(target_rank, "", name, st->incoming.data(), n);
+            std::lock_guard<std::mutex> lk(st->mu);
+            if (ok) {
+                st->model.swap(st->incoming);
+                ++st->fresh;
+            }
+            st->requesting = false;
+            st->cv.notify_all();
+        });
+    }
+    std::lock_guard<std::mutex> lk(st->mu);
+    memcpy(out, st->model.data(), n);
+    if (fresh) *fresh = st->fresh;
+    return 0;
+}
+
+void kf_prefetch_free(kf_prefetch *pf)
+{
+    if (!pf) return;
+    {
+        std::unique_lock<std::mutex> lk(pf->st->mu);
+        pf->st->cv.wait_for(lk, std::chrono::seconds(30), [&] { return !pf->st->requesting; });
+    }
+    delete pf;
 }
 
 int kf_send_fd(kf_peer *p, int target_rank, const char *tag, int fd)

@@ -260,6 +260,7 @@ std::string HostList::str() const
 bool parse_host_list(const std::string &s, HostList *out)
 {
     out->clear();
+    if (s.empty()) return true;  // no hosts: valid and empty, like the peer list
     for (auto &part : split(s, ',')) {
         HostSpec h;
         if (!parse_host_spec(part, &h)) return false;

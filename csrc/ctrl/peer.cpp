@@ -86,13 +86,20 @@ Peer::~Peer() { close(); }
 
 void Peer::set_error(const std::string &e)
 {
-    last_error_ = e;
+    {
+        std::lock_guard<std::mutex> lk(err_mu_);
+        last_error_ = e;
+    }
     KF_ERROR("%s", e.c_str());
 }
 
 std::string Peer::last_error()
 {
-    std::string e = last_error_;
+    std::string e;
+    {
+        std::lock_guard<std::mutex> lk(err_mu_);
+        e = last_error_;
+    }
     if (session_) {
         const std::string s = session_->last_error();
         if (!s.empty()) e += (e.empty() ? "" : "; ") + s;
@@ -368,7 +375,8 @@ bool Peer::request(int target_rank, const std::string &version, const std::strin
     }
     std::string err;
     if (!client_->request(s->peers()[target_rank], version, name, buf, n, &err)) {
-        last_error_ = err;
+        std::lock_guard<std::mutex> lk(err_mu_);
+        last_error_ = err;  // a missing blob is an expected outcome: recorded, not logged
         return false;
     }
     return true;

@@ -65,6 +65,7 @@ class Peer
     int version_   = 0;
     bool detached_ = false;
     bool started_  = false;
+    std::mutex err_mu_;  // async ops fail on worker threads
     std::string last_error_;
 
     // async ops

@@ -12,8 +12,10 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <cctype>
 #include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <fstream>
@@ -344,6 +346,64 @@ void GpuPool::put(int id)
     if (id >= 0 && id < (int)used_.size()) used_[id] = false;
 }
 
+// The runner's own CUDA_VISIBLE_DEVICES narrows and orders the GPUs its workers may use: slot k
+// of the pool is the k-th entry of that list. A list of integers gives the device number (negative
+// entries are skipped, a repeated one makes the list invalid); any other form (GPU-<uuid>, MIG-...)
+// is handed on token by token and the slot stays the index into it.
+int map_cuda_index(int slot, const char *visible, std::string *token)
+{
+    if (token) token->clear();
+    if (slot < 0) return -1;
+    if (visible == nullptr) {
+        if (token) *token = std::to_string(slot);
+        return slot;
+    }
+    std::vector<std::string> toks;
+    {
+        std::string cur;
+        for (const char *c = visible;; ++c) {
+            if (*c == ',' || *c == 0) {
+                size_t b = cur.find_first_not_of(" \t"), e = cur.find_last_not_of(" \t");
+                if (b != std::string::npos) toks.push_back(cur.substr(b, e - b + 1));
+                cur.clear();
+                if (*c == 0) break;
+            } else {
+                cur += *c;
+            }
+        }
+    }
+    bool numeric = true;
+    for (auto &t : toks) {
+        size_t i = (t[0] == '-' || t[0] == '+') ? 1 : 0;
+        if (i >= t.size() || t.size() > 9) numeric = false;
+        for (; i < t.size(); ++i) numeric = numeric && isdigit((unsigned char)t[i]);
+    }
+    if (!numeric) {
+        if (slot >= (int)toks.size()) {
+            KF_WARN("CUDA_VISIBLE_DEVICES=%s has no entry for local slot %d", visible, slot);
+            return -1;
+        }
+        if (token) *token = toks[slot];
+        return slot;
+    }
+    std::vector<int> ids;
+    for (auto &t : toks) {
+        const int n = atoi(t.c_str());
+        if (n < 0) continue;
+        if (std::find(ids.begin(), ids.end(), n) != ids.end()) {
+            KF_WARN("invalid CUDA_VISIBLE_DEVICES=%s: device %d is listed twice", visible, n);
+            return -1;
+        }
+        ids.push_back(n);
+    }
+    if (slot >= (int)ids.size()) {
+        KF_WARN("CUDA_VISIBLE_DEVICES=%s has no entry for local slot %d", visible, slot);
+        return -1;
+    }
+    if (token) *token = std::to_string(ids[slot]);
+    return ids[slot];
+}
+
 ProcSpec make_worker_proc(const RunFlags &f, const PeerID &self, const PeerID &parent, const Cluster &cluster,
                           int version, int gpu_id)
 {
@@ -366,12 +426,16 @@ ProcSpec make_worker_proc(const RunFlags &f, const PeerID &self, const PeerID &p
     e[env::kAllowNvlink] = f.allow_nvlink ? "true" : "false";
     e[env::kJobStart]    = std::to_string(f.t0);
     e[env::kProcStart]   = std::to_string((long)time(nullptr));
-    e[env::kCudaVisible] = std::to_string(gpu_id);
+    // slot of the GPU pool -> device, through the runner's own CUDA_VISIBLE_DEVICES
+    // (/root/reference/srcs/go/kungfu/job/cuda_visible_device.go:17-58, job.go:47-53)
+    std::string token;
+    const int cuda_idx   = map_cuda_index(gpu_id, getenv("CUDA_VISIBLE_DEVICES"), &token);
+    e[env::kCudaVisible] = std::to_string(cuda_idx);
     // Without -allow-nvlink each worker only sees its own GPU (the reference's
     // default). Peer-memory collectives need every GPU of the node mapped, so
     // GPU jobs should pass -allow-nvlink; the worker then selects its device
-    // from KUNGFU_CUDA_VISIBLE_DEVICES.
-    if (!f.allow_nvlink && gpu_id >= 0) e["CUDA_VISIBLE_DEVICES"] = std::to_string(gpu_id);
+    // from KUNGFU_CUDA_VISIBLE_DEVICES (looked up in the inherited CUDA_VISIBLE_DEVICES).
+    if (!f.allow_nvlink && cuda_idx >= 0) e["CUDA_VISIBLE_DEVICES"] = token;
     e["PYTHONUNBUFFERED"] = "1";
     return p;
 }

@@ -92,6 +92,11 @@ class GpuPool
     int cap() const { return (int)used_.size(); }
 };
 
+// Device for pool slot `slot` given the runner's CUDA_VISIBLE_DEVICES (`visible`, nullptr if unset):
+// the value of KUNGFU_CUDA_VISIBLE_DEVICES, -1 if there is none; *token = what CUDA_VISIBLE_DEVICES of
+// the worker is narrowed to. /root/reference/srcs/go/kungfu/job/cuda_visible_device.go:17-58
+int map_cuda_index(int slot, const char *visible, std::string *token);
+
 struct ProcSpec {
     std::string name;  // shown as the log prefix
     std::string prog;

@@ -63,6 +63,20 @@ int kf_submit(kf_peer *p, int (*fn)(void *), void *arg, void (*on_done)(void *, 
 int kf_save(kf_peer *p, const char *version, const char *name, const void *data, int64_t nbytes);
 int kf_request(kf_peer *p, int target_rank, const char *version, const char *name, void *buf, int64_t nbytes);
 
+/* async request: a handle for kf_wait_handle (0 iff the blob was found with that size) */
+int64_t kf_request_async(kf_peer *p, int target_rank, const char *version, const char *name, void *buf, int64_t nbytes);
+
+/* Double-buffered pull of a peer's fused model (the reference's ModelBuffer + AsyncModelAveraging /
+ * AsyncRequestModel, srcs/cpp/src/tensorflow/ops/cpu/peer_to_peer.cpp:156-258,411-524): the first
+ * kf_prefetch_next blocks on the request; every call then starts the request for the NEXT call on the
+ * runtime's workers (unless one is still in flight) and hands out the newest complete model, so the
+ * training loop never waits on the network. *fresh (may be NULL) = number of completed prefetches so far.
+ * kf_prefetch_free waits for the request in flight. */
+typedef struct kf_prefetch kf_prefetch;
+kf_prefetch *kf_prefetch_new(kf_peer *p, const char *name, int64_t nbytes);
+int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh);
+void kf_prefetch_free(kf_prefetch *pf);
+
 /* elastic control */
 int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached);
 int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached);

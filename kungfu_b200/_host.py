@@ -82,6 +82,10 @@ def _declare(l):
     f('kf_wait_handle', C.c_int, _VP, C.c_int64)
     f('kf_save', C.c_int, _VP, C.c_char_p, C.c_char_p, _VP, C.c_int64)
     f('kf_request', C.c_int, _VP, C.c_int, C.c_char_p, C.c_char_p, _VP, C.c_int64)
+    f('kf_request_async', C.c_int64, _VP, C.c_int, C.c_char_p, C.c_char_p, _VP, C.c_int64)
+    f('kf_prefetch_new', _VP, _VP, C.c_char_p, C.c_int64)
+    f('kf_prefetch_next', C.c_int, _VP, C.c_int, _VP, C.POINTER(C.c_int64))
+    f('kf_prefetch_free', None, _VP)
     f('kf_resize_cluster', C.c_int, _VP, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int))
     f('kf_resize_cluster_from_url', C.c_int, _VP, C.POINTER(C.c_int), C.POINTER(C.c_int))
     f('kf_peek_cluster_change', C.c_int, _VP, C.POINTER(C.c_int))
@@ -345,3 +349,33 @@ class Peer(object):
         v = version.encode() if version is not None else None
         rc = lib().kf_request(self._h, target, v, name.encode(), buf_ptr, nbytes)
         return rc == 0
+
+    def request_async(self, target, name, buf_ptr, nbytes, version=None):
+        """Start a request on the runtime's workers; `wait_handle(h)` is True iff the blob arrived.
+        The caller keeps the buffer alive until then."""
+        v = version.encode() if version is not None else None
+        h = lib().kf_request_async(self._h, target, v, name.encode(), buf_ptr, nbytes)
+        if h < 0:
+            raise KungFuHostError('request_async failed: %s' % lib().kf_last_error().decode())
+        return h
+
+    def wait(self, handle):
+        """Block until an async op finishes; True iff it succeeded."""
+        return lib().kf_wait_handle(self._h, handle) == 0
+
+    def prefetch_new(self, name, nbytes):
+        pf = lib().kf_prefetch_new(self._h, name.encode(), nbytes)
+        if not pf:
+            raise KungFuHostError('prefetch_new failed: %s' % lib().kf_last_error().decode())
+        return pf
+
+    @staticmethod
+    def prefetch_next(pf, target, buf_ptr):
+        """(ok, completed background pulls so far); see kf_prefetch_next in include/kungfu_host.h."""
+        fresh = C.c_int64(0)
+        rc = lib().kf_prefetch_next(pf, target, buf_ptr, C.byref(fresh))
+        return rc == 0, int(fresh.value)
+
+    @staticmethod
+    def prefetch_free(pf):
+        lib().kf_prefetch_free(pf)

@@ -206,22 +206,39 @@ def egress_rates():
     return rates
 
 
-def _get_cuda_index():
-    """GPU this worker should use: KUNGFU_CUDA_VISIBLE_DEVICES if the launcher
-    pinned one, else the local rank
-    (/root/reference/srcs/cpp/src/python/cuda.cpp:29-47)."""
-    v = os.environ.get('KUNGFU_CUDA_VISIBLE_DEVICES')
-    if v not in (None, ''):
-        first = int(v.split(',')[0])
+def _cuda_index_from_env(kf_visible, visible, local_rank_env, local_rank):
+    """Pure function behind get_cuda_index() (testable without touching os.environ)."""
+    if kf_visible not in (None, ''):
+        first = int(kf_visible.split(',')[0])
         if first < 0:
             return -1
-        visible = os.environ.get('CUDA_VISIBLE_DEVICES')
-        if visible:  # launcher already narrowed the visible set to one device
-            return 0 if len(visible.split(',')) == 1 else first
+        if visible:
+            toks = [t.strip() for t in visible.split(',') if t.strip()]
+            try:
+                ids = [i for i in (int(t) for t in toks) if i >= 0]
+            except ValueError:
+                ids = None  # GPU-<uuid> / MIG-... entries: the launcher passes the slot
+            if ids is not None and first in ids:
+                return ids.index(first)  # the launcher names the device; the runtime counts within the visible list
+            if len(toks) == 1:
+                return 0  # already narrowed to one device
+            return first if first < len(toks) else -1
         return first
-    if 'LOCAL_RANK' in os.environ:
-        return int(os.environ['LOCAL_RANK'])
-    return current_local_rank()
+    if local_rank_env not in (None, ''):
+        return int(local_rank_env)
+    return local_rank()
+
+
+def _get_cuda_index():
+    """GPU (index for torch.cuda.set_device) this worker should use. The launcher
+    names a device in KUNGFU_CUDA_VISIBLE_DEVICES; it is looked up in
+    CUDA_VISIBLE_DEVICES, which the launcher narrows to that one device unless
+    -allow-nvlink keeps the whole node visible
+    (/root/reference/srcs/cpp/src/python/cuda.cpp:29-47,
+    /root/reference/srcs/go/kungfu/job/cuda_visible_device.go:17-58). Without a
+    KungFu launcher: LOCAL_RANK, else the local rank."""
+    return _cuda_index_from_env(os.environ.get('KUNGFU_CUDA_VISIBLE_DEVICES'), os.environ.get('CUDA_VISIBLE_DEVICES'),
+                                os.environ.get('LOCAL_RANK'), current_local_rank)
 
 
 def _get_other_ranks():

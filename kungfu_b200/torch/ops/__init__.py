@@ -7,6 +7,8 @@ from .collective import (all_gather, all_reduce_fn, barrier, broadcast,  # noqa:
                          wait_all_handles, wait_handle)
 from .local import request_model, request_variable_with_template, save_model, save_variables  # noqa: F401
 from .monitor import egress_rates, global_noise_scale  # noqa: F401
+from .p2p import (AsyncModelAveraging, AsyncRequestModel, ModelAveraging, PeerSelector, RequestModel,  # noqa: F401
+                  async_model_averaging, async_request_model, model_averaging)
 from .state import counter, exponential_moving_average  # noqa: F401
 from .topology import (cluster_size, get_neighbour_mask, get_peer_latencies, get_random_peer,  # noqa: F401
                        global_minimum_spanning_tree, minimum_spanning_tree, mst_to_tree,

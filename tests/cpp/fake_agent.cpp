@@ -86,6 +86,32 @@ int main()
         CHECK(peer.Request(target, "m!", other, sizeof(other)) != 0);
         CHECK(peer.Barrier() == 0);
     }
+    // double-buffered model pull (kf_prefetch_*) and the async request handle: the pull for the next
+    // call runs on the runtime's workers while this thread keeps publishing new models
+    {
+        const int target = (rank + 1) % np;
+        std::vector<float> m(4096, (float)rank);
+        CHECK(peer.Save("pf", m.data(), m.size() * 4) == 0);
+        CHECK(peer.Barrier() == 0);
+        kf_prefetch *pf = kf_prefetch_new(peer.raw(), "pf", (int64_t)m.size() * 4);
+        CHECK(pf != nullptr);
+        std::vector<float> got(m.size(), -1.f);
+        int64_t fresh = 0;
+        for (int it = 0; it < 40; ++it) {
+            std::fill(m.begin(), m.end(), (float)(rank + 1000 * (it + 1)));
+            CHECK(peer.Save("pf", m.data(), m.size() * 4) == 0);  // overwrite while peers pull
+            CHECK(kf_prefetch_next(pf, target, got.data(), &fresh) == 0);
+            CHECK(got.front() == got.back());  // one snapshot, never a mixture of two
+            CHECK(((int)got.front() - target) % 1000 == 0);
+        }
+        kf_prefetch_free(pf);  // waits for the pull in flight
+        std::vector<float> a(m.size(), -1.f);
+        const int64_t h = kf_request_async(peer.raw(), target, nullptr, "pf", a.data(), (int64_t)a.size() * 4);
+        CHECK(h > 0 && kf_wait_handle(peer.raw(), h) == 0 && a.front() == a.back());
+        const int64_t h2 = kf_request_async(peer.raw(), target, nullptr, "pf", a.data(), 8);  // wrong size
+        CHECK(h2 > 0 && kf_wait_handle(peer.raw(), h2) != 0);
+        CHECK(peer.Barrier() == 0);
+    }
     // latencies + set_tree
     {
         std::vector<float> lat(np);

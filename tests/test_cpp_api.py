@@ -69,3 +69,55 @@ def test_fake_adaptive_trainer(tmp_path):
     assert res.returncode == 0, res.stdout[-3000:]
     assert 'resized 1 -> 3' in res.stdout and 'resized 3 -> 4' in res.stdout and 'resized 4 -> 2' in res.stdout
     assert res.stdout.count('OK fake-adaptive-trainer') == 2 and res.stdout.count('detached at step') == 2
+
+
+def test_runtime_internals(tmp_path):
+    """tests/cpp/runtime_unit_test.cpp: the subjects of the reference's Go unit tests (host / peer lists, cluster
+    resize, hostfile, forest arrays, runner flags, CUDA_VISIBLE_DEVICES remap, versioned store window, message
+    framing incl. hostile headers, mailbox rendezvous, rate accumulators) against the runtime's own classes."""
+    out = str(tmp_path / 'runtime-unit')
+    lib = os.path.join(ROOT, 'kungfu_b200', 'lib')
+    subprocess.check_call(['g++', '-O1', '-std=c++17', '-pthread', '-I', os.path.join(ROOT, 'include'), '-I',
+                           os.path.join(ROOT, 'csrc'), os.path.join(ROOT, 'tests', 'cpp', 'runtime_unit_test.cpp'), '-o', out,
+                           '-L', lib, '-lkungfu_host', '-Wl,-rpath,' + lib])
+    res = subprocess.run([out], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert res.returncode == 0 and 'OK runtime-unit' in res.stdout, res.stdout[-3000:]
+
+
+def test_worker_environment_through_the_runner():
+    """What a worker really sees: the runner's CUDA_VISIBLE_DEVICES picks and orders the devices
+    (reference: kungfu/job/cuda_visible_device.go), values containing '=' survive the environment merge
+    (reference: proc/proc_test.go), and the worker-side lookup turns the device into an index."""
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
+    base = 21000 + (os.getpid() * 67) % 11000
+    script = 'echo "W $KUNGFU_SELF_SPEC kf=$KUNGFU_CUDA_VISIBLE_DEVICES cuda=$CUDA_VISIBLE_DEVICES y=$Y"'
+
+    def run(extra, env_cuda):
+        env = dict(os.environ, Y='Z=2')
+        env.pop('CUDA_VISIBLE_DEVICES', None)
+        if env_cuda is not None:
+            env['CUDA_VISIBLE_DEVICES'] = env_cuda
+        r = subprocess.run([exe, '-q', '-np', '2', '-port-range', '%d-%d' % (base, base + 8), '-port', str(base + 40)] + extra +
+                           ['sh', '-c', script], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=60)
+        assert r.returncode == 0, r.stdout
+        return sorted(l[l.index('W '):] for l in r.stdout.splitlines() if 'W 127.0.0.1:' in l)
+
+    a, b = run([], '4,6')
+    assert a.endswith(':%d kf=4 cuda=4 y=Z=2' % base) and b.endswith(':%d kf=6 cuda=6 y=Z=2' % (base + 1))
+    a, b = run(['-allow-nvlink'], '4,6')  # the node stays visible; the worker looks its device up in the list
+    assert a.endswith('kf=4 cuda=4,6 y=Z=2') and b.endswith('kf=6 cuda=4,6 y=Z=2')
+    a, b = run([], None)                  # nothing set: slot == device
+    assert a.endswith('kf=0 cuda=0 y=Z=2') and b.endswith('kf=1 cuda=1 y=Z=2')
+    a, b = run([], 'GPU-aa,GPU-bb')       # uuid form is handed on by position
+    assert a.endswith('kf=0 cuda=GPU-aa y=Z=2') and b.endswith('kf=1 cuda=GPU-bb y=Z=2')
+
+    from kungfu_b200.python import _cuda_index_from_env as idx
+    never = lambda: 1 / 0  # noqa: E731
+    assert idx('6', '4,6', None, never) == 1        # -allow-nvlink: device 6 is the second visible one
+    assert idx('6', '6', None, never) == 0          # narrowed to one device
+    assert idx('1', None, None, never) == 1         # nothing hidden
+    assert idx('-1', '4,6', None, never) == -1      # the launcher had no GPU for this worker
+    assert idx('1', 'GPU-aa,GPU-bb', None, never) == 1 and idx('1', 'GPU-bb', None, never) == 0
+    assert idx('1', '0,1,2,3', '3', never) == 1     # a KungFu launcher wins over LOCAL_RANK
+    assert idx(None, '0,1', '3', never) == 3        # torchrun: LOCAL_RANK
+    assert idx(None, None, None, lambda: 2) == 2    # bare process: the local rank

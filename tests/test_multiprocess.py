@@ -204,3 +204,10 @@ def test_modelarts_environment_describes_the_cluster():
     r = subprocess.run([sys.executable, '-c', code], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env,
                        timeout=60)
     assert r.returncode != 0 and 'BATCH_CUSTOM1_HOSTS' in r.stdout, r.stdout
+
+
+@pytest.mark.parametrize('np_', [1, 2, 4])
+def test_p2p_model_ops(np_):
+    """Selectors, ModelAveraging / RequestModel and their prefetching variants (native double buffer)."""
+    res = run_workers(np_, os.path.join(ROOT, 'tests', 'workers', 'p2p_model_worker.py'), timeout=90)
+    assert res.returncode == 0 and res.stdout.count('OK p2p-model') == np_, res.stdout[-3000:]
