@@ -16,6 +16,10 @@ for _name in ('python', 'torch', 'torch.ops', 'torch.optimizers', 'cmd', 'info',
         globals()[_name] = _mod
 
 
+_utils = importlib.import_module('kungfu_b200._utils')  # measure, map_maybe, show_duration, _log_event, ...
+sys.modules['kungfu._utils'] = _utils
+
+
 # ``kungfu.tensorflow.*``: the reference's main front end was TensorFlow 1.x. Its module layout and names are
 # kept so that ported code finds everything in the same place; the objects are the PyTorch ones (there is no
 # TensorFlow in a B200 stack built on torch): optimizers wrap torch optimizers, ops take torch tensors.

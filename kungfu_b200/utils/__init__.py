@@ -142,6 +142,32 @@ def show_duration(seconds):
     return '%dh%dm%ds' % (mm // 60, mm % 60, ss)
 
 
+def since_job_start():
+    """Seconds since kungfu-run started the job (KUNGFU_JOB_START_TIMESTAMP; reference: kungfu/_utils.py:33-36)."""
+    import os
+    import time
+    return time.time() - int(os.getenv('KUNGFU_JOB_START_TIMESTAMP') or '0')
+
+
+def since_proc_start():
+    """Seconds since the runner spawned this worker (KUNGFU_PROC_START_TIMESTAMP; reference: kungfu/_utils.py:39-42)."""
+    import os
+    import time
+    return time.time() - int(os.getenv('KUNGFU_PROC_START_TIMESTAMP') or '0')
+
+
+def log_event(name):
+    """One 'TS=<unix time> <name> :: <duration> since proc started' line, the format the scaling benchmark's
+    log scraper expects (reference: kungfu/_utils.py:44-50)."""
+    import time
+    line = 'TS=%f %s :: %s since proc started' % (time.time(), name, show_duration(since_proc_start()))
+    print(line, flush=True)
+    return line
+
+
+_since_job_start, _since_proc_start, _log_event = since_job_start, since_proc_start, log_event
+
+
 class EMA(ExponentialMovingAverage):
     """Moving average whose input is clamped to [value / scale_cap, value * scale_cap] first: one wild
     reading (a noise-scale spike) cannot move the average by more than that factor
