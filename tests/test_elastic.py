@@ -101,3 +101,19 @@ def test_regrow_onto_a_used_address_restarts_the_control_exchange():
                       extra_flags=['-w', '-builtin-config-port', str(_free_port())])
     assert res.returncode == 0, res.stdout[-4000:]
     assert 'OK regrow worker rank 0 done at step 7' in res.stdout
+
+
+def test_resizes_leave_no_descriptors_threads_or_memory_behind():
+    """Seven grow / shrink cycles 1 -> 3 -> 1: the survivor's open descriptors and threads at size 1 are the same
+    after the last cycle as after the second one, and its resident memory does not creep."""
+    import re
+    cycles = 7
+    schedule = ','.join(['1:1', '3:1'] * cycles + ['1:1'])
+    res = run_workers(1, os.path.join(W, 'leak_worker.py'), args=[schedule, str(2 * cycles + 1)], timeout=240,
+                      extra_flags=['-w', '-builtin-config-port', str(_free_port())])
+    assert res.returncode == 0 and 'OK leak worker done' in res.stdout, res.stdout[-4000:]
+    rows = [tuple(map(int, m.groups())) for m in re.finditer(r'LEAK step (\d+) fds (\d+) threads (\d+) rss_mib (\d+)', res.stdout)]
+    assert len(rows) == cycles + 1, rows
+    (_, fds2, thr2, rss2), (_, fds_n, thr_n, rss_n) = rows[2], rows[-1]
+    assert fds_n <= fds2 and thr_n <= thr2, rows
+    assert rss_n - rss2 <= 16, rows
