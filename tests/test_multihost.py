@@ -26,6 +26,25 @@ def test_three_hosts_on_loopback(strategy):
     assert sum(o.count('OK multihost') for o in outs) == 5
 
 
+@pytest.mark.parametrize('strategy', ['MULTI_BINARY_TREE_STAR', 'AUTO'])
+def test_sixteen_workers_on_four_hosts(strategy):
+    """The reference's virtual cluster shape (4 nodes x 4 slots): every op of the multi-host worker at np = 16."""
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
+    base = 22000 + (os.getpid() * 43) % 10000
+    ips = ['127.0.0.%d' % (i + 1) for i in range(4)]
+    hosts = ','.join(ip + ':4' for ip in ips)
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    procs = []
+    for ip in ips:
+        cmd = [exe, '-q', '-np', '16', '-H', hosts, '-self', ip, '-strategy', strategy, '-timeout', '150s', '-port-range',
+               '%d-%d' % (base, base + 16), '-port', str(base + 20), sys.executable,
+               os.path.join(ROOT, 'tests', 'workers', 'multihost_worker.py')]
+        procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
+    outs = [p.communicate(timeout=200)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), '\n'.join(o[-1500:] for o in outs)
+    assert sum(o.count('OK multihost') for o in outs) == 16
+
+
 FAKE_SSH = """#!/bin/sh
 # stands in for the system ssh: drops the options and the target, runs the command on this machine
 while [ "$1" = "-o" ]; do shift 2; done

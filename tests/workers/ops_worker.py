@@ -18,14 +18,15 @@ def check_all_reduce():
         x = (torch.arange(20) % 3 + 1).to(dt) if dt == torch.uint8 else (torch.arange(20) + rank).to(dt)
         y = kf.ops.all_reduce_fn(x, 'sum')
         exp = (torch.arange(20) % 3 + 1).double() * np_ if dt == torch.uint8 else sum((torch.arange(20) + r).double() for r in range(np_))
-        assert torch.allclose(y.double(), exp, rtol=1e-2), (dt, y, exp)
+        # 16-bit sums are rounded at every hop of the graph walk: the bound grows with the length of the chain
+        assert torch.allclose(y.double(), exp, rtol=1e-2 * max(1, np_ / 4)), (dt, y, exp)
     x = torch.tensor([float(rank + 1)] * 5)
     assert kf.ops.all_reduce_fn(x, 'max')[0] == np_
     assert kf.ops.all_reduce_fn(x, 'min')[0] == 1
     prod = 1.0
     for r in range(np_):
         prod *= r + 1
-    assert kf.ops.all_reduce_fn(x, 'prod')[0] == prod
+    assert abs(float(kf.ops.all_reduce_fn(x, 'prod')[0]) - prod) <= 1e-6 * prod  # np! leaves fp32's exact range at np = 14
     # larger than the 1 MiB chunk: exercises chunking + strategy hashing
     big = torch.full((700000, ), float(rank + 1))
     out = kf.ops.all_reduce_fn(big)
