@@ -150,6 +150,36 @@ def test_transform2_bf16_sum_rounds_to_nearest_even():
     assert torch.equal(z, (a.float() + b.float()).bfloat16())
 
 
+@pytest.mark.parametrize('n', [0, 1, 7, 8, 9, 1003, 4099])
+def test_transform2_16bit_ops_are_exact_and_in_place_safe(n):
+    """fp16 / bf16 through all four ops: the 8-lane path and the scalar tail give the fp32 result rounded to
+    nearest even, bit for bit, also when the output is one of the inputs (the graph walk reduces in place)."""
+    import torch
+    l = _lib()
+    g = torch.Generator().manual_seed(n)
+    for dt, code in ((torch.float16, H.F16), (torch.bfloat16, H.BF16)):
+        a = (torch.randn(n, generator=g) * 3).to(dt)
+        b = (torch.randn(n, generator=g) * 3).to(dt)
+        for op, f in ((0, torch.add), (1, torch.minimum), (2, torch.maximum), (3, torch.mul)):
+            ref = f(a.float(), b.float()).to(dt)
+            z = torch.full((n, ), 7, dtype=dt)
+            l.kf_transform2(a.data_ptr(), b.data_ptr(), z.data_ptr(), n, code, op)
+            assert torch.equal(z, ref), (dt, op)
+            x = a.clone()
+            l.kf_transform2(x.data_ptr(), b.data_ptr(), x.data_ptr(), n, code, op)  # z is x
+            assert torch.equal(x, ref), (dt, op, 'in place on x')
+            y = b.clone()
+            l.kf_transform2(a.data_ptr(), y.data_ptr(), y.data_ptr(), n, code, op)  # z is y
+            assert torch.equal(y, ref), (dt, op, 'in place on y')
+    for dt, code in ((torch.float32, H.F32), (torch.int32, H.I32), (torch.float64, H.F64), (torch.int64, H.I64)):
+        a = (torch.randn(n, generator=g) * 100).to(dt)
+        b = (torch.randn(n, generator=g) * 100).to(dt)
+        for op, f in ((0, torch.add), (1, torch.minimum), (2, torch.maximum), (3, torch.mul)):
+            x = a.clone()
+            l.kf_transform2(x.data_ptr(), b.data_ptr(), x.data_ptr(), n, code, op)
+            assert torch.equal(x, f(a, b)), (dt, op)
+
+
 def test_cluster_resize_grow_and_shrink():
     l = _lib()
     c = json.dumps({'Runners': ['10.0.0.1:38080', '10.0.0.2:38080'], 'Workers': ['10.0.0.1:10000']}).encode()
