@@ -372,6 +372,7 @@ int map_cuda_index(int slot, const char *visible, std::string *token)
             }
         }
     }
+    if (toks.empty()) return -1;  // CUDA_VISIBLE_DEVICES="": a CPU-only job by configuration, nothing to warn about
     bool numeric = true;
     for (auto &t : toks) {
         size_t i = (t[0] == '-' || t[0] == '+') ? 1 : 0;
