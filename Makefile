@@ -1,5 +1,5 @@
 # Convenience targets; the build itself is kungfu_b200/_build.py (no CMake, no Go).
-.PHONY: build test gpu-test sanitize fuzz sass docs clean
+.PHONY: build test gpu-test sanitize fuzz sass docs package-check clean
 
 build:
 	python -m kungfu_b200._build
@@ -21,6 +21,9 @@ sass: build
 
 docs:
 	python scripts/gen-api-doc.py
+
+package-check:
+	scripts/package-check.sh
 
 clean:
 	rm -rf build kungfu_b200/lib kungfu_b200/bin
