@@ -42,12 +42,11 @@ def test_mnist_slp_np_invariance(tmp_path):
     to 1e-12 and the accuracy exactly. In float32 (the reference's precision) that reordering is visible
     in the last bits of every gradient sum; over 40 steps it reaches a few 1e-5 (bound used: 1e-4) and the accuracy, a count
     over 2000 samples, is still identical."""
+    for np_ in (1, 2, 3, 4):  # both precisions in one launch per cluster size
+        res = run_workers(np_, os.path.join(W, 'mnist_slp_worker.py'), args=['48', '40', str(tmp_path / ('slp%d.pt' % np_)), 'f64,f32'])
+        assert res.returncode == 0 and res.stdout.count('OK rank') == 2 * np_, res.stdout[-3000:]
     for dt, tol in (('f64', 1e-12), ('f32', 1e-4)):
-        outs = []
-        for np_ in (1, 2, 3, 4):
-            out = str(tmp_path / ('slp%d%s.pt' % (np_, dt)))
-            _ok(run_workers(np_, os.path.join(W, 'mnist_slp_worker.py'), args=['48', '40', out, dt]), np_)
-            outs.append(torch.load(out))
+        outs = [torch.load(str(tmp_path / ('slp%d.pt.%s' % (np_, dt)))) for np_ in (1, 2, 3, 4)]
         for o in outs[1:]:
             assert torch.allclose(o['w'], outs[0]['w'], atol=tol, rtol=0), (dt, (o['w'] - outs[0]['w']).abs().max())
             assert torch.allclose(o['b'], outs[0]['b'], atol=tol, rtol=0), (dt, (o['b'] - outs[0]['b']).abs().max())
