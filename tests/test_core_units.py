@@ -305,7 +305,7 @@ def test_built_library_contains_the_blackwell_instructions():
                               ('UTMALDG.2D', 'cp.async.bulk.tensor (TMA)'), ('UTCBAR', 'tcgen05.commit'),
                               ('LDTM', 'tcgen05.ld'), ('UCGABAR_ARV', 'barrier.cluster'), ('LDGMC', 'multimem.ld_reduce'),
                               ('SYNCS.PHASECHK', 'mbarrier.try_wait')):
-        assert re.search(r'\b' + re.escape(mnemonic), sass), '%s (%s) not found in the SASS' % (mnemonic, meaning)
+        assert mnemonic in sass, '%s (%s) not found in the SASS' % (mnemonic, meaning)
 
 
 def test_json_and_hostfile_parsers_survive_mutated_and_deeply_nested_input():
