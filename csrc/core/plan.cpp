@@ -365,7 +365,13 @@ bool Cluster::resize(int new_size, Cluster *out, std::string *err) const
         uint16_t port = 0;
         for (auto &w : out->workers)
             if (w.ipv4 == host && port <= w.port) port = w.port + 1;
-        if (port == 0) port = PortRange().begin;
+        if (port == 0) {
+            // a host without workers: start where the job's other hosts start (a job launched with -port-range keeps
+            // its ports on new hosts too); the default range only for an empty cluster, as in the reference
+            for (auto &w : out->workers)
+                if (port == 0 || w.port < port) port = w.port;
+            if (port == 0) port = PortRange().begin;
+        }
         out->workers.push_back(PeerID{host, port});
     }
     return true;

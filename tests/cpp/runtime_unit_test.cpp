@@ -80,6 +80,13 @@ static void test_cluster_resize()
     CHECK(c.resize(4, &d, &err) && d.workers.size() == 4 && d.workers[3] == (PeerID{2, 101}));
     CHECK(c.resize(1, &d, &err) && d.workers.size() == 1 && d.workers[0] == c.workers[0]);  // shrink keeps the head
     CHECK(c.resize(3, &d, &err) && d == c);
+    // a host that has no worker yet starts at the lowest port the job uses elsewhere; an empty cluster at the default
+    Cluster e2;
+    e2.runners = {PeerID{1, 38080}, PeerID{2, 38080}};
+    e2.workers = {PeerID{1, 31700}, PeerID{1, 31701}};
+    CHECK(e2.resize(3, &d, &err) && d.workers[2] == (PeerID{2, 31700}));
+    e2.workers.clear();
+    CHECK(e2.resize(1, &d, &err) && d.workers[0] == (PeerID{1, 10000}));
     // JSON round trip (what the config server stores)
     Cluster e;
     CHECK(parse_cluster_json(c.json(), &e, &err) && e == c);

@@ -81,3 +81,32 @@ def test_rrun_starts_one_runner_per_host_through_ssh(tmp_path):
     r = subprocess.run([os.path.join(bindir, 'kungfu-distribute'), '-H', '127.0.0.1:1,127.0.0.2:1', 'sh', '-c', 'exit 3'],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=60)
     assert r.returncode == 3 and r.stdout.count('exited with 3') == 2, r.stdout
+
+
+def test_experiment_tools_install_and_scale_through_ssh(tmp_path):
+    """benchmarks/experiments.py --remote-install and --scaling over two loopback hosts, with the stand-in ssh:
+    the packed tree is pushed and pip-installed per host, then a config server + kungfu-rrun job follows a
+    resize schedule that spreads over both hosts (reference: experiments/cmd/kungfu-remote-install,
+    kungfu-run-scaling-experiments)."""
+    fake = tmp_path / 'ssh'
+    fake.write_text(FAKE_SSH)
+    fake.chmod(0o755)
+    bindir = os.path.join(ROOT, 'kungfu_b200', 'bin')
+    env = dict(os.environ, PYTHONPATH=ROOT, PATH='%s:%s:%s' % (tmp_path, bindir, os.environ.get('PATH', '')))
+    exp = [sys.executable, os.path.join(ROOT, 'benchmarks', 'experiments.py')]
+    # dry run of the install: one ssh per host, public address honoured
+    r = subprocess.run(exp + ['--remote-install', '--hosts', '10.0.0.1:8,10.0.0.2:8:node2.example', '--user', 'me', '--dry-run'],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=60)
+    lines = r.stdout.strip().splitlines()
+    assert r.returncode == 0 and len(lines) == 2 and 'me@10.0.0.1' in lines[0] and 'me@node2.example' in lines[1], r.stdout
+    # the scaling experiment for real: 1 -> 3 -> 4 -> 2 workers over two hosts with two slots each
+    base = 34000 + (os.getpid() * 13) % 8000
+    r = subprocess.run(exp + ['--scaling', '2:1,2:3,2:4,2:2', '--model-mb', '1', '--hosts', '127.0.0.1:2,127.0.0.2:2', '--config-port',
+                              str(base + 90), '--port-range', '%d-%d' % (base, base + 16), '--runner-port', str(base + 80),
+                              '--timeout', '200'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=240)
+    assert r.returncode == 0, r.stdout[-4000:]
+    for a, b in ((1, 3), (3, 4), (4, 2)):
+        assert 'RESIZE %d -> %d took' % (a, b) in r.stdout, r.stdout[-4000:]
+    assert r.stdout.count(' done') == 2 and r.stdout.count('detached at step') == 2, r.stdout[-4000:]
+    # every worker of the second host listens inside the job's port range, not the default one
+    assert '[127.0.0.2.%d::' % base in r.stdout and '127.0.0.2.10000' not in r.stdout, r.stdout[-4000:]
