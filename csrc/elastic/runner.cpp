@@ -129,7 +129,8 @@ int config_server_main(int argc, char **argv)
     bool has_init = false;
     if (!init_file.empty()) {
         std::string text, err;
-        if (!open_url(init_file, &text, &err) || !parse_cluster_json(text, &init, &err)) {
+        // the same checks a PUT goes through: a cluster that workers would refuse must not be published
+        if (!open_url(init_file, &text, &err) || !parse_cluster_json(text, &init, &err) || !init.validate(&err)) {
             fprintf(stderr, "bad -init %s: %s\n", init_file.c_str(), err.c_str());
             return 1;
         }

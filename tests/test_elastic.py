@@ -94,6 +94,40 @@ def test_config_server_rest_api(tmp_path):
             p.kill()
 
 
+def test_config_server_init_file_endpoint_and_ttl(tmp_path):
+    """-init publishes a cluster from a file, -endpoint moves the REST path (the reference's examples use /get and
+    /put), -ttl makes the server leave by itself (reference: cmd/kungfu-config-server/kungfu-config-server.go:19-65)."""
+    port = _free_port()
+    init = tmp_path / 'cluster.json'
+    init.write_text('{"Runners":["127.0.0.1:38080"],"Workers":["127.0.0.1:10000","127.0.0.1:10001","127.0.0.1:10002"]}')
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-config-server')
+    t0 = time.time()
+    p = subprocess.Popen([exe, '-port', str(port), '-init', str(init), '-endpoint', '/get', '-ttl', '2s'],
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    try:
+        got = None
+        for _ in range(50):
+            try:
+                got = urllib.request.urlopen('http://127.0.0.1:%d/get' % port).read().decode()
+                break
+            except urllib.error.HTTPError:
+                raise
+            except Exception:
+                time.sleep(0.05)
+        assert got is not None and got.count('127.0.0.1:1000') == 3, got
+        with pytest.raises(urllib.error.HTTPError) as ei:  # the default path is not served when -endpoint moved it
+            urllib.request.urlopen('http://127.0.0.1:%d/config' % port)
+        assert ei.value.code == 404
+        assert p.wait(timeout=10) == 0 and 1.5 < time.time() - t0 < 9
+    finally:
+        if p.poll() is None:
+            p.kill()
+    bad = tmp_path / 'bad.json'
+    bad.write_text('{"Runners":[],"Workers":["127.0.0.1:10000"]}')
+    r = subprocess.run([exe, '-port', str(_free_port()), '-init', str(bad)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=10)
+    assert r.returncode != 0 and 'bad -init' in r.stdout
+
+
 def test_regrow_onto_a_used_address_restarts_the_control_exchange():
     """1 -> 2 -> 1 -> 2 -> 1 -> 2: same size, same rank, new peer each time (found on GPUs, where the second
     grow hung in PeerComm's first all-gather because the survivor kept counting message names)."""
