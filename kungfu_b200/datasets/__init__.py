@@ -91,6 +91,85 @@ class ElasticShardedDataset(object):
         return self.xs[idx], self.ys[idx]
 
 
+class ElasticBatchSampler(object):
+    """``batch_sampler`` for ``torch.utils.data.DataLoader`` under a changing cluster size.
+
+    Every step consumes ``global_batch_size`` consecutive positions of a per-epoch permutation that all
+    workers derive from ``(seed, epoch)``; this worker takes its slice of them. The whole state is the
+    number of samples consumed so far (``consumed``), which ``ElasticState`` already keeps in step with
+    the cluster: after a resize call ``reshard(rank, size)`` (optionally with the synced ``consumed``)
+    and the stream goes on where the cluster as a whole stopped -- nothing is skipped or seen twice,
+    whatever the sizes before and after. The reference keeps the same three integers in tf.Variables
+    (/root/reference/srcs/python/kungfu/tensorflow/v1/datasets/adaptor.py:4-45).
+
+        sampler = ElasticBatchSampler(len(ds), 256, kf.current_rank(), kf.current_cluster_size(), shuffle=True)
+        loader = DataLoader(ds, batch_sampler=sampler, num_workers=4)
+    """
+
+    def __init__(self, n_samples, global_batch_size, rank=0, size=1, shuffle=False, seed=0, consumed=0, drop_last=True):
+        self.n = int(n_samples)
+        self.global_batch_size = int(global_batch_size)
+        self.shuffle, self.seed, self.drop_last = shuffle, seed, drop_last
+        self.consumed = int(consumed)
+        self._perm_epoch, self._perm = None, None
+        self.reshard(rank, size)
+
+    def reshard(self, rank, size, consumed=None, global_batch_size=None):
+        if global_batch_size is not None:
+            self.global_batch_size = int(global_batch_size)
+        if self.global_batch_size % size:
+            raise ValueError('global batch %d is not divisible by %d workers' % (self.global_batch_size, size))
+        self.rank, self.size = int(rank), int(size)
+        if consumed is not None:
+            self.consumed = int(consumed)
+
+    @property
+    def epoch(self):
+        return self.consumed // self._epoch_len()
+
+    def _epoch_len(self):
+        # samples handed out per epoch: whole global batches only (drop_last), else the tail wraps into the next epoch
+        if self.drop_last:
+            return max(self.n - self.n % self.global_batch_size, self.global_batch_size)
+        return self.n
+
+    def _order(self, epoch):
+        if not self.shuffle:
+            return None
+        if self._perm_epoch != epoch:
+            g = torch.Generator().manual_seed(self.seed * 1000003 + epoch)
+            self._perm, self._perm_epoch = torch.randperm(self.n, generator=g).tolist(), epoch
+        return self._perm
+
+    def next_indices(self):
+        """This worker's indices for the next step; advances ``consumed`` by one global batch."""
+        local = self.global_batch_size // self.size
+        out = []
+        for i in range(local):
+            g = self.consumed + self.rank * local + i
+            epoch, pos = divmod(g, self._epoch_len())
+            order = self._order(epoch)
+            out.append(order[pos % self.n] if order is not None else pos % self.n)
+        self.consumed += self.global_batch_size
+        return out
+
+    def __iter__(self):
+        # one epoch's worth of steps from wherever the cluster is now
+        epoch = self.epoch
+        while self.epoch == epoch:
+            yield self.next_indices()
+
+    def __len__(self):
+        return self._epoch_len() // self.global_batch_size
+
+    def state_dict(self):
+        return {'consumed': self.consumed, 'global_batch_size': self.global_batch_size, 'seed': self.seed}
+
+    def load_state_dict(self, state):
+        self.consumed, self.global_batch_size, self.seed = state['consumed'], state['global_batch_size'], state['seed']
+        self._perm_epoch = None
+
+
 from .vision import (ImageFolder, gpu_augment, load_cifar10, npz_to_idx_tar, random_input)  # noqa: E402,F401
 
 

@@ -60,3 +60,45 @@ def test_image_folder_and_batched_augmentation(tmp_path):
     assert float((ev[0, 0] - ev[0, 0, 0, 0]).abs().max()) < 1e-4
     xs, ys = random_input((3, 8, 8), 5, batch=4)
     assert xs.shape == (4, 3, 8, 8) and ys.shape == (4, 5) and float(ys.sum()) == 4
+
+
+def test_elastic_batch_sampler_covers_every_sample_once_across_resizes():
+    """Cluster sizes 2 -> 3 -> 1 -> 4 in the middle of epochs: the union over the workers of every step is one
+    contiguous run of the epoch's permutation, an epoch (whole batches) touches each of its samples exactly once,
+    and the permutation changes from epoch to epoch but is the same on every worker."""
+    import torch
+    from torch.utils.data import DataLoader, TensorDataset
+
+    from kungfu_b200.datasets import ElasticBatchSampler
+    n, gb = 1000, 24
+    plan = [(2, 7), (3, 9), (1, 11), (4, 60)]  # (cluster size, steps at that size)
+    consumed, seen = 0, []
+    for size, steps in plan:
+        workers = [ElasticBatchSampler(n, gb, r, size, shuffle=True, seed=5, consumed=consumed) for r in range(size)]
+        for _ in range(steps):
+            step = [w.next_indices() for w in workers]
+            assert all(len(s) == gb // size for s in step)
+            seen.append([i for s in step for i in s])
+        consumed = workers[0].consumed
+        assert all(w.consumed == consumed for w in workers)
+    per_epoch = n - n % gb  # 984: whole global batches only
+    flat = [i for s in seen for i in s]
+    e0, e1 = flat[:per_epoch], flat[per_epoch:2 * per_epoch]
+    assert len(set(e0)) == per_epoch and len(set(e1)) == per_epoch  # nothing twice within an epoch
+    assert e0 != e1                                                  # reshuffled
+    ref = ElasticBatchSampler(n, gb, 0, 1, shuffle=True, seed=5)
+    assert [i for _ in range(len(seen)) for i in ref.next_indices()] == flat  # == what one worker alone would have seen
+
+    # as a DataLoader batch_sampler: one epoch from the current position, then the next one
+    ds = TensorDataset(torch.arange(100))
+    s = ElasticBatchSampler(100, 10, rank=1, size=2)
+    got = [b[0].tolist() for b in DataLoader(ds, batch_sampler=s)]
+    assert len(got) == len(s) == 10 and got[0] == [5, 6, 7, 8, 9] and got[-1] == [95, 96, 97, 98, 99]
+    s.reshard(0, 5)
+    assert next(iter(DataLoader(ds, batch_sampler=s)))[0].tolist() == [0, 1]
+    t = ElasticBatchSampler(100, 10)
+    t.load_state_dict(s.state_dict())
+    assert t.consumed == s.consumed == 110
+    import pytest
+    with pytest.raises(ValueError):
+        s.reshard(0, 3)
