@@ -107,12 +107,16 @@ def scaling(args):
         full = json.loads(subprocess.check_output(init, text=True))
         full['Workers'] = full['Workers'][:first]
         for _ in range(50):
+            if srv.poll() is not None:
+                raise RuntimeError('kungfu-config-server exited with %d (is port %d taken?)' % (srv.returncode, args.config_port))
             try:
                 req = urllib.request.Request(url, data=json.dumps(full).encode(), method='PUT')
                 urllib.request.urlopen(req, timeout=5).read()
                 break
             except Exception:
                 time.sleep(0.1)
+        else:
+            raise RuntimeError('the config server at %s never accepted the first cluster' % url)
         return subprocess.run(job, timeout=args.timeout).returncode
     finally:
         try:

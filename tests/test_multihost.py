@@ -3,6 +3,7 @@ each with its own kungfu-run (the way kungfu-rrun would start them)."""
 import os
 import subprocess
 import sys
+import time
 
 import pytest
 
@@ -63,7 +64,7 @@ def test_rrun_starts_one_runner_per_host_through_ssh(tmp_path):
     fake.write_text(FAKE_SSH)
     fake.chmod(0o755)
     bindir = os.path.join(ROOT, 'kungfu_b200', 'bin')
-    base = 33000 + (os.getpid() * 17) % 10000
+    base = 20000 + (os.getpid() * 17) % 10000  # below the ephemeral range
     env = dict(os.environ, PYTHONPATH=ROOT, PATH='%s:%s:%s' % (tmp_path, bindir, os.environ.get('PATH', '')))
     cmd = [os.path.join(bindir, 'kungfu-rrun'), '-H', '127.0.0.1:2,127.0.0.2:1', '-u', 'nobody', '-q', '-np', '3', '-timeout', '90s',
            '-port-range', '%d-%d' % (base, base + 16), '-port', str(base + 20), sys.executable, '-c',
@@ -77,10 +78,15 @@ def test_rrun_starts_one_runner_per_host_through_ssh(tmp_path):
     # output is prefixed with the host it came from
     assert '[127.0.0.1] ' in r.stdout and '[127.0.0.2] ' in r.stdout
 
-    # a failing host is reported and fails the whole call
-    r = subprocess.run([os.path.join(bindir, 'kungfu-distribute'), '-H', '127.0.0.1:1,127.0.0.2:1', 'sh', '-c', 'exit 3'],
-                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=60)
-    assert r.returncode == 3 and r.stdout.count('exited with 3') == 2, r.stdout
+    # a failing host fails the whole call and the other hosts are cancelled, as the reference does: whichever host
+    # takes the lock sleeps for a minute, the other one exits 3 at once
+    lock = tmp_path / 'lock'
+    t0 = time.time()
+    r = subprocess.run([os.path.join(bindir, 'kungfu-distribute'), '-H', '127.0.0.1:1,127.0.0.2:1', 'sh', '-c',
+                        'mkdir %s 2>/dev/null && exec sleep 60 || exit 3' % lock],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=90)
+    assert r.returncode == 3 and 'exited with 3: stopping the other hosts' in r.stdout, r.stdout
+    assert time.time() - t0 < 20, 'the sleeping host was not cancelled'
 
 
 def test_experiment_tools_install_and_scale_through_ssh(tmp_path):
@@ -100,7 +106,7 @@ def test_experiment_tools_install_and_scale_through_ssh(tmp_path):
     lines = r.stdout.strip().splitlines()
     assert r.returncode == 0 and len(lines) == 2 and 'me@10.0.0.1' in lines[0] and 'me@node2.example' in lines[1], r.stdout
     # the scaling experiment for real: 1 -> 3 -> 4 -> 2 workers over two hosts with two slots each
-    base = 34000 + (os.getpid() * 13) % 8000
+    base = 21000 + (os.getpid() * 13) % 9000  # below the ephemeral range (a port someone's outgoing connection holds cannot be bound)
     r = subprocess.run(exp + ['--scaling', '2:1,2:3,2:4,2:2', '--model-mb', '1', '--hosts', '127.0.0.1:2,127.0.0.2:2', '--config-port',
                               str(base + 90), '--port-range', '%d-%d' % (base, base + 16), '--runner-port', str(base + 80),
                               '--timeout', '200'], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env, timeout=240)
