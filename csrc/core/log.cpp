@@ -28,7 +28,7 @@ void log_set_file(const std::string &path)
 {
     std::lock_guard<std::mutex> lk(g_log_mu);
     if (g_file) fclose(g_file);
-    g_file = path.empty() ? nullptr : fopen(path.c_str(), "a");
+    g_file = path.empty() ? nullptr : fopen(path.c_str(), "ae");  // close-on-exec: a log file is not for the workers to inherit
 }
 
 void log_msg(LogLevel l, const char *fmt, ...)

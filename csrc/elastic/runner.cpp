@@ -547,8 +547,8 @@ class ProcTable
         FILE *lo = nullptr, *le = nullptr;
         if (!spec.logdir.empty()) {
             mkdir(spec.logdir.c_str(), 0755);
-            lo = fopen((spec.logdir + "/" + spec.log_tag + ".stdout.log").c_str(), "w");
-            le = fopen((spec.logdir + "/" + spec.log_tag + ".stderr.log").c_str(), "w");
+            lo = fopen((spec.logdir + "/" + spec.log_tag + ".stdout.log").c_str(), "we");
+            le = fopen((spec.logdir + "/" + spec.log_tag + ".stderr.log").c_str(), "we");
         }
         const char *color = kColors[color_++ % 6];
         rp->out_th = std::thread([=] { pump(po[0], spec.name + "::stdout", color, verbose_, lo, false); if (lo) fclose(lo); });
