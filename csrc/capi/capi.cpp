@@ -13,6 +13,7 @@
 #include "core/log.hpp"
 #include "core/plan.hpp"
 #include "ctrl/peer.hpp"
+#include "ctrl/transport.hpp"
 #include "elastic/runner.hpp"
 
 using namespace kf;
@@ -301,6 +302,7 @@ int64_t kf_request_async(kf_peer *p, int target_rank, const char *version, const
 struct kf_prefetch_state {
     std::mutex mu;
     std::condition_variable cv;
+    size_t nbytes = 0;  // of either buffer; fixed (the vectors themselves are swapped under mu)
     std::vector<uint8_t> model, incoming;
     bool have = false, requesting = false;
     int64_t fresh = 0;
@@ -319,19 +321,20 @@ kf_prefetch *kf_prefetch_new(kf_peer *p, const char *name, int64_t nbytes)
         return nullptr;
     }
     auto *pf = new kf_prefetch{p, name, std::make_shared<kf_prefetch_state>()};
+    pf->st->nbytes = (size_t)nbytes;
     pf->st->model.resize((size_t)nbytes);
     pf->st->incoming.resize((size_t)nbytes);
     return pf;
 }
 
-int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh)
+// First call: blocking pull. Every call: start the pull for the next one unless one is in flight.
+static bool prefetch_acquire(kf_prefetch *pf, int target_rank)
 {
-    if (!pf || !out) return fail("kf_prefetch_next: null argument");
     auto st    = pf->st;
     Peer *peer = pf->peer->peer.get();
-    const size_t n = st->model.size();
+    const size_t n = st->nbytes;
     if (!st->have) {
-        if (!peer->request(target_rank, "", pf->name, st->model.data(), n)) return done(pf->peer, false);
+        if (!peer->request(target_rank, "", pf->name, st->model.data(), n)) return false;
         st->have = true;
     }
     bool start = false;
@@ -353,8 +356,63 @@ int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh
             st->cv.notify_all();
         });
     }
+    return true;
+}
+
+int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh)
+{
+    if (!pf || !out) return fail("kf_prefetch_next: null argument");
+    if (!prefetch_acquire(pf, target_rank)) return done(pf->peer, false);
+    auto st = pf->st;
     std::lock_guard<std::mutex> lk(st->mu);
-    memcpy(out, st->model.data(), n);
+    memcpy(out, st->model.data(), st->nbytes);
+    if (fresh) *fresh = st->fresh;
+    return 0;
+}
+
+int kf_save_parts(kf_peer *p, const char *version, const char *name, const void *const *parts, const int64_t *nbytes, int n)
+{
+    if (!p || !name || n < 0 || (n > 0 && (!parts || !nbytes))) return fail("kf_save_parts: bad argument");
+    size_t total = 0;
+    for (int i = 0; i < n; ++i) {
+        if (nbytes[i] < 0 || (nbytes[i] > 0 && !parts[i])) return fail("kf_save_parts: bad part");
+        total += (size_t)nbytes[i];
+    }
+    auto blob = new_blob(total);  // recycled storage when a previous version of this size has been released
+    size_t off = 0;
+    for (int i = 0; i < n; ++i) {
+        if (nbytes[i]) memcpy(blob->data() + off, parts[i], (size_t)nbytes[i]);
+        off += (size_t)nbytes[i];
+    }
+    p->peer->save_blob(version ? version : "", name, std::move(blob));
+    return 0;
+}
+
+__attribute__((optimize("O3", "tree-vectorize"))) static void blend_half(float *t, const float *o, int64_t n)
+{
+#pragma GCC ivdep
+    for (int64_t i = 0; i < n; ++i) t[i] = 0.5f * (t[i] + o[i]);
+}
+
+void kf_blend_f32(float *const *tensors, const int64_t *counts, int n, const float *other)
+{
+    int64_t off = 0;
+    for (int i = 0; i < n; ++i) {
+        blend_half(tensors[i], other + off, counts[i]);
+        off += counts[i];
+    }
+}
+
+int kf_prefetch_blend_f32(kf_prefetch *pf, int target_rank, float *const *tensors, const int64_t *counts, int n, int64_t *fresh)
+{
+    if (!pf || n < 0 || (n > 0 && (!tensors || !counts))) return fail("kf_prefetch_blend_f32: bad argument");
+    int64_t total = 0;
+    for (int i = 0; i < n; ++i) total += counts[i];
+    if ((size_t)total * sizeof(float) != pf->st->nbytes) return fail("kf_prefetch_blend_f32: tensors do not add up to the model size");
+    if (!prefetch_acquire(pf, target_rank)) return done(pf->peer, false);
+    auto st = pf->st;
+    std::lock_guard<std::mutex> lk(st->mu);  // the background pull swaps buffers under this lock
+    kf_blend_f32(tensors, counts, n, (const float *)st->model.data());
     if (fresh) *fresh = st->fresh;
     return 0;
 }

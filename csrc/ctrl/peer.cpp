@@ -360,6 +360,12 @@ void Peer::save(const std::string &version, const std::string &name, const void 
     else server_->vstore.save(version, name, data, n);
 }
 
+void Peer::save_blob(const std::string &version, const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob)
+{
+    if (version.empty()) server_->store.adopt(name, std::move(blob));
+    else server_->vstore.adopt(version, name, std::move(blob));
+}
+
 bool Peer::request(int target_rank, const std::string &version, const std::string &name, void *buf, size_t n)
 {
     Session *s = session();

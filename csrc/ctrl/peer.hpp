@@ -110,6 +110,8 @@ class Peer
 
     // p2p model store
     void save(const std::string &version, const std::string &name, const void *data, size_t n);
+    // publish a blob that was assembled by the caller (one copy from the tensors into the store, not two)
+    void save_blob(const std::string &version, const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob);
     bool request(int target_rank, const std::string &version, const std::string &name, void *buf, size_t n);
 
     // descriptor passing for the device layer

@@ -449,14 +449,73 @@ void Mailbox::reset()
 }
 
 // ---- stores -----------------------------------------------------------------------------
+namespace {
+class BlobPool
+{
+    static constexpr size_t kMinPooled = size_t(1) << 20, kKeep = 4;
+    std::mutex mu_;
+    std::vector<std::vector<uint8_t> *> free_;
+
+  public:
+    std::vector<uint8_t> *take(size_t n)
+    {
+        if (n >= kMinPooled) {
+            std::lock_guard<std::mutex> lk(mu_);
+            for (size_t i = 0; i < free_.size(); ++i) {
+                if (free_[i]->capacity() >= n && free_[i]->capacity() <= n + n / 8) {
+                    std::vector<uint8_t> *v = free_[i];
+                    free_.erase(free_.begin() + i);
+                    v->resize(n);  // within capacity: no reallocation, no page faults on the recycled part
+                    return v;
+                }
+            }
+        }
+        return new std::vector<uint8_t>(n);
+    }
+    void give(std::vector<uint8_t> *v)
+    {
+        if (v->capacity() >= kMinPooled) {
+            std::lock_guard<std::mutex> lk(mu_);
+            if (free_.size() < kKeep) {
+                free_.push_back(v);
+                return;
+            }
+        }
+        delete v;
+    }
+};
+BlobPool &blob_pool()
+{
+    static BlobPool *p = new BlobPool();  // never destroyed: blobs may outlive static destructors
+    return *p;
+}
+}  // namespace
+
+std::shared_ptr<std::vector<uint8_t>> new_blob(size_t n)
+{
+    return std::shared_ptr<std::vector<uint8_t>>(blob_pool().take(n), [](std::vector<uint8_t> *v) { blob_pool().give(v); });
+}
+
 void BlobStore::save(const std::string &name, const void *data, size_t n)
 {
-    // A fresh vector per save: readers holding the old shared_ptr never see a
-    // torn blob (the reference copied in place without a lock,
-    // /root/reference/srcs/go/store/blob.go:20-26).
-    auto v = std::make_shared<std::vector<uint8_t>>((const uint8_t *)data, (const uint8_t *)data + n);
+    // A vector of its own per save (new, or storage that no reader holds any more): readers
+    // holding the old shared_ptr never see a torn blob (the reference copied in place without
+    // a lock, /root/reference/srcs/go/store/blob.go:20-26).
+    auto v = new_blob(n);
+    if (n) memcpy(v->data(), data, n);
     std::lock_guard<std::mutex> lk(mu_);
     blobs_[name] = v;
+}
+
+void BlobStore::adopt(const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob)
+{
+    std::shared_ptr<std::vector<uint8_t>> old;  // dies after the lock is released: its deleter takes the pool's lock
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto &slot = blobs_[name];
+        old.swap(slot);
+        slot = std::move(blob);
+    }
 }
 
 std::shared_ptr<std::vector<uint8_t>> BlobStore::get(const std::string &name)
@@ -466,7 +525,7 @@ std::shared_ptr<std::vector<uint8_t>> BlobStore::get(const std::string &name)
     return it == blobs_.end() ? nullptr : it->second;
 }
 
-void VersionedStore::save(const std::string &version, const std::string &name, const void *data, size_t n)
+void VersionedStore::adopt(const std::string &version, const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob)
 {
     std::shared_ptr<BlobStore> s;
     {
@@ -479,7 +538,14 @@ void VersionedStore::save(const std::string &version, const std::string &name, c
             while (versions_.size() > window_) versions_.pop_front();
         }
     }
-    s->save(name, data, n);
+    s->adopt(name, std::move(blob));
+}
+
+void VersionedStore::save(const std::string &version, const std::string &name, const void *data, size_t n)
+{
+    auto v = new_blob(n);
+    if (n) memcpy(v->data(), data, n);
+    adopt(version, name, std::move(v));
 }
 
 std::shared_ptr<std::vector<uint8_t>> VersionedStore::get(const std::string &version, const std::string &name)

@@ -147,6 +147,12 @@ class Mailbox
 
 // ---- versioned in-memory blob store (the model store PairAveraging pulls from) -------------
 // Parity: /root/reference/srcs/go/store/{store.go,versionedstore.go,blob.go}
+// Storage for published blobs. A model is published every step and each version lives until its last reader is
+// done with it; a fresh 100 MB vector per step costs more in page faults than the copy into it. new_blob(n) hands
+// out a vector of n bytes (contents unspecified) whose storage goes back to a small free list when the last
+// shared_ptr to it dies, in whichever thread that happens.
+std::shared_ptr<std::vector<uint8_t>> new_blob(size_t n);
+
 class BlobStore
 {
     std::mutex mu_;
@@ -154,6 +160,7 @@ class BlobStore
 
   public:
     void save(const std::string &name, const void *data, size_t n);
+    void adopt(const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob);  // no copy
     std::shared_ptr<std::vector<uint8_t>> get(const std::string &name);
 };
 
@@ -166,6 +173,7 @@ class VersionedStore
   public:
     explicit VersionedStore(size_t window = 3) : window_(window) {}
     void save(const std::string &version, const std::string &name, const void *data, size_t n);
+    void adopt(const std::string &version, const std::string &name, std::shared_ptr<std::vector<uint8_t>> blob);
     std::shared_ptr<std::vector<uint8_t>> get(const std::string &version, const std::string &name);
     size_t versions() const { return versions_.size(); }
 };

@@ -77,6 +77,17 @@ kf_prefetch *kf_prefetch_new(kf_peer *p, const char *name, int64_t nbytes);
 int kf_prefetch_next(kf_prefetch *pf, int target_rank, void *out, int64_t *fresh);
 void kf_prefetch_free(kf_prefetch *pf);
 
+/* Fused-model helpers for a model that lives in n separate tensors (fp32 unless noted), so the host path touches
+ * every byte once instead of concatenating, copying and splitting in the caller:
+ *   kf_save_parts        gather n byte ranges straight into a new blob of the store (any dtype);
+ *   kf_blend_f32         t_i <- 0.5 * (t_i + other[off_i ...]) for every tensor, 8 lanes at a time;
+ *   kf_prefetch_blend_f32  kf_prefetch_next + kf_blend_f32 without the intermediate copy: the newest complete
+ *                          model is blended into the tensors directly from the double buffer.
+ * counts are elements for the f32 calls, bytes for kf_save_parts. */
+int kf_save_parts(kf_peer *p, const char *version, const char *name, const void *const *parts, const int64_t *nbytes, int n);
+void kf_blend_f32(float *const *tensors, const int64_t *counts, int n, const float *other);
+int kf_prefetch_blend_f32(kf_prefetch *pf, int target_rank, float *const *tensors, const int64_t *counts, int n, int64_t *fresh);
+
 /* elastic control */
 int kf_resize_cluster(kf_peer *p, int new_size, int *changed, int *detached);
 int kf_resize_cluster_from_url(kf_peer *p, int *changed, int *detached);

@@ -86,6 +86,9 @@ def _declare(l):
     f('kf_prefetch_new', _VP, _VP, C.c_char_p, C.c_int64)
     f('kf_prefetch_next', C.c_int, _VP, C.c_int, _VP, C.POINTER(C.c_int64))
     f('kf_prefetch_free', None, _VP)
+    f('kf_save_parts', C.c_int, _VP, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int)
+    f('kf_blend_f32', None, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int, _VP)
+    f('kf_prefetch_blend_f32', C.c_int, _VP, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int, C.POINTER(C.c_int64))
     f('kf_resize_cluster', C.c_int, _VP, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int))
     f('kf_resize_cluster_from_url', C.c_int, _VP, C.POINTER(C.c_int), C.POINTER(C.c_int))
     f('kf_peek_cluster_change', C.c_int, _VP, C.POINTER(C.c_int))
@@ -379,3 +382,28 @@ class Peer(object):
     @staticmethod
     def prefetch_free(pf):
         lib().kf_prefetch_free(pf)
+
+    @staticmethod
+    def _parts(ptrs, counts):
+        n = len(ptrs)
+        return (C.c_void_p * n)(*ptrs), (C.c_int64 * n)(*counts), n
+
+    def save_parts(self, name, ptrs, nbytes, version=None):
+        """Publish the concatenation of several byte ranges as one blob (gathered natively, one copy)."""
+        pa, ca, n = self._parts(ptrs, nbytes)
+        v = version.encode() if version is not None else None
+        _check(lib().kf_save_parts(self._h, v, name.encode(), pa, ca, n), 'save_parts')
+
+    @classmethod
+    def blend_f32(cls, ptrs, counts, other_ptr):
+        """t_i <- 0.5 * (t_i + other[...]) for fp32 tensors given by pointer / element count."""
+        pa, ca, n = cls._parts(ptrs, counts)
+        lib().kf_blend_f32(pa, ca, n, other_ptr)
+
+    @classmethod
+    def prefetch_blend_f32(cls, pf, target, ptrs, counts):
+        """prefetch_next fused with the blend: (ok, completed background pulls so far)."""
+        pa, ca, n = cls._parts(ptrs, counts)
+        fresh = C.c_int64(0)
+        rc = lib().kf_prefetch_blend_f32(pf, target, pa, ca, n, C.byref(fresh))
+        return rc == 0, int(fresh.value)

@@ -73,6 +73,7 @@ class _ModelOp(object):
         self._strategy = peer_selection_strategy
         self._seed = seed
         self._selector = None
+        self._landing = None
 
     def _next_peer(self):
         # built lazily: the cluster may not be up when the op is constructed
@@ -83,12 +84,27 @@ class _ModelOp(object):
             self._selector = PeerSelector(self._strategy, ranks, self._seed)
         return self._selector.next()
 
+    def _native(self):
+        """fp32 CPU tensors stored densely: the runtime gathers, pulls and blends them in place (one pass each)."""
+        return all(t.dtype == torch.float32 and not t.is_cuda and t.is_contiguous() for t in self.tensors)
+
+    def _ptrs(self):
+        return [t.data_ptr() for t in self.tensors], [t.numel() for t in self.tensors]
+
     def save(self):
         """Publish this worker's current model (SaveModel)."""
+        if self._native():
+            ptrs, counts = self._ptrs()
+            kfpy.peer().save_parts(self.name, ptrs, [4 * c for c in counts])
+            return self.total
         return _local.save_model([(None, t) for t in self.tensors], self.name)
 
     def _blend(self, flat):
         with torch.no_grad():
+            if self._native():
+                ptrs, counts = self._ptrs()
+                kfpy.peer().blend_f32(ptrs, counts, flat.data_ptr())
+                return
             for t, o in zip(self.tensors, _split(flat, self.tensors)):
                 t.mul_(0.5).add_(o.to(device=t.device, dtype=t.dtype), alpha=0.5)
 
@@ -100,7 +116,9 @@ class ModelAveraging(_ModelOp):
 
     def __call__(self):
         target = self._next_peer()
-        flat = torch.empty(self.total, dtype=torch.float32)
+        if self._landing is None:
+            self._landing = torch.empty(self.total, dtype=torch.float32)  # kept: no 100 MB allocation per step
+        flat = self._landing
         if not kfpy.peer().request(target, self.name, flat.data_ptr(), flat.numel() * 4, None):
             return -1
         self._blend(flat)
@@ -152,6 +170,16 @@ class AsyncModelAveraging(_Prefetching):
     nothing published."""
 
     def __call__(self):
+        if self._native():
+            peer = kfpy.peer()
+            if self._pf is None:
+                self._pf = peer.prefetch_new(self.name, self.total * 4)
+            ptrs, counts = self._ptrs()
+            with torch.no_grad():
+                ok, fresh = peer.prefetch_blend_f32(self._pf, self._next_peer(), ptrs, counts)
+            if ok:
+                self.fresh = fresh
+            return ok
         flat = self._pull()
         if flat is None:
             return False

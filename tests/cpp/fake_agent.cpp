@@ -99,11 +99,25 @@ int main()
         int64_t fresh = 0;
         for (int it = 0; it < 40; ++it) {
             std::fill(m.begin(), m.end(), (float)(rank + 1000 * (it + 1)));
-            CHECK(peer.Save("pf", m.data(), m.size() * 4) == 0);  // overwrite while peers pull
+            if (it % 2) {
+                CHECK(peer.Save("pf", m.data(), m.size() * 4) == 0);  // overwrite while peers pull
+            } else {  // the same from two parts, gathered by the runtime into a recycled blob
+                const void *parts[2]    = {m.data(), m.data() + 1000};
+                const int64_t nbytes[2] = {1000 * 4, (int64_t)(m.size() - 1000) * 4};
+                CHECK(kf_save_parts(peer.raw(), nullptr, "pf", parts, nbytes, 2) == 0);
+            }
             CHECK(kf_prefetch_next(pf, target, got.data(), &fresh) == 0);
             CHECK(got.front() == got.back());  // one snapshot, never a mixture of two
             CHECK(((int)got.front() - target) % 1000 == 0);
         }
+        // blend straight out of the double buffer: t <- 0.5 (t + newest model), two tensors
+        std::vector<float> t0(1000, 2.f), t1(m.size() - 1000, 4.f);
+        float *tensors[2]      = {t0.data(), t1.data()};
+        const int64_t cnts[2]  = {(int64_t)t0.size(), (int64_t)t1.size()};
+        CHECK(kf_prefetch_blend_f32(pf, target, tensors, cnts, 2, &fresh) == 0);
+        CHECK(t0.front() - 1.f == t1.back() - 2.f && t0.front() == t0.back());  // both halves of ONE snapshot v: 1 + v/2, 2 + v/2
+        const int64_t bad_cnts[2] = {1, 1};
+        CHECK(kf_prefetch_blend_f32(pf, target, tensors, bad_cnts, 2, &fresh) != 0);  // sizes must add up to the model
         kf_prefetch_free(pf);  // waits for the pull in flight
         std::vector<float> a(m.size(), -1.f);
         const int64_t h = kf_request_async(peer.raw(), target, nullptr, "pf", a.data(), (int64_t)a.size() * 4);

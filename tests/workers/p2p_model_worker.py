@@ -88,6 +88,23 @@ for _ in range(50):  # many calls in flight back to back: the double buffer neve
 aavg.close()
 aavg.close()  # idempotent
 
+# ---- models that are not dense fp32 take the generic path (fp32 on the wire, cast back on arrival) ----
+kf.run_barrier()
+mixed = [('w', torch.full((4, 6), float(rank), dtype=torch.float64).t()), ('b', torch.full((3, ), float(rank) + 0.5, dtype=torch.float16))]
+assert not mixed[0][1].is_contiguous()
+gen = p2p.ModelAveraging(mixed, 'roundrobin', name='mixed-model')
+assert not gen._native() and avg._native()
+gen.save()
+kf.run_barrier()
+t = gen()
+assert t == others[0] and mixed[0][1].dtype == torch.float64 and mixed[1][1].dtype == torch.float16
+assert torch.allclose(mixed[0][1], torch.full((6, 4), 0.5 * (rank + t), dtype=torch.float64))
+assert torch.allclose(mixed[1][1].float(), torch.full((3, ), 0.5 * (rank + t) + 0.5))
+agen = p2p.AsyncModelAveraging(mixed, 'roundrobin', name='mixed-model')
+assert agen() is True
+agen.close()
+kf.run_barrier()
+
 # ---- the raw async request handle ----
 buf = torch.empty(17, dtype=torch.float32)
 h = kfpy.peer().request_async(others[0], p2p.MODEL_NAME, buf.data_ptr(), 17 * 4)
