@@ -162,14 +162,35 @@ class _PairAveraging(object):
     def _fused_model(self):
         return torch.cat([tops.to_host(p.data.detach().reshape(-1).float()) for _, p in self._kf_named])
 
+    def _host_native(self):
+        """Dense fp32 parameters in host memory: the runtime publishes them by one gather into the store, lands the
+        peer's model in a buffer that is kept between steps and blends in one AVX pass (include/kungfu_host.h:
+        kf_save_parts, kf_blend_f32); nothing is concatenated, split or cast in Python."""
+        return all(p.dtype == torch.float32 and not p.is_cuda and p.data.is_contiguous() for _, p in self._kf_named)
+
+    def _publish(self, name):
+        if self._host_native():
+            params = [p.data for _, p in self._kf_named]
+            kfpy.peer().save_parts(name, [t.data_ptr() for t in params], [4 * t.numel() for t in params])
+        else:
+            tops.save_variable(self._fused_model(), name)
+
     def _generic_step(self):
         name = self._kf_model_name
         if not self._kf_started:
-            tops.save_variable(self._fused_model(), name)
+            self._publish(name)
             kfpy.run_barrier()
             self._kf_started = True
         target = self._pick()
-        if target >= 0:
+        if target >= 0 and self._host_native():
+            params = [p.data for _, p in self._kf_named]
+            total = sum(t.numel() for t in params)
+            land = getattr(self, '_kf_landing', None)
+            if land is None or land.numel() != total:
+                land = self._kf_landing = torch.empty(total, dtype=torch.float32)
+            if kfpy.peer().request(int(target), name, land.data_ptr(), total * 4, None):
+                kfpy.peer().blend_f32([t.data_ptr() for t in params], [t.numel() for t in params], land.data_ptr())
+        elif target >= 0:
             mine = self._fused_model()
             ok, other = tops.request_variable(target, name, mine)
             if ok:
@@ -180,7 +201,7 @@ class _PairAveraging(object):
                     p.data.add_(o).mul_(0.5)
                     off += n
         super(self.__class__, self).step()
-        tops.save_variable(self._fused_model(), name)
+        self._publish(name)
 
     def _on_device(self):
         if not all(p.is_cuda for _, p in self._kf_named):
