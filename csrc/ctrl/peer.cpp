@@ -332,8 +332,23 @@ bool Peer::resize_cluster(int new_size, bool *changed, bool *detached)
     *changed = *detached = false;
     if (cfg_.single) return true;
     if (!cfg_.config_server.empty()) {
-        if (session()->rank() == 0 && !propose_new_size(new_size)) return false;
-        // everyone waits until the server shows a cluster of the requested size
+        // Rank 0 publishes the new cluster; the others fetch it only after that PUT has landed (one tiny MIN
+        // all-reduce of rank 0's outcome), so the first fetch already agrees: no "diverged proposal" round with
+        // its 50 ms back-off, and a failed PUT fails the call on every rank instead of leaving the others polling.
+        int32_t ok = 1, all_ok = 0;
+        if (session()->rank() == 0 && !propose_new_size(new_size)) ok = 0;
+        Workspace w;
+        w.send  = &ok;
+        w.recv  = &all_ok;
+        w.count = 1;
+        w.dtype = I32;
+        w.op    = MIN;
+        w.name  = "kungfu::resize::proposed";
+        if (!session()->all_reduce(w)) return false;
+        if (!all_ok) {
+            if (session()->rank() != 0) set_error("rank 0 could not publish the resized cluster");
+            return false;
+        }
         return resize_cluster_from_url(changed, detached);
     }
     // No config server: every rank derives the same next cluster locally.

@@ -3,6 +3,7 @@ resident memory. Connections to removed peers, their reader threads and their bu
 the membership that used them (reference: rchannel/client/connection_pool.go:29-51, peer.go:144-166)."""
 import os
 import sys
+import time
 
 import torch
 
@@ -20,9 +21,14 @@ while step < max_step:
         ok, _ = kf.ops.request_variable((kf.current_rank() + 1) % np_, 'v', torch.ones(10))
         assert ok
     elif kf.current_rank() == 0:
+        # the peers that just left are still being disconnected by their reader threads: take the floor of a second
+        fds, threads = 1 << 30, 1 << 30
+        for _ in range(10):
+            fds = min(fds, len(os.listdir('/proc/self/fd')))
+            threads = min(threads, len(os.listdir('/proc/self/task')))
+            time.sleep(0.1)
         rss = int(open('/proc/self/statm').read().split()[1]) * os.sysconf('SC_PAGE_SIZE') >> 20
-        print('LEAK step %d fds %d threads %d rss_mib %d' % (step, len(os.listdir('/proc/self/fd')),
-                                                             len(os.listdir('/proc/self/task')), rss), flush=True)
+        print('LEAK step %d fds %d threads %d rss_mib %d' % (step, fds, threads, rss), flush=True)
     step += 1
     want = step_based_schedule(schedule, step, default=np_, strict=False)
     changed, detached = kf.resize_cluster(want)
