@@ -210,3 +210,50 @@ def test_p2p_model_ops(np_):
     """Selectors, ModelAveraging / RequestModel and their prefetching variants (native double buffer)."""
     res = run_workers(np_, os.path.join(ROOT, 'tests', 'workers', 'p2p_model_worker.py'), timeout=90)
     assert res.returncode == 0 and res.stdout.count('OK p2p-model') == np_, res.stdout[-3000:]
+
+
+def _state(pid):
+    try:
+        with open('/proc/%d/stat' % pid) as f:
+            return f.read().rsplit(')', 1)[1].split()[0]
+    except OSError:
+        return None  # gone (reaped)
+
+
+def test_workers_never_outlive_their_runner_and_a_killed_worker_stops_the_job(tmp_path):
+    """(1) SIGKILL of the runner: its workers are killed by the kernel (PR_SET_PDEATHSIG), nobody keeps a port or a
+    GPU. (2) SIGKILL of one worker in the middle of a job: the runner stops the others and reports 128 + 9 within
+    seconds (reference: local.RunAll cancels every sibling on the first failure, utils/runner/local/local.go:62-92)."""
+    import signal
+    import subprocess
+    import time
+    exe = os.path.join(ROOT, 'kungfu_b200', 'bin', 'kungfu-run')
+    base = 20000 + (os.getpid() * 29) % 11000
+    run = subprocess.Popen([exe, '-q', '-np', '2', '-port-range', '%d-%d' % (base, base + 8), '-port', str(base + 20), 'sleep', '60'],
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    kids = []
+    for _ in range(50):
+        kids = [int(p) for p in subprocess.run(['pgrep', '-P', str(run.pid)], stdout=subprocess.PIPE, text=True).stdout.split()]
+        if len(kids) == 2:
+            break
+        time.sleep(0.1)
+    assert len(kids) == 2
+    run.send_signal(signal.SIGKILL)
+    run.wait(timeout=10)
+    for _ in range(50):
+        if all(_state(k) in (None, 'Z', 'X') for k in kids):
+            break
+        time.sleep(0.1)
+    assert all(_state(k) in (None, 'Z', 'X') for k in kids), [(_state(k)) for k in kids]  # dead (a zombie until init reaps it)
+
+    script = tmp_path / 'victim.py'
+    script.write_text('import os, signal, time, torch\nimport kungfu_b200.torch as kf\n'
+                      'for i in range(400):\n'
+                      '    kf.ops.all_reduce_fn(torch.ones(1000))\n'
+                      '    if kf.current_rank() == 1 and i == 5:\n'
+                      '        os.kill(os.getpid(), signal.SIGKILL)\n'
+                      '    time.sleep(0.05)\n')
+    t0 = time.time()
+    res = run_workers(3, str(script), timeout=60)
+    assert res.returncode == 137 and 'exited with 137; stopping the others' in res.stdout, res.stdout[-2000:]
+    assert time.time() - t0 < 40
