@@ -28,3 +28,11 @@ def test_cli_fuzzing_leaves_no_files_behind_and_finds_no_crash():
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     assert set(os.listdir(ROOT)) == before
+
+
+def test_no_python_source_reads_a_name_it_never_binds():
+    """scripts/check_names.py over every Python file: the device-side modules and the GPU workers only execute on a
+    GPU box, so an un-imported or misspelt name in them must be caught here."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'check_names.py')], cwd=ROOT,
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-3000:]
