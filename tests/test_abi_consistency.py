@@ -165,3 +165,51 @@ def test_every_call_site_passes_what_the_entry_point_takes():
             problems.append('%s:%d passes %d arguments to %s, which takes %d' %
                             (os.path.relpath(path, ROOT), line, nargs, name, len(protos[name][1])))
     assert not problems, '\n'.join(problems)
+
+
+def test_struct_layouts_and_constants_match_the_header(tmp_path):
+    """kfb_comm / kfb_sgd_hyper as ctypes Structures against sizeof / offsetof printed by a C program that includes
+    the header, and every constant the Python side restates (dtype / op / algo codes, flag bits, table sizes)."""
+    import subprocess
+
+    from kungfu_b200.ops import _cuda as K
+    structs = {'kfb_comm': K.KfbComm, 'kfb_sgd_hyper': K.SgdHyper}
+    rename = {'bias_corr1': 'bias_corr1', 'bias_corr2': 'bias_corr2'}
+    consts = {'KFB_MAX_RANKS': K.MAX_RANKS, 'KFB_MAX_BLOCKS': K.MAX_BLOCKS, 'KFB_PAD_FLAG_WORDS': K.PAD_FLAG_WORDS,
+              'KFB_PAD_MISC_WORD': K.PAD_MISC_WORD, 'KFB_PAD_BYTES': K.PAD_BYTES, 'KFB_STATE_EPOCH_WORDS': K.STATE_EPOCH_WORDS,
+              'KFB_SCRATCH_FLOATS': K.SCRATCH_FLOATS, 'KFB_FUSE_SCRATCH_FLOATS': K.FUSE_SCRATCH_FLOATS,
+              'KFB_VAR_WORK_WORDS': K.VAR_WORK_WORDS, 'KFB_F32': K.F32, 'KFB_BF16': K.BF16, 'KFB_F16': K.F16, 'KFB_I32': K.I32,
+              'KFB_F64': K.F64, 'KFB_I64': K.I64, 'KFB_U8': K.U8, 'KFB_OP_SUM': K.OP_SUM, 'KFB_OP_MIN': K.OP_MIN,
+              'KFB_OP_MAX': K.OP_MAX, 'KFB_OP_PROD': K.OP_PROD, 'KFB_ALGO_ONESHOT': K.ALGO_ONESHOT,
+              'KFB_ALGO_TWOSHOT': K.ALGO_TWOSHOT, 'KFB_ALGO_NVLS': K.ALGO_NVLS, 'KFB_STEP_PRESIGNALED': K.STEP_PRESIGNALED,
+              'KFB_STEP_NO_EXIT_BARRIER': K.STEP_NO_EXIT_BARRIER, 'KFB_STEP_PARTIAL_NORM': K.STEP_PARTIAL_NORM}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "kungfu_b200.h"', 'int main(void) {']
+    for cname, st in structs.items():
+        lines.append('  printf("sizeof %s %%zu\\n", sizeof(%s));' % (cname, cname))
+        for fname, _ in st._fields_:
+            lines.append('  printf("offset %s.%s %%zu\\n", offsetof(%s, %s));' % (cname, fname, cname, rename.get(fname, fname)))
+    for c in consts:
+        lines.append('  printf("const %s %%lld\\n", (long long)(%s));' % (c, c))
+    lines += ['  return 0;', '}']
+    src = tmp_path / 'probe.c'
+    src.write_text('\n'.join(lines))
+    exe = str(tmp_path / 'probe')
+    subprocess.check_call(['gcc', '-std=c99', '-Wall', '-I', os.path.join(ROOT, 'include'), str(src), '-o', exe])
+    got = {}
+    for line in subprocess.run([exe], stdout=subprocess.PIPE, text=True, check=True).stdout.splitlines():
+        kind, key, val = line.split()
+        got[(kind, key)] = int(val)
+    for cname, st in structs.items():
+        assert got[('sizeof', cname)] == C.sizeof(st), (cname, got[('sizeof', cname)], C.sizeof(st))
+        for fname, _ in st._fields_:
+            assert got[('offset', '%s.%s' % (cname, fname))] == getattr(st, fname).offset, (cname, fname)
+    for c, v in consts.items():
+        assert got[('const', c)] == v, (c, got[('const', c)], v)
+    # the host-side dtype codes (a different, bit-packed encoding) against include/kungfu_host.h
+    from kungfu_b200 import _host as H
+    text = open(os.path.join(ROOT, 'include', 'kungfu_host.h')).read()
+    host_consts = dict(re.findall(r'\b(KF_[A-Z0-9_]+)\s*=\s*(-?\d+)', text))
+    for name, py in (('KF_F32', 'F32'), ('KF_F64', 'F64'), ('KF_F16', 'F16'), ('KF_BF16', 'BF16'), ('KF_I32', 'I32'), ('KF_I64', 'I64'),
+                     ('KF_U8', 'U8')):
+        if name in host_consts and hasattr(H, py):
+            assert int(host_consts[name]) == getattr(H, py), (name, host_consts[name], getattr(H, py))
