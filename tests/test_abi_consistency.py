@@ -205,11 +205,10 @@ def test_struct_layouts_and_constants_match_the_header(tmp_path):
             assert got[('offset', '%s.%s' % (cname, fname))] == getattr(st, fname).offset, (cname, fname)
     for c, v in consts.items():
         assert got[('const', c)] == v, (c, got[('const', c)], v)
-    # the host-side dtype codes (a different, bit-packed encoding) against include/kungfu_host.h
+    # the host-side dtype codes (the reference's bit-packed encoding) against the runtime's enum
     from kungfu_b200 import _host as H
-    text = open(os.path.join(ROOT, 'include', 'kungfu_host.h')).read()
-    host_consts = dict(re.findall(r'\b(KF_[A-Z0-9_]+)\s*=\s*(-?\d+)', text))
-    for name, py in (('KF_F32', 'F32'), ('KF_F64', 'F64'), ('KF_F16', 'F16'), ('KF_BF16', 'BF16'), ('KF_I32', 'I32'), ('KF_I64', 'I64'),
-                     ('KF_U8', 'U8')):
-        if name in host_consts and hasattr(H, py):
-            assert int(host_consts[name]) == getattr(H, py), (name, host_consts[name], getattr(H, py))
+    text = open(os.path.join(ROOT, 'csrc', 'core', 'base.hpp')).read()
+    codes = re.findall(r'\b([A-Z][A-Z0-9]+)\s*=\s*type_code\((\d+),\s*(\d+)\)', text)
+    assert len(codes) >= 13, codes
+    for name, cat, nbytes in codes:
+        assert getattr(H, name) == (int(cat) << 16) | (int(nbytes) << 8) | 8, name
