@@ -6,6 +6,8 @@
 Most of the device-side Python only runs on a GPU box; a misspelt or un-imported name there would first show up
 in the round-end GPU run. This walks every module with `ast`, keeps the chain of enclosing scopes (module,
 functions, lambdas, comprehensions, class bodies) and reports every name that is read but bound nowhere visible.
+A second pass resolves every alias of one of this repository's own modules (`from ..ops import _cuda as K`,
+also inside functions) and checks that `K.<attr>` exists in that module (all of them import without a GPU).
 Exit code 1 if anything is found."""
 import ast
 import builtins
@@ -84,4 +86,56 @@ for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
         mod=bound_names(tree)|set(dir(builtins))|{'__file__','__name__','__doc__','__builtins__','__spec__','__path__'}
         check(tree,[mod],p)
 print('undefined names: %d' % bad)
-sys.exit(1 if bad else 0)
+
+
+# ---- second pass: attributes of this repository's modules ------------------------------------------
+import importlib  # noqa: E402
+
+sys.path.insert(0, ROOT)
+missing = 0
+
+
+def _module_name(path):
+    rel = os.path.relpath(path, ROOT)[:-3].replace(os.sep, '.')
+    return rel[:-9] if rel.endswith('.__init__') else rel
+
+
+def _resolve(frm, level, pkg):
+    if level == 0:
+        return frm
+    parts = pkg.split('.')
+    return '.'.join(parts[:len(parts) - (level - 1)] + ([frm] if frm else []))
+
+
+for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
+    files = [base] if base.endswith('.py') else [os.path.join(r, f) for r, _, fs in os.walk(base) for f in fs if f.endswith('.py')]
+    for path in files:
+        tree = ast.parse(open(path).read())
+        mod = _module_name(path)
+        pkg = mod if path.endswith('__init__.py') else (mod.rsplit('.', 1)[0] if '.' in mod else '')
+        aliases = {}
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Import):
+                for a in node.names:
+                    if a.name.startswith('kungfu_b200') and a.asname:
+                        aliases[a.asname] = a.name
+            elif isinstance(node, ast.ImportFrom):
+                src = _resolve(node.module or '', node.level, pkg) if node.level else (node.module or '')
+                if not src.startswith('kungfu_b200'):
+                    continue
+                for a in node.names:
+                    try:
+                        importlib.import_module(src + '.' + a.name)  # only names that ARE modules
+                        aliases[a.asname or a.name] = src + '.' + a.name
+                    except Exception:
+                        pass
+        mods = {k: importlib.import_module(v) for k, v in aliases.items()}
+        rebound = {n.id for n in ast.walk(tree) if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Store)}
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Attribute) and isinstance(node.value, ast.Name) and isinstance(node.ctx, ast.Load) \
+                    and node.value.id in mods and node.value.id not in rebound and not hasattr(mods[node.value.id], node.attr):
+                print('%s:%d %s.%s: module %s has no such attribute' %
+                      (path, node.lineno, node.value.id, node.attr, mods[node.value.id].__name__))
+                missing += 1
+print('missing module attributes: %d' % missing)
+sys.exit(1 if bad or missing else 0)
