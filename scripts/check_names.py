@@ -8,6 +8,8 @@ in the round-end GPU run. This walks every module with `ast`, keeps the chain of
 functions, lambdas, comprehensions, class bodies) and reports every name that is read but bound nowhere visible.
 A second pass resolves every alias of one of this repository's own modules (`from ..ops import _cuda as K`,
 also inside functions) and checks that `K.<attr>` exists in that module (all of them import without a GPU).
+A third pass binds the arguments of every call of one of the repository's own functions or classes
+(`coll.all_reduce(comm, buf, n, ..., out=stage)`) against its signature: wrong arity or an unknown keyword.
 Exit code 1 if anything is found."""
 import ast
 import builtins
@@ -138,4 +140,61 @@ for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
                       (path, node.lineno, node.value.id, node.attr, mods[node.value.id].__name__))
                 missing += 1
 print('missing module attributes: %d' % missing)
-sys.exit(1 if bad or missing else 0)
+
+# ---- third pass: calls of this repository's own functions / classes against their signatures ----------
+import inspect  # noqa: E402
+
+checked = mismatched = 0
+for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
+    files = [base] if base.endswith('.py') else [os.path.join(r, f) for r, _, fs in os.walk(base) for f in fs if f.endswith('.py')]
+    for path in files:
+        tree = ast.parse(open(path).read())
+        mod = _module_name(path)
+        pkg = mod if path.endswith('__init__.py') else (mod.rsplit('.', 1)[0] if '.' in mod else '')
+        objs = {}
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Import):
+                for a in node.names:
+                    if a.name.startswith('kungfu_b200') and a.asname:
+                        objs[a.asname] = importlib.import_module(a.name)
+            elif isinstance(node, ast.ImportFrom):
+                src = _resolve(node.module or '', node.level, pkg) if node.level else (node.module or '')
+                if not src.startswith('kungfu_b200'):
+                    continue
+                try:
+                    m = importlib.import_module(src)
+                except Exception:
+                    continue
+                for a in node.names:
+                    try:
+                        objs[a.asname or a.name] = importlib.import_module(src + '.' + a.name)
+                    except Exception:
+                        if hasattr(m, a.name):
+                            objs[a.asname or a.name] = getattr(m, a.name)
+        rebound = {n.id for n in ast.walk(tree) if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Store)}
+        rebound |= {n.name for n in ast.walk(tree) if isinstance(n, (ast.FunctionDef, ast.ClassDef))}
+        for node in ast.walk(tree):
+            if not isinstance(node, ast.Call) or any(isinstance(a, ast.Starred) for a in node.args) \
+                    or any(k.arg is None for k in node.keywords):
+                continue
+            f, target = node.func, None
+            if isinstance(f, ast.Attribute) and isinstance(f.value, ast.Name) and f.value.id in objs and f.value.id not in rebound:
+                o = objs[f.value.id]
+                if inspect.ismodule(o) and hasattr(o, f.attr):
+                    target = getattr(o, f.attr)
+            elif isinstance(f, ast.Name) and f.id in objs and f.id not in rebound:
+                target = objs[f.id]
+            if inspect.isclass(target) and inspect.isfunction(target.__init__):
+                sig, args = inspect.signature(target.__init__), [None] * (len(node.args) + 1)
+            elif inspect.isfunction(target):
+                sig, args = inspect.signature(target), [None] * len(node.args)
+            else:
+                continue
+            checked += 1
+            try:
+                sig.bind(*args, **{k.arg: None for k in node.keywords})
+            except TypeError as e:
+                print('%s:%d %s(...): %s' % (path, node.lineno, ast.unparse(f), e))
+                mismatched += 1
+print('calls of own functions checked: %d, not matching the signature: %d' % (checked, mismatched))
+sys.exit(1 if bad or missing or mismatched else 0)
