@@ -9,7 +9,8 @@ functions, lambdas, comprehensions, class bodies) and reports every name that is
 A second pass resolves every alias of one of this repository's own modules (`from ..ops import _cuda as K`,
 also inside functions) and checks that `K.<attr>` exists in that module (all of them import without a GPU).
 A third pass binds the arguments of every call of one of the repository's own functions or classes
-(`coll.all_reduce(comm, buf, n, ..., out=stage)`) against its signature: wrong arity or an unknown keyword.
+(`coll.all_reduce(comm, buf, n, ..., out=stage)`) against its signature: wrong arity or an unknown keyword;
+a fourth does the same for `self.method(...)` inside the package's classes.
 Exit code 1 if anything is found."""
 import ast
 import builtins
@@ -197,4 +198,40 @@ for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
                 print('%s:%d %s(...): %s' % (path, node.lineno, ast.unparse(f), e))
                 mismatched += 1
 print('calls of own functions checked: %d, not matching the signature: %d' % (checked, mismatched))
-sys.exit(1 if bad or missing or mismatched else 0)
+
+# ---- fourth pass: self.method(...) inside the package's classes against the method found on the class ----
+# (methods that a dynamically composed base provides -- the optimizer mix-ins -- are not resolvable here and are skipped)
+self_checked = self_bad = 0
+pkg_root = os.path.join(ROOT, 'kungfu_b200')
+for r, _, fs in os.walk(pkg_root):
+    for fname in fs:
+        if not fname.endswith('.py') or fname == '__main__.py':
+            continue
+        path = os.path.join(r, fname)
+        try:
+            m = importlib.import_module(_module_name(path))
+        except Exception:
+            continue
+        for cls in [n for n in ast.parse(open(path).read()).body if isinstance(n, ast.ClassDef)]:
+            c = getattr(m, cls.name, None)
+            if not inspect.isclass(c):
+                continue
+            for node in ast.walk(cls):
+                if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and isinstance(node.func.value, ast.Name)
+                        and node.func.value.id == 'self' and hasattr(c, node.func.attr)):
+                    continue
+                if any(isinstance(a, ast.Starred) for a in node.args) or any(k.arg is None for k in node.keywords):
+                    continue
+                t = inspect.getattr_static(c, node.func.attr)
+                fn = t.__func__ if isinstance(t, (staticmethod, classmethod)) else t
+                if not inspect.isfunction(fn):
+                    continue
+                self_checked += 1
+                try:
+                    inspect.signature(fn).bind(*([None] * (len(node.args) + (0 if isinstance(t, staticmethod) else 1))),
+                                               **{k.arg: None for k in node.keywords})
+                except TypeError as e:
+                    print('%s:%d self.%s(...): %s' % (path, node.lineno, node.func.attr, e))
+                    self_bad += 1
+print('self.method calls checked: %d, not matching: %d' % (self_checked, self_bad))
+sys.exit(1 if bad or missing or mismatched or self_bad else 0)
