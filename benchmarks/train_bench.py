@@ -74,8 +74,15 @@ if is_bert:
     def loss_fn():
         return model(ids, mlm_labels=labels, nsp_labels=nsp, mlm_positions=mlm_pos)
 else:
-    kw = {'fused_bn': bool(args.fused_bn)} if not args.model.startswith('vgg') else {}
-    model = models.to_b200_layout(getattr(models, args.model)(**kw).to(dev), torch.bfloat16)
+    if hasattr(models, args.model):
+        kw = {'fused_bn': bool(args.fused_bn)} if not args.model.startswith('vgg') else {}
+        net = getattr(models, args.model)(**kw)
+    else:
+        # any other torchvision architecture by name, as the reference's benchmark accepts
+        # (benchmark_kungfu_torch.py: getattr(torchvision.models, args.model)()); random init, stock torch layers
+        import torchvision
+        net = getattr(torchvision.models, args.model)(weights=None)
+    model = models.to_b200_layout(net.to(dev), torch.bfloat16)
     x = torch.randn(B, 3, args.image_size, args.image_size, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
     y = torch.randint(0, 1000, (B, ), device=dev)
     unit = 'img/s'
