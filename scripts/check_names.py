@@ -18,76 +18,92 @@ import os
 import sys
 
 def bound_names(node):
-    """names bound directly in this scope (not descending into nested function/class/lambda/comprehension scopes)"""
-    out=set()
-    def visit(n, top=False):
+    """Names bound directly in this scope (nested function / class / lambda / comprehension scopes are not entered)."""
+    out = set()
+
+    def visit(n):
         for ch in ast.iter_child_nodes(n):
-            if isinstance(ch,(ast.FunctionDef,ast.AsyncFunctionDef,ast.ClassDef)):
-                out.add(ch.name); 
-                for d in ch.decorator_list: visit(d)
+            if isinstance(ch, (ast.FunctionDef, ast.AsyncFunctionDef, ast.ClassDef)):
+                out.add(ch.name)
+                for d in ch.decorator_list:
+                    visit(d)
                 continue
-            if isinstance(ch,ast.Lambda): continue
-            if isinstance(ch,(ast.ListComp,ast.SetComp,ast.DictComp,ast.GeneratorExp)):
-                # comprehension targets are local to the comprehension, but walrus not used; skip
+            if isinstance(ch, (ast.Lambda, ast.ListComp, ast.SetComp, ast.DictComp, ast.GeneratorExp)):
                 continue
-            if isinstance(ch,ast.Import):
-                for a in ch.names: out.add((a.asname or a.name).split('.')[0])
-            elif isinstance(ch,ast.ImportFrom):
-                for a in ch.names: out.add(a.asname or a.name)
-            elif isinstance(ch,ast.Name) and isinstance(ch.ctx,(ast.Store,ast.Del)): out.add(ch.id)
-            elif isinstance(ch,ast.ExceptHandler) and ch.name: out.add(ch.name)
-            elif isinstance(ch,(ast.Global,ast.Nonlocal)):
-                for a in ch.names: out.add(a)
+            if isinstance(ch, ast.Import):
+                out.update((a.asname or a.name).split('.')[0] for a in ch.names)
+            elif isinstance(ch, ast.ImportFrom):
+                out.update(a.asname or a.name for a in ch.names)
+            elif isinstance(ch, ast.Name) and isinstance(ch.ctx, (ast.Store, ast.Del)):
+                out.add(ch.id)
+            elif isinstance(ch, ast.ExceptHandler) and ch.name:
+                out.add(ch.name)
+            elif isinstance(ch, (ast.Global, ast.Nonlocal)):
+                out.update(ch.names)
             visit(ch)
+
     visit(node)
     return out
 
+
 def args_of(fn):
-    a=fn.args; out={x.arg for x in a.args+a.kwonlyargs+a.posonlyargs}
-    if a.vararg: out.add(a.vararg.arg)
-    if a.kwarg: out.add(a.kwarg.arg)
+    a = fn.args
+    out = {x.arg for x in a.args + a.kwonlyargs + a.posonlyargs}
+    for extra in (a.vararg, a.kwarg):
+        if extra:
+            out.add(extra.arg)
     return out
 
-bad=0
+
+bad = 0
+
+
 def check(node, scopes, path):
+    """Every name read under `node` must be bound in one of `scopes` (innermost last)."""
     global bad
     for ch in ast.iter_child_nodes(node):
-        if isinstance(ch,(ast.FunctionDef,ast.AsyncFunctionDef)):
-            for d in ch.decorator_list+ch.args.defaults+[x for x in ch.args.kw_defaults if x]: check_expr(d,scopes,path)
-            check(ch, scopes+[bound_names(ch)|args_of(ch)], path)
-        elif isinstance(ch,ast.Lambda):
-            check(ch, scopes+[args_of(ch)], path)
-        elif isinstance(ch,ast.ClassDef):
-            # class body names are visible in the body itself only; methods see enclosing function/module scopes
-            body_names=bound_names(ch)
-            for b in ch.bases+ch.decorator_list: check_expr(b,scopes,path)
+        if isinstance(ch, (ast.FunctionDef, ast.AsyncFunctionDef)):
+            for d in ch.decorator_list + ch.args.defaults + [x for x in ch.args.kw_defaults if x]:
+                check_expr(d, scopes, path)
+            check(ch, scopes + [bound_names(ch) | args_of(ch)], path)
+        elif isinstance(ch, ast.Lambda):
+            check(ch, scopes + [args_of(ch)], path)
+        elif isinstance(ch, ast.ClassDef):
+            # names of a class body are visible in the body itself only; its methods see the enclosing scopes
+            body_names = bound_names(ch)
+            for b in ch.bases + ch.decorator_list:
+                check_expr(b, scopes, path)
             for stmt in ch.body:
-                if isinstance(stmt,(ast.FunctionDef,ast.AsyncFunctionDef)):
-                    check(ast.Module(body=[stmt],type_ignores=[]), scopes, path)
-                else:
-                    check(ast.Module(body=[stmt],type_ignores=[]), scopes+[body_names], path)
-        elif isinstance(ch,(ast.ListComp,ast.SetComp,ast.DictComp,ast.GeneratorExp)):
-            names=set()
-            for g in ch.generators:
-                for n in ast.walk(g.target):
-                    if isinstance(n,ast.Name): names.add(n.id)
-            check(ch, scopes+[names], path)
-        elif isinstance(ch,ast.Name) and isinstance(ch.ctx,ast.Load):
+                inner = scopes if isinstance(stmt, (ast.FunctionDef, ast.AsyncFunctionDef)) else scopes + [body_names]
+                check(ast.Module(body=[stmt], type_ignores=[]), inner, path)
+        elif isinstance(ch, (ast.ListComp, ast.SetComp, ast.DictComp, ast.GeneratorExp)):
+            names = {n.id for g in ch.generators for n in ast.walk(g.target) if isinstance(n, ast.Name)}
+            check(ch, scopes + [names], path)
+        elif isinstance(ch, ast.Name) and isinstance(ch.ctx, ast.Load):
             if not any(ch.id in s for s in scopes):
-                print('%s:%d undefined name %s'%(path,ch.lineno,ch.id)); bad+=1
+                print('%s:%d undefined name %s' % (path, ch.lineno, ch.id))
+                bad += 1
         else:
             check(ch, scopes, path)
-def check_expr(e,scopes,path):
-    check(ast.Module(body=[ast.Expr(e)],type_ignores=[]),scopes,path)
+
+
+def check_expr(e, scopes, path):
+    check(ast.Module(body=[ast.Expr(e)], type_ignores=[]), scopes, path)
+
+
+def python_files(base):
+    return [base] if base.endswith('.py') else [os.path.join(r, f) for r, _, fs in os.walk(base) for f in fs if f.endswith('.py')]
+
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DEFAULT = ['kungfu_b200', 'kungfu', 'tests', 'benchmarks', 'examples', 'scripts', 'bench.py', '__graft_entry__.py', 'setup.py']
-for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
-    files=[base] if base.endswith('.py') else [os.path.join(r,f) for r,_,fs in os.walk(base) for f in fs if f.endswith('.py')]
-    for p in files:
-        tree=ast.parse(open(p).read())
-        mod=bound_names(tree)|set(dir(builtins))|{'__file__','__name__','__doc__','__builtins__','__spec__','__path__'}
-        check(tree,[mod],p)
+TARGETS = sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]
+MODULE_GLOBALS = set(dir(builtins)) | {'__file__', '__name__', '__doc__', '__builtins__', '__spec__', '__path__'}
+for base in TARGETS:
+    for p in python_files(base):
+        with open(p) as fh:
+            tree = ast.parse(fh.read())
+        check(tree, [bound_names(tree) | MODULE_GLOBALS], p)
 print('undefined names: %d' % bad)
 
 
@@ -110,9 +126,8 @@ def _resolve(frm, level, pkg):
     return '.'.join(parts[:len(parts) - (level - 1)] + ([frm] if frm else []))
 
 
-for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
-    files = [base] if base.endswith('.py') else [os.path.join(r, f) for r, _, fs in os.walk(base) for f in fs if f.endswith('.py')]
-    for path in files:
+for base in TARGETS:
+    for path in python_files(base):
         tree = ast.parse(open(path).read())
         mod = _module_name(path)
         pkg = mod if path.endswith('__init__.py') else (mod.rsplit('.', 1)[0] if '.' in mod else '')
@@ -146,9 +161,8 @@ print('missing module attributes: %d' % missing)
 import inspect  # noqa: E402
 
 checked = mismatched = 0
-for base in (sys.argv[1:] or [os.path.join(ROOT, d) for d in DEFAULT]):
-    files = [base] if base.endswith('.py') else [os.path.join(r, f) for r, _, fs in os.walk(base) for f in fs if f.endswith('.py')]
-    for path in files:
+for base in TARGETS:
+    for path in python_files(base):
         tree = ast.parse(open(path).read())
         mod = _module_name(path)
         pkg = mod if path.endswith('__init__.py') else (mod.rsplit('.', 1)[0] if '.' in mod else '')
