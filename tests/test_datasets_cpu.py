@@ -102,3 +102,33 @@ def test_elastic_batch_sampler_covers_every_sample_once_across_resizes():
     import pytest
     with pytest.raises(ValueError):
         s.reshard(0, 3)
+
+
+def test_elastic_batch_sampler_random_resize_sequences():
+    """Property: for ANY sequence of cluster sizes dividing the global batch, the concatenated per-step unions equal
+    what a single worker would have drawn, epoch after epoch, shuffled or not."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+
+    from kungfu_b200.datasets import ElasticBatchSampler
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.integers(30, 400), st.sampled_from([12, 24, 60]), st.booleans(), st.booleans(),
+           st.lists(st.tuples(st.sampled_from([1, 2, 3, 4, 6, 12]), st.integers(1, 9)), min_size=1, max_size=8))
+    def prop(n, gb, shuffle, drop_last, plan):
+        consumed, seen = 0, []
+        for size, steps in plan:
+            ws = [ElasticBatchSampler(n, gb, r, size, shuffle=shuffle, seed=3, consumed=consumed, drop_last=drop_last) for r in range(size)]
+            for _ in range(steps):
+                seen += [i for w in ws for i in w.next_indices()]
+            consumed = ws[0].consumed
+        ref = ElasticBatchSampler(n, gb, 0, 1, shuffle=shuffle, seed=3, drop_last=drop_last)
+        want = [i for _ in range(len(seen) // gb) for i in ref.next_indices()]
+        assert seen == want
+        assert all(0 <= i < n for i in seen)
+        per_epoch = max(n - n % gb, gb) if drop_last else n
+        if n >= gb:
+            first = seen[:per_epoch]
+            assert len(set(first)) == len(first)  # an epoch never repeats a sample
+
+    prop()
