@@ -335,3 +335,36 @@ def test_json_and_hostfile_parsers_survive_mutated_and_deeply_nested_input():
     for depth in (65, 1000, 100000):
         assert l.kf_cluster_resize(b'[' * depth, 2, buf, len(buf)) < 0
         assert l.kf_cluster_resize(b'{"a":' * depth, 2, buf, len(buf)) < 0
+
+
+def test_cluster_resize_properties_under_random_histories():
+    """Property (hypothesis): along ANY sequence of sizes, a resized cluster has exactly that many distinct workers,
+    all on hosts that have a runner; shrinking keeps a prefix; growing keeps every existing worker in place and puts
+    the new ones on the least loaded host at a port nobody on that host uses."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+    l = _lib()
+
+    @settings(max_examples=80, deadline=None)
+    @given(st.integers(1, 4), st.integers(2000, 60000), st.lists(st.integers(0, 24), min_size=1, max_size=10))
+    def prop(n_hosts, base_port, sizes):
+        runners = ['10.1.0.%d:38080' % (i + 1) for i in range(n_hosts)]
+        cur = {'Runners': runners, 'Workers': ['10.1.0.1:%d' % base_port]}
+        for n in sizes:
+            nxt = json.loads(_s(l.kf_cluster_resize, json.dumps(cur).encode(), n))
+            w_old, w_new = cur['Workers'], nxt['Workers']
+            assert nxt['Runners'] == runners and len(w_new) == n and len(set(w_new)) == n
+            assert all(w.split(':')[0] in {r.split(':')[0] for r in runners} for w in w_new)
+            if n <= len(w_old):
+                assert w_new == w_old[:n]
+            else:
+                assert w_new[:len(w_old)] == w_old
+                for k in range(len(w_old), n):  # each addition goes to a least loaded host
+                    load = {r.split(':')[0]: 0 for r in runners}
+                    for w in w_new[:k]:
+                        load[w.split(':')[0]] += 1
+                    assert load[w_new[k].split(':')[0]] == min(load.values())
+            if n > 0:
+                cur = nxt
+
+    prop()
