@@ -68,6 +68,6 @@ for epoch in range(args.epochs):
         acc = (model(x_test.to(device)).argmax(1).cpu() == y_test).float().mean()
     acc = kf.ops.all_reduce_fn(acc.reshape(1)) / size
     if rank == 0:
-        print('epoch %d loss %.4f test accuracy %.4f' % (epoch, float(loss), float(acc)))
+        print('epoch %d loss %.4f test accuracy %.4f' % (epoch, float(loss.detach()), float(acc)))
 if rank == 0 and args.save:
     torch.save(model.state_dict(), args.save)
