@@ -24,7 +24,7 @@ def test_tracked_root_entries_are_the_expected_ones():
 
 def test_cli_fuzzing_leaves_no_files_behind_and_finds_no_crash():
     before = set(os.listdir(ROOT))
-    r = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'fuzz_cli.py'), '-n', '40', '--seed', '7'], cwd=ROOT,
+    r = subprocess.run([sys.executable, os.path.join(ROOT, 'scripts', 'fuzz_cli.py'), '-n', '25', '--seed', '7'], cwd=ROOT,
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
     assert set(os.listdir(ROOT)) == before
