@@ -223,6 +223,19 @@ def _state(pid):
         return None  # gone (reaped)
 
 
+def _children(pid):
+    out = []
+    for d in os.listdir('/proc'):
+        if d.isdigit():
+            try:
+                with open('/proc/%s/stat' % d) as f:
+                    if int(f.read().rsplit(')', 1)[1].split()[1]) == pid:
+                        out.append(int(d))
+            except (OSError, ValueError, IndexError):
+                pass
+    return out
+
+
 def test_workers_never_outlive_their_runner_and_a_killed_worker_stops_the_job(tmp_path):
     """(1) SIGKILL of the runner: its workers are killed by the kernel (PR_SET_PDEATHSIG), nobody keeps a port or a
     GPU. (2) SIGKILL of one worker in the middle of a job: the runner stops the others and reports 128 + 9 within
@@ -236,7 +249,7 @@ def test_workers_never_outlive_their_runner_and_a_killed_worker_stops_the_job(tm
                            stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
     kids = []
     for _ in range(50):
-        kids = [int(p) for p in subprocess.run(['pgrep', '-P', str(run.pid)], stdout=subprocess.PIPE, text=True).stdout.split()]
+        kids = _children(run.pid)
         if len(kids) == 2:
             break
         time.sleep(0.1)
